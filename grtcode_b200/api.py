@@ -1,0 +1,430 @@
+"""ctypes bindings of ``libgrtcode.so`` -- the reference's C API on sm_100a.
+
+Every function below is the entry point of the same name in the reference's
+``libgas_optics`` / ``liblongwave`` / ``libshortwave`` / utilities
+(include/*.h cite the reference headers), loaded from the in-tree shared
+libraries built by ``__graft_entry__.build()``.  There is no fallback: if the
+libraries are missing, or no GPU is visible, the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_HOST = os.path.join(HERE, "libgrtcode.so")
+LIB_CUDA = os.path.join(HERE, "libgrt_sm100.so")
+
+WAVENUMBER_SWEEP, LINE_SWEEP, LINE_SAMPLE = 0, 1, 2   # include/gas_optics.h
+NUM_MOLS, NUM_CFCS, NUM_CIAS, MAX_NUM_CIAS, DIR_PATH_LEN = 53, 21, 2, 3, 1024
+
+
+class GrtcodeError(RuntimeError):
+    def __init__(self, code: int, what: str, text: str):
+        super().__init__(f"{what} failed with code {code}: {text}")
+        self.code = code
+
+
+class SpectralGrid(C.Structure):
+    _fields_ = [("dw", C.c_double), ("n", C.c_uint64), ("wn", C.c_double), ("w0", C.c_double)]
+
+
+class Optics(C.Structure):
+    _fields_ = [("device", C.c_int), ("g", C.c_void_p), ("grid", SpectralGrid),
+                ("num_layers", C.c_int), ("omega", C.c_void_p), ("tau", C.c_void_p)]
+
+
+class Longwave(C.Structure):
+    _fields_ = [("num_levels", C.c_int), ("grid", SpectralGrid), ("device", C.c_int),
+                ("layer_temperature", C.c_void_p), ("level_temperature", C.c_void_p),
+                ("emissivity", C.c_void_p), ("flux_up", C.c_void_p), ("flux_down", C.c_void_p)]
+
+
+class Shortwave(C.Structure):
+    _fields_ = [("num_levels", C.c_int), ("grid", SpectralGrid), ("device", C.c_int),
+                ("solar_flux", C.c_void_p), ("sfc_alpha_dir", C.c_void_p),
+                ("sfc_alpha_dif", C.c_void_p), ("flux_up", C.c_void_p), ("flux_down", C.c_void_p)]
+
+
+class SolarFlux(C.Structure):
+    _fields_ = [("grid", SpectralGrid), ("incident_flux", C.POINTER(C.c_double)),
+                ("n", C.c_uint64)]
+
+
+class GasOpticsStruct(C.Structure):
+    _fields_ = [("device", C.c_int), ("num_levels", C.c_int), ("num_layers", C.c_int),
+                ("num_molecules", C.c_int), ("molecule_bit_field", C.c_uint64),
+                ("molecule_ids", C.c_int*NUM_MOLS), ("num_lines", C.c_uint64*NUM_MOLS),
+                ("num_cfcs", C.c_int), ("cfc_bit_field", C.c_uint64), ("num_cias", C.c_int),
+                ("cia_bit_field", C.c_uint64), ("cia_pairs", (C.c_int*2)*MAX_NUM_CIAS),
+                ("h2o_ctm_dir", C.c_char*DIR_PATH_LEN), ("use_h2o_ctm", C.c_int),
+                ("o3_ctm_file", C.c_char*DIR_PATH_LEN), ("use_o3_ctm", C.c_int),
+                ("grid", SpectralGrid), ("hitran_path", C.c_char*DIR_PATH_LEN),
+                ("wcutoff", C.c_double), ("optical_depth_method", C.c_int),
+                ("x", C.c_void_p), ("x_cfc", C.c_void_p), ("x_cia", C.c_void_p),
+                ("sm100", C.c_void_p)]
+
+
+_dbl_p = C.POINTER(C.c_double)
+_lib = None
+_cuda = None
+
+
+def libraries_present() -> bool:
+    return os.path.exists(LIB_HOST) and os.path.exists(LIB_CUDA)
+
+
+def load():
+    """Load the two shared libraries (raises if they have not been built)."""
+    global _lib, _cuda
+    if _lib is not None:
+        return _lib
+    if not libraries_present():
+        raise FileNotFoundError(
+            f"{LIB_CUDA} / {LIB_HOST} not built: run `python -c 'import __graft_entry__ as g; "
+            "g.build()'` (there is no CPU fallback)")
+    _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
+    L = C.CDLL(LIB_HOST, mode=C.RTLD_GLOBAL)
+    L.create_spectral_grid.argtypes = [C.POINTER(SpectralGrid), C.c_double, C.c_double, C.c_double]
+    L.create_device.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.get_num_gpus.argtypes = [C.POINTER(C.c_int), C.c_int]
+    L.create_optics.argtypes = [C.POINTER(Optics), C.c_int, C.POINTER(SpectralGrid),
+                                C.POINTER(C.c_int)]
+    L.destroy_optics.argtypes = [C.POINTER(Optics)]
+    L.add_optics.argtypes = [C.POINTER(C.POINTER(Optics)), C.c_int, C.POINTER(Optics)]
+    L.update_optics.argtypes = [C.POINTER(Optics), _dbl_p, _dbl_p, _dbl_p]
+    L.optical_properties.argtypes = [C.POINTER(Optics), _dbl_p, _dbl_p, _dbl_p]
+    L.create_gas_optics.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, C.POINTER(SpectralGrid),
+                                    C.POINTER(C.c_int), C.c_char_p, C.c_char_p, C.c_char_p,
+                                    C.POINTER(C.c_double), C.POINTER(C.c_int)]
+    L.destroy_gas_optics.argtypes = [C.POINTER(GasOpticsStruct)]
+    L.add_molecule.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, C.POINTER(C.c_double),
+                               C.POINTER(C.c_double)]
+    L.set_molecule_ppmv.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, _dbl_p]
+    L.add_cfc.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, C.c_char_p]
+    L.set_cfc_ppmv.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, _dbl_p]
+    L.add_cia.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, C.c_int, C.c_char_p]
+    L.set_cia_ppmv.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, _dbl_p]
+    L.calculate_optical_depth.argtypes = [C.POINTER(GasOpticsStruct), _dbl_p, _dbl_p,
+                                          C.POINTER(Optics)]
+    L.get_num_molecules.argtypes = [C.POINTER(GasOpticsStruct), C.POINTER(C.c_int)]
+    L.gas_optics_stats.argtypes = [C.POINTER(GasOpticsStruct), C.POINTER(C.c_uint64)]
+    L.rayleigh_scattering.argtypes = [C.POINTER(Optics), _dbl_p]
+    L.create_longwave.argtypes = [C.POINTER(Longwave), C.c_int, C.POINTER(SpectralGrid),
+                                  C.POINTER(C.c_int)]
+    L.destroy_longwave.argtypes = [C.POINTER(Longwave)]
+    L.calculate_lw_fluxes.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), C.c_double, _dbl_p,
+                                      _dbl_p, _dbl_p, _dbl_p, _dbl_p]
+    L.calculate_lw_column.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), _dbl_p, C.c_double,
+                                      _dbl_p, _dbl_p, _dbl_p, _dbl_p, _dbl_p]
+    L.create_shortwave.argtypes = [C.POINTER(Shortwave), C.c_int, C.POINTER(SpectralGrid),
+                                   C.POINTER(C.c_int)]
+    L.destroy_shortwave.argtypes = [C.POINTER(Shortwave)]
+    L.calculate_sw_fluxes.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), C.c_double,
+                                      C.c_double, _dbl_p, _dbl_p, C.c_double, _dbl_p, _dbl_p,
+                                      _dbl_p]
+    L.calculate_sw_column.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), _dbl_p, C.c_double,
+                                      C.c_double, _dbl_p, _dbl_p, C.c_double, _dbl_p, _dbl_p,
+                                      _dbl_p]
+    L.create_solar_flux.argtypes = [C.POINTER(SolarFlux), C.POINTER(SpectralGrid), C.c_char_p]
+    L.destroy_solar_flux.argtypes = [C.POINTER(SolarFlux)]
+    L.integrate_fluxes.argtypes = [C.c_int, C.c_int, C.POINTER(SpectralGrid), C.c_void_p, _dbl_p]
+    L.heating_rates.argtypes = [C.c_int, _dbl_p, _dbl_p, _dbl_p, _dbl_p]
+    L.grtcode_errstr.argtypes = [C.c_int, C.c_char_p, C.c_int]
+    L.grt_tips_q.restype = C.c_double
+    L.grt_tips_q.argtypes = [C.c_int, C.c_double, C.c_int]
+    _cuda.grt_measure_fma_peak.argtypes = [C.c_int, _dbl_p, _dbl_p]
+    _cuda.grt_synchronize.argtypes = [C.c_int]
+    _cuda.grt_stream_handle.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    _cuda.grt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
+    _cuda.grt_host_free.argtypes = [C.c_void_p]
+    _cuda.grt_copy_to_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
+    _lib = L
+    return L
+
+
+def cuda_layer():
+    load()
+    return _cuda
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        buf = C.create_string_buffer(4096)
+        _lib.grtcode_errstr(rc, buf, 4096)
+        raise GrtcodeError(rc, what, buf.value.decode(errors="replace").strip())
+
+
+def _dp(a: np.ndarray):
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_dbl_p)
+
+
+def _f64(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def num_gpus() -> int:
+    n = C.c_int(0)
+    _check(load().get_num_gpus(C.byref(n), 0), "get_num_gpus")
+    return n.value
+
+
+def spectral_grid(w0: float, wn: float, dw: float) -> SpectralGrid:
+    g = SpectralGrid()
+    _check(load().create_spectral_grid(C.byref(g), w0, wn, dw), "create_spectral_grid")
+    return g
+
+
+def tips_q(mol: int, t: float, iso: int) -> float:
+    return float(load().grt_tips_q(mol, t, iso))
+
+
+def stream_handle(device: int) -> int:
+    """cudaStream_t of the library's stream on ``device`` (for event timing)."""
+    h = C.c_void_p()
+    if cuda_layer().grt_stream_handle(device, C.byref(h)) != 0:
+        raise RuntimeError("grt_stream_handle failed")
+    return h.value or 0
+
+
+def measure_fma_peak(device: int = 0) -> tuple[float, float]:
+    a, b = C.c_double(0.), C.c_double(0.)
+    if cuda_layer().grt_measure_fma_peak(device, C.byref(a), C.byref(b)) != 0:
+        raise RuntimeError("grt_measure_fma_peak failed")
+    return a.value, b.value
+
+
+class OpticsObject:
+    """Optics_t on a GPU (include/optics.h)."""
+
+    def __init__(self, num_layers: int, grid: SpectralGrid, device: int = 0, _create=True):
+        self.L = load()
+        self.o = Optics()
+        self.shape = (num_layers, int(grid.n))
+        self._live = False
+        if _create:
+            dev = C.c_int(device)
+            _check(self.L.create_optics(C.byref(self.o), num_layers, C.byref(grid),
+                                        C.byref(dev)), "create_optics")
+            self._live = True
+
+    def arrays(self, tau=True, omega=False, g=False):
+        out = []
+        bufs = []
+        for want in (tau, omega, g):
+            bufs.append(np.empty(self.shape) if want else None)
+        _check(self.L.optical_properties(
+            C.byref(self.o), *[(_dp(b) if b is not None else None) for b in bufs]),
+            "optical_properties")
+        out = [b for b in bufs if b is not None]
+        return out[0] if len(out) == 1 else out
+
+    @property
+    def tau(self) -> np.ndarray:
+        return self.arrays(True, False, False)
+
+    def update(self, tau, omega, g):
+        _check(self.L.update_optics(C.byref(self.o), _dp(_f64(tau)), _dp(_f64(omega)),
+                                    _dp(_f64(g))), "update_optics")
+
+    def close(self):
+        if self._live:
+            _check(self.L.destroy_optics(C.byref(self.o)), "destroy_optics")
+            self._live = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def add_optics(parts: list[OpticsObject]) -> OpticsObject:
+    L = load()
+    arr = (C.POINTER(Optics)*len(parts))(*[C.pointer(p.o) for p in parts])
+    grid = parts[0].o.grid
+    out = OpticsObject(parts[0].shape[0], grid, _create=False)
+    _check(L.add_optics(arr, len(parts), C.byref(out.o)), "add_optics")
+    out._live = True
+    return out
+
+
+def rayleigh_scattering(optics: OpticsObject, p_mb):
+    _check(load().rayleigh_scattering(C.byref(optics.o), _dp(_f64(p_mb))), "rayleigh_scattering")
+
+
+class GasOptics:
+    """GasOptics_t (include/gas_optics.h): create -> add_* -> set_*_ppmv -> optical depth."""
+
+    def __init__(self, num_levels: int, grid: SpectralGrid, hitran: str,
+                 h2o_ctm_dir: str | None = None, o3_ctm: str | None = None,
+                 method: int | None = LINE_SAMPLE, device: int = 0,
+                 wcutoff: float | None = None):
+        self.L = load()
+        self.s = GasOpticsStruct()
+        self.grid = grid
+        self.num_levels = num_levels
+        dev = C.c_int(device)
+        m = C.c_int(method) if method is not None else None
+        wc = C.c_double(wcutoff) if wcutoff is not None else None
+        self._live = False
+        _check(self.L.create_gas_optics(
+            C.byref(self.s), num_levels, C.byref(grid), C.byref(dev), hitran.encode(),
+            h2o_ctm_dir.encode() if h2o_ctm_dir else None, o3_ctm.encode() if o3_ctm else None,
+            C.byref(wc) if wc is not None else None, C.byref(m) if m is not None else None),
+            "create_gas_optics")
+        self._live = True
+
+    def add_molecule(self, mol: int, wmin: float | None = None, wmax: float | None = None):
+        a = C.byref(C.c_double(wmin)) if wmin is not None else None
+        b = C.byref(C.c_double(wmax)) if wmax is not None else None
+        _check(self.L.add_molecule(C.byref(self.s), mol, a, b), "add_molecule")
+
+    def add_cfc(self, cfc: int, path: str):
+        _check(self.L.add_cfc(C.byref(self.s), cfc, path.encode()), "add_cfc")
+
+    def add_cia(self, a: int, b: int, path: str):
+        _check(self.L.add_cia(C.byref(self.s), a, b, path.encode()), "add_cia")
+
+    def set_ppmv(self, kind: str, ident: int, ppmv):
+        fn = {"mol": self.L.set_molecule_ppmv, "cfc": self.L.set_cfc_ppmv,
+              "cia": self.L.set_cia_ppmv}[kind]
+        _check(fn(C.byref(self.s), ident, _dp(_f64(ppmv))), f"set_{kind}_ppmv")
+
+    def optical_depth(self, p_mb, t, optics: OpticsObject):
+        _check(self.L.calculate_optical_depth(C.byref(self.s), _dp(_f64(p_mb)), _dp(_f64(t)),
+                                              C.byref(optics.o)), "calculate_optical_depth")
+
+    def num_molecules(self) -> int:
+        n = C.c_int(0)
+        _check(self.L.get_num_molecules(C.byref(self.s), C.byref(n)), "get_num_molecules")
+        return n.value
+
+    def stats(self) -> dict:
+        out = (C.c_uint64*4)()
+        _check(self.L.gas_optics_stats(C.byref(self.s), out), "gas_optics_stats")
+        return {"records": out[0], "samples": out[1], "launches": out[2], "lorentz": out[3]}
+
+    def close(self):
+        if self._live:
+            _check(self.L.destroy_gas_optics(C.byref(self.s)), "destroy_gas_optics")
+            self._live = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class LongwaveSolver:
+    def __init__(self, num_levels: int, grid: SpectralGrid, device: int = 0):
+        self.L = load()
+        self.s = Longwave()
+        self.num_levels = num_levels
+        self.n = int(grid.n)
+        dev = C.c_int(device)
+        self._live = False
+        _check(self.L.create_longwave(C.byref(self.s), num_levels, C.byref(grid), C.byref(dev)),
+               "create_longwave")
+        self._live = True
+
+    def fluxes(self, optics: OpticsObject, t_surf, t_layers, t_levels, emis):
+        up = np.empty((self.num_levels, self.n))
+        dn = np.empty((self.num_levels, self.n))
+        _check(self.L.calculate_lw_fluxes(C.byref(self.s), C.byref(optics.o), float(t_surf),
+                                          _dp(_f64(t_layers)), _dp(_f64(t_levels)),
+                                          _dp(_f64(emis)), _dp(up), _dp(dn)),
+               "calculate_lw_fluxes")
+        return up, dn
+
+    def column(self, gas: OpticsObject, p_mb, t_surf, t_layers, t_levels, emis):
+        up = np.empty(self.num_levels)
+        dn = np.empty(self.num_levels)
+        _check(self.L.calculate_lw_column(C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)),
+                                          float(t_surf), _dp(_f64(t_layers)), _dp(_f64(t_levels)),
+                                          _dp(_f64(emis)), _dp(up), _dp(dn)),
+               "calculate_lw_column")
+        return up, dn
+
+    def close(self):
+        if self._live:
+            _check(self.L.destroy_longwave(C.byref(self.s)), "destroy_longwave")
+            self._live = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class ShortwaveSolver:
+    def __init__(self, num_levels: int, grid: SpectralGrid, device: int = 0):
+        self.L = load()
+        self.s = Shortwave()
+        self.num_levels = num_levels
+        self.n = int(grid.n)
+        dev = C.c_int(device)
+        self._live = False
+        _check(self.L.create_shortwave(C.byref(self.s), num_levels, C.byref(grid), C.byref(dev)),
+               "create_shortwave")
+        self._live = True
+
+    def fluxes(self, optics: OpticsObject, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar):
+        up = np.empty((self.num_levels, self.n))
+        dn = np.empty((self.num_levels, self.n))
+        _check(self.L.calculate_sw_fluxes(C.byref(self.s), C.byref(optics.o), float(mu_dir),
+                                          float(mu_dif), _dp(_f64(alb_dir)), _dp(_f64(alb_dif)),
+                                          float(tsi), _dp(_f64(solar)), _dp(up), _dp(dn)),
+               "calculate_sw_fluxes")
+        return up, dn
+
+    def column(self, gas: OpticsObject, p_mb, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar):
+        up = np.empty(self.num_levels)
+        dn = np.empty(self.num_levels)
+        a1 = _f64(alb_dir)
+        a2 = a1 if alb_dif is alb_dir else _f64(alb_dif)
+        _check(self.L.calculate_sw_column(C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)),
+                                          float(mu_dir), float(mu_dif), _dp(a1), _dp(a2),
+                                          float(tsi), _dp(_f64(solar)), _dp(up), _dp(dn)),
+               "calculate_sw_column")
+        return up, dn
+
+    def close(self):
+        if self._live:
+            _check(self.L.destroy_shortwave(C.byref(self.s)), "destroy_shortwave")
+            self._live = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def solar_flux(grid: SpectralGrid, path: str) -> np.ndarray:
+    L = load()
+    s = SolarFlux()
+    _check(L.create_solar_flux(C.byref(s), C.byref(grid), path.encode()), "create_solar_flux")
+    out = np.ctypeslib.as_array(s.incident_flux, shape=(int(s.n),)).copy()
+    _check(L.destroy_solar_flux(C.byref(s)), "destroy_solar_flux")
+    return out
+
+
+def integrate_fluxes(device: int, num_levels: int, grid: SpectralGrid, flux_dev_ptr: int):
+    out = np.empty(num_levels)
+    _check(load().integrate_fluxes(device, num_levels, C.byref(grid), C.c_void_p(flux_dev_ptr),
+                                   _dp(out)), "integrate_fluxes")
+    return out
+
+
+def heating_rates(p_mb, up, down) -> np.ndarray:
+    p = _f64(p_mb)
+    rate = np.empty(len(p) - 1)
+    _check(load().heating_rates(len(p), _dp(p), _dp(_f64(up)), _dp(_f64(down)), _dp(rate)),
+           "heating_rates")
+    return rate

@@ -1,0 +1,634 @@
+// Rayleigh optics, optics mixing, the longwave and shortwave column solvers and
+// spectral -> broadband integration on sm_100a.
+//
+// Replaces rayleigh_scattering (shortwave/src/rayleigh.c:29-144), add_optics
+// (utilities/src/optics.c:84-148), lw_fluxes_kernel/lw_flux/effective_planck/
+// planck_law (longwave/src/longwave.c:68-309), sw_fluxes_kernel/sw_flux/
+// sw_adding/eddington_mw1980/meador_weaver_1980/delta_eddington_scaling_jww1976
+// (shortwave/src/shortwave.c:68-503) and the trapezoid loop of output_fluxes
+// (framework/src/driver.c:302-319).
+//
+// One thread owns one wavenumber and walks the layers; every global access is
+// layer-major with the wavenumber contiguous, so a warp reads/writes 256
+// contiguous bytes per layer.  The "column" variants never materialise
+// Rayleigh/total optics or spectral fluxes: they mix on the fly and reduce the
+// fluxes to broadband values inside the kernel.
+#include <cmath>
+#include "common.cuh"
+
+namespace grt {
+
+constexpr int kSolverThreads = 128;
+
+struct LevelTemps
+{
+    double t_layers[GRT_MAX_LAYERS];
+    double t_levels[GRT_MAX_LAYERS + 1];
+};
+
+struct LayerDensity
+{
+    double n[GRT_MAX_LAYERS];   // integrated air number density (curtis_godson.c:25)
+};
+
+
+// ---- Rayleigh (rayleigh.c:29-41) -------------------------------------------------
+__device__ __forceinline__ double rayleigh_tau(double const w, double const n)
+{
+    double const W = w*1.e-4;
+    return (n*1.e-20*W*W*W*W)/(0.268675*1.e5*(9.38076E2 - 10.8426*W*W));
+}
+
+__global__ void rayleigh_kernel(int const num_layers, double const w0, double const dw,
+                                uint64_t const nw, LayerDensity const dens, double *omega,
+                                double *g, double *tau)
+{
+    uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+    if (i >= nw) return;
+    double const w = w0 + (double)i*dw;
+    for (int j=0; j<num_layers; ++j)
+    {
+        size_t const o = (size_t)j*nw + i;
+        omega[o] = 1.;
+        g[o] = 0.;
+        tau[o] = rayleigh_tau(w, dens.n[j]);
+    }
+}
+
+
+// ---- add_optics (optics.c:124-148) ------------------------------------------------
+struct OpticsList
+{
+    double const *g[8];
+    double const *omega[8];
+    double const *tau[8];
+};
+
+__global__ void add_optics_kernel(uint64_t const n, int const num_optics, OpticsList const in,
+                                  double *g_out, double *omega_out, double *tau_out)
+{
+    uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double g = 0., omega = 0., tau = 0.;
+    for (int j=0; j<num_optics; ++j)
+    {
+        double const gi = in.g[j][i];
+        double const oi = in.omega[j][i];
+        double const ti = in.tau[j][i];
+        g += gi*oi*ti;
+        omega += oi*ti;
+        tau += ti;
+    }
+    g_out[i] = g/omega;
+    omega_out[i] = omega/tau;
+    tau_out[i] = tau;
+}
+
+
+// ---- longwave ----------------------------------------------------------------------
+__device__ __forceinline__ double planck(double const T, double const w)
+{
+    double const c1 = 1.1910429526245744e-8;
+    double const c2 = 1.4387773538277202;
+    double e = c2*w/T;
+    if (e > 700.) e = 700.;
+    e = exp(e);
+    return (c1*w*w*w)/(e - 1.);
+}
+
+__device__ __forceinline__ double effective_planck(double const Tc, double const Te,
+                                                   double const w, double const tau)
+{
+    double const a = 0.193;
+    double const b = 0.013;
+    double const pc = planck(Tc, w);
+    double const pe = planck(Te, w);
+    return (pc + (a*tau + b*tau*tau)*pe)/(1. + a*tau + b*tau*tau);
+}
+
+// Accumulates one value per thread into out[level] (block reduction + one
+// atomic per block); used by the fused column kernels.
+__device__ __forceinline__ void block_accumulate(double v, double *dst, double *warp_sums)
+{
+    for (int o=16; o>0; o>>=1) v += __shfl_down_sync(0xffffffffu, v, o);
+    int const lane = threadIdx.x & 31;
+    int const warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) warp_sums[warp] = v;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double s = 0.;
+        for (int k=0; k<(int)(blockDim.x >> 5); ++k) s += warp_sums[k];
+        atomicAdd(dst, s);
+    }
+}
+
+// FUSED = false: tau/omega are the caller's total optics, spectral fluxes are
+// stored (drop-in calculate_lw_fluxes).  FUSED = true: tau is the gas optical
+// depth; Rayleigh is mixed in on the fly (as column_calculation does through
+// rayleigh_scattering + add_optics, driver.c:381-383) and the fluxes are reduced
+// to broadband values with trapezoid weights.
+template <bool FUSED>
+__global__ void __launch_bounds__(kSolverThreads)
+lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const nw,
+          double const t_surf, LevelTemps const temps, LayerDensity const dens,
+          double const *tau, double const *omega, double const *emis, double *flux_up,
+          double *flux_down)
+{
+    __shared__ double warp_sums[kSolverThreads/32];
+    uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+    bool const live = i < nw;
+    uint64_t const ii = live ? i : nw - 1;
+    int const L = num_levels - 1;
+    double const w = w0 + (double)ii*dw;
+    double const c1[4] = {-14.402613260847248, -3.0302159969901132, -1.4925584280108841,
+                          -1.0746123148178333};
+    double const c2[4] = {0.07587638482015649, 0.676114979733751, 1.3726594476601073,
+                          1.0169418413757783};
+    double weight = 0.;
+    if (FUSED)
+    {
+        weight = live ? ((ii == 0 || ii == nw - 1) ? 0.5*dw : dw) : 0.;
+        if (nw == 1) weight = 0.;
+    }
+
+    auto layer_tau = [&](int const j) -> double
+    {
+        size_t const o = (size_t)j*nw + ii;
+        if (FUSED)
+        {
+            double const tg = tau[o];
+            double const tr = rayleigh_tau(w, dens.n[j]);
+            double const tt = tg + tr;
+            double const om = tr/tt;
+            return tt*(1. - om);
+        }
+        return tau[o]*(1. - omega[o]);
+    };
+
+    double I[4] = {0., 0., 0., 0.};
+    if (FUSED)
+    {
+        // flux_down at the top of the atmosphere is zero: nothing to add.
+    }
+    else if (live)
+    {
+        flux_down[ii] = 0.;
+    }
+    for (int j=0; j<L; ++j)
+    {
+        double const t = layer_tau(j);
+        double const b = effective_planck(temps.t_layers[j], temps.t_levels[j+1], w, t);
+        double f = 0.;
+#pragma unroll
+        for (int s=0; s<4; ++s)
+        {
+            double const ext = exp(c1[s]*t);
+            double const pp = (1. - ext)*b;
+            I[s] = pp + I[s]*ext;
+            f += c2[s]*I[s];
+        }
+        if (FUSED)
+        {
+            block_accumulate(f*weight, &flux_down[j+1], warp_sums);
+        }
+        else if (live)
+        {
+            flux_down[(size_t)(j+1)*nw + ii] = f;
+        }
+    }
+    double const bs = planck(t_surf, w);
+    double const em = emis[ii];
+    double f = 0.;
+#pragma unroll
+    for (int s=0; s<4; ++s)
+    {
+        I[s] = em*bs + (1. - em)*I[s];
+        f += c2[s]*I[s];
+    }
+    if (FUSED)
+    {
+        block_accumulate(f*weight, &flux_up[L], warp_sums);
+    }
+    else if (live)
+    {
+        flux_up[(size_t)L*nw + ii] = f;
+    }
+    for (int j=L-1; j>=0; --j)
+    {
+        double const t = layer_tau(j);
+        double const b = effective_planck(temps.t_layers[j], temps.t_levels[j], w, t);
+        f = 0.;
+#pragma unroll
+        for (int s=0; s<4; ++s)
+        {
+            double const ext = exp(c1[s]*t);
+            double const pp = (1. - ext)*b;
+            I[s] = pp + I[s]*ext;
+            f += c2[s]*I[s];
+        }
+        if (FUSED)
+        {
+            block_accumulate(f*weight, &flux_up[j], warp_sums);
+        }
+        else if (live)
+        {
+            flux_up[(size_t)j*nw + ii] = f;
+        }
+    }
+}
+
+
+// ---- shortwave ---------------------------------------------------------------------
+// meador_weaver_1980 (shortwave.c:97-209) with the Eddington gammas of
+// eddington_mw1980 (shortwave.c:214-236).  t_pure == nullptr for the diffuse beam.
+__device__ void eddington(double const omega, double const tau, double const mu,
+                          double const g, double *R, double *T, double *T_pure)
+{
+    double const gamma1 = 0.25*(7. - omega*(4. + 3.*g));
+    double const gamma2 = -0.25*(1. - omega*(4. - 3.*g));
+    double const gamma3 = 0.25*(2. - 3.*g*mu);
+    if (omega <= 0.0)
+    {
+        *R = 0.;
+        *T = exp(-tau/mu);
+        if (T_pure != nullptr) *T_pure = *T;
+    }
+    else
+    {
+        double const gamma4 = 1. - gamma3;
+        double const alpha1 = gamma1*gamma4 + gamma2*gamma3;
+        double const alpha2 = gamma1*gamma3 + gamma2*gamma4;
+        double const k = sqrt(gamma1*gamma1 - gamma2*gamma2);
+        double t = tau;
+        if (1./mu > k && tau/mu > 700.)
+        {
+            t = 700.*mu;
+        }
+        else if (tau*k > 700.)
+        {
+            t = 700./k;
+        }
+        double const tp = exp(t/mu);
+        if (tp <= 1.0)
+        {
+            *R = 0.;
+            *T = 1.;
+            if (T_pure != nullptr) *T_pure = 1.;
+        }
+        else
+        {
+            double const tm = exp(-t/mu);
+            double const tkm = exp(-t*k);
+            double const tkp = exp(t*k);
+            if (T_pure != nullptr) *T_pure = tm;
+            if (omega >= 1.)
+            {
+                *R = (1./(1. + gamma1*t))*(gamma1*t + (gamma3 - gamma1*mu)*(1. - tm));
+                *T = 1. - *R;
+            }
+            else
+            {
+                *R = (omega/((1. - k*k*mu*mu)*((k + gamma1)*tkp + (k - gamma1)*tkm)))*
+                     ((1. - k*mu)*(alpha2 + k*gamma3)*tkp - (1. + k*mu)*(alpha2 - k*gamma3)*tkm -
+                      2.*k*(gamma3 - alpha2*mu)*tm);
+                *T = tm*(1. - (omega/((1. - k*k*mu*mu)*((k + gamma1)*tkp + (k - gamma1)*tkm)))*
+                     ((1. + k*mu)*(alpha1 + k*gamma4)*tkp - (1. - k*mu)*(alpha1 - k*gamma4)*tkm -
+                      2.*k*(gamma4 + alpha1*mu)*tp));
+            }
+        }
+    }
+    if (T_pure != nullptr)
+    {
+        if (*T_pure > *T) *T = *T_pure;
+    }
+}
+
+template <int MAXL, bool FUSED>
+__global__ void __launch_bounds__(kSolverThreads)
+sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const nw,
+          LayerDensity const dens, double const *omega_in, double const *g_in,
+          double const *tau_in, double const mu_dir, double const mu_dif,
+          double const *alb_dir, double const *alb_dif, double const tsi, double const *solar,
+          double *flux_up, double *flux_down)
+{
+    __shared__ double warp_sums[kSolverThreads/32];
+    uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+    bool const live = i < nw;
+    if (!FUSED && !live) return;
+    uint64_t const ii = live ? i : nw - 1;
+    int const L = num_levels - 1;
+    double const w = w0 + (double)ii*dw;
+
+    double R_dir[MAXL], R_dif[MAXL], T_dir[MAXL], T_dif[MAXL], T_pure[MAXL];
+    for (int j=0; j<L; ++j)
+    {
+        size_t const o = (size_t)j*nw + ii;
+        double omega, g, tau;
+        if (FUSED)
+        {
+            // add_optics of [gas, rayleigh] (optics.c:134-146): g = 0*tau_R/tau_R,
+            // omega = tau_R/(tau_gas + tau_R).
+            double const tg = tau_in[o];
+            double const tr = rayleigh_tau(w, dens.n[j]);
+            tau = tg + tr;
+            g = 0./tr;
+            omega = tr/tau;
+        }
+        else
+        {
+            omega = omega_in[o];
+            g = g_in[o];
+            tau = tau_in[o];
+        }
+        // delta-Eddington scaling (shortwave.c:86-89).
+        double const gs = g/(g + 1.);
+        double const f = g*g;
+        double const os = (1. - f)*omega/(1. - omega*f);
+        double const ts = tau*(1. - omega*f);
+        eddington(os, ts, mu_dir, gs, &R_dir[j], &T_dir[j], &T_pure[j]);
+        eddington(os, ts, mu_dif, gs, &R_dif[j], &T_dif[j], nullptr);
+    }
+
+    // Adding (shortwave.c:242-330).
+    double Rdd[MAXL + 1], Rfd[MAXL + 1], Rfu[MAXL];
+    Rdd[L] = alb_dir[ii];
+    Rfd[L] = alb_dif[ii];
+    for (int j=L-1; j>=0; --j)
+    {
+        double const A = T_pure[j];
+        double const B = 1./(1. - R_dif[j]*Rfd[j+1]);
+        Rdd[j] = R_dir[j] + (A*Rdd[j+1] + (T_dir[j] - A)*Rfd[j+1])*T_dif[j]*B;
+        Rfd[j] = R_dif[j] + T_dif[j]*T_dif[j]*Rfd[j+1]*B;
+    }
+    Rfu[0] = R_dif[0];
+    for (int j=1; j<L; ++j)
+    {
+        double const B = 1./(1. - R_dif[j]*Rfu[j-1]);
+        Rfu[j] = R_dif[j] + T_dif[j]*T_dif[j]*Rfu[j-1]*B;
+    }
+    double const scale = solar[ii]*mu_dir;
+    double weight = 0.;
+    if (FUSED)
+    {
+        weight = live ? ((ii == 0 || ii == nw - 1) ? 0.5*dw : dw) : 0.;
+        if (nw == 1) weight = 0.;
+    }
+    double dir_beam = 1.;
+    double dif_beam = 0.;
+    {
+        double const up = tsi*((dir_beam*Rdd[0])*scale);
+        double const down = tsi*(dir_beam*scale);
+        if (FUSED)
+        {
+            block_accumulate(up*weight, &flux_up[0], warp_sums);
+            block_accumulate(down*weight, &flux_down[0], warp_sums);
+        }
+        else
+        {
+            flux_up[ii] = up;
+            flux_down[ii] = down;
+        }
+    }
+    for (int j=1; j<num_levels; ++j)
+    {
+        if (j > 1)
+        {
+            double const C = 1./(1. - R_dif[j-1]*Rfu[j-2]);
+            dif_beam = (dir_beam*R_dir[j-1]*Rfu[j-2] + dif_beam)*T_dif[j-1]*C +
+                       dir_beam*(T_dir[j-1] - T_pure[j-1]);
+        }
+        else
+        {
+            dif_beam = dir_beam*(T_dir[j-1] - T_pure[j-1]);
+        }
+        dir_beam *= T_pure[j-1];
+        double const B = 1./(1. - Rfd[j]*Rfu[j-1]);
+        double const R = (dir_beam*Rdd[j] + dif_beam*Rfd[j])*B;
+        double const T = dir_beam*(1. + Rdd[j]*Rfu[j-1]*B) + dif_beam*B;
+        double const up = tsi*(R*scale);
+        double const down = tsi*(T*scale);
+        if (FUSED)
+        {
+            block_accumulate(up*weight, &flux_up[j], warp_sums);
+            block_accumulate(down*weight, &flux_down[j], warp_sums);
+        }
+        else
+        {
+            flux_up[(size_t)j*nw + ii] = up;
+            flux_down[(size_t)j*nw + ii] = down;
+        }
+    }
+}
+
+
+// ---- broadband integration (driver.c:302-319) ----------------------------------------
+__global__ void __launch_bounds__(256)
+integrate_kernel(uint64_t const nw, double const dw, double const *flux, double *out)
+{
+    __shared__ double warp_sums[8];
+    int const level = blockIdx.y;
+    double const *f = flux + (size_t)level*nw;
+    double acc = 0.;
+    for (uint64_t i=(uint64_t)blockIdx.x*blockDim.x + threadIdx.x; i + 1 < nw;
+         i += (uint64_t)gridDim.x*blockDim.x)
+    {
+        acc += 0.5*(f[i] + f[i+1])*dw;
+    }
+    block_accumulate(acc, &out[level], warp_sums);
+}
+
+
+// Per-device scratch for broadband results.
+static double *g_out_buf[64];
+
+static int out_buffer(int device, double **buf)
+{
+    if (g_out_buf[device] == nullptr)
+    {
+        GRT_CUDA(cudaMalloc(&g_out_buf[device], sizeof(double)*4*(GRT_MAX_LAYERS + 1)));
+    }
+    *buf = g_out_buf[device];
+    return 0;
+}
+
+static void number_densities(int num_layers, double const *p_atm, LayerDensity *d)
+{
+    for (int i=0; i<num_layers; ++i)
+    {
+        double dp = p_atm[i] - p_atm[i+1];
+        dp = dp >= 0. ? dp : -dp;
+        d->n[i] = 2.147822334314468e+25*dp;
+    }
+}
+
+}  // namespace grt
+
+using namespace grt;
+
+template <bool FUSED>
+static int launch_sw(cudaStream_t st, int num_levels, double w0, double dw, uint64_t nw,
+                     LayerDensity const &dens, double const *omega, double const *g,
+                     double const *tau, double mu_dir, double mu_dif, double const *alb_dir,
+                     double const *alb_dif, double tsi, double const *solar, double *up,
+                     double *down)
+{
+    unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
+    if (num_levels - 1 <= 64)
+    {
+        sw_kernel<64, FUSED><<<blocks, kSolverThreads, 0, st>>>(
+            num_levels, w0, dw, nw, dens, omega, g, tau, mu_dir, mu_dif, alb_dir, alb_dif, tsi,
+            solar, up, down);
+    }
+    else
+    {
+        sw_kernel<GRT_MAX_LAYERS, FUSED><<<blocks, kSolverThreads, 0, st>>>(
+            num_levels, w0, dw, nw, dens, omega, g, tau, mu_dir, mu_dif, alb_dir, alb_dif, tsi,
+            solar, up, down);
+    }
+    GRT_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" {
+
+int grt_rayleigh(int device, int num_layers, double w0, double dw, uint64_t nw,
+                 double const *p_atm, double *omega_dev, double *g_dev, double *tau_dev)
+{
+    if (num_layers < 1 || num_layers > GRT_MAX_LAYERS) return fail("bad layer count %d", num_layers);
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));
+    LayerDensity dens;
+    number_densities(num_layers, p_atm, &dens);
+    rayleigh_kernel<<<(unsigned)((nw + 255)/256), 256, 0, st>>>(num_layers, w0, dw, nw, dens,
+                                                                omega_dev, g_dev, tau_dev);
+    GRT_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int grt_add_optics(int device, uint64_t n, int num_optics, double const *const *g_dev,
+                   double const *const *omega_dev, double const *const *tau_dev,
+                   double *g_out_dev, double *omega_out_dev, double *tau_out_dev)
+{
+    if (num_optics < 1 || num_optics > 8) return fail("add_optics supports 1..8 objects");
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));
+    OpticsList list;
+    for (int j=0; j<num_optics; ++j)
+    {
+        list.g[j] = g_dev[j];
+        list.omega[j] = omega_dev[j];
+        list.tau[j] = tau_dev[j];
+    }
+    add_optics_kernel<<<(unsigned)((n + 255)/256), 256, 0, st>>>(n, num_optics, list, g_out_dev,
+                                                                 omega_out_dev, tau_out_dev);
+    GRT_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int grt_lw_fluxes(int device, int num_levels, double w0, double dw, uint64_t nw, double t_surf,
+                  double const *t_layers, double const *t_levels, double const *tau_dev,
+                  double const *omega_dev, double const *emis_dev, double *flux_up_dev,
+                  double *flux_down_dev)
+{
+    if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));
+    LevelTemps temps;
+    for (int i=0; i<num_levels-1; ++i) temps.t_layers[i] = t_layers[i];
+    for (int i=0; i<num_levels; ++i) temps.t_levels[i] = t_levels[i];
+    LayerDensity dens{};
+    unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
+    lw_kernel<false><<<blocks, kSolverThreads, 0, st>>>(num_levels, w0, dw, nw, t_surf, temps,
+                                                        dens, tau_dev, omega_dev, emis_dev,
+                                                        flux_up_dev, flux_down_dev);
+    GRT_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int grt_sw_fluxes(int device, int num_levels, uint64_t nw, double const *omega_dev,
+                  double const *g_dev, double const *tau_dev, double mu_dir, double mu_dif,
+                  double const *alb_dir_dev, double const *alb_dif_dev, double tsi,
+                  double const *solar_dev, double *flux_up_dev, double *flux_down_dev)
+{
+    if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));
+    LayerDensity dens{};
+    return launch_sw<false>(st, num_levels, 0., 0., nw, dens, omega_dev, g_dev, tau_dev, mu_dir,
+                            mu_dif, alb_dir_dev, alb_dif_dev, tsi, solar_dev, flux_up_dev,
+                            flux_down_dev);
+}
+
+int grt_integrate_flux(int device, int num_levels, uint64_t nw, double dw,
+                       double const *flux_dev, double *out)
+{
+    if (num_levels < 1 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));
+    double *buf;
+    GRT_TRY(out_buffer(device, &buf));
+    GRT_CUDA(cudaMemsetAsync(buf, 0, sizeof(double)*num_levels, st));
+    unsigned bx = (unsigned)((nw + 255)/256);
+    if (bx > 64) bx = 64;
+    if (bx < 1) bx = 1;
+    integrate_kernel<<<dim3(bx, (unsigned)num_levels), 256, 0, st>>>(nw, dw, flux_dev, buf);
+    GRT_CUDA(cudaGetLastError());
+    GRT_CUDA(cudaMemcpyAsync(out, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
+                  double const *p_atm, double t_surf, double const *t_layers,
+                  double const *t_levels, double const *tau_gas_dev, double const *emis_dev,
+                  double *up, double *down)
+{
+    if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));
+    LevelTemps temps;
+    for (int i=0; i<num_levels-1; ++i) temps.t_layers[i] = t_layers[i];
+    for (int i=0; i<num_levels; ++i) temps.t_levels[i] = t_levels[i];
+    LayerDensity dens;
+    number_densities(num_levels - 1, p_atm, &dens);
+    double *buf;
+    GRT_TRY(out_buffer(device, &buf));
+    GRT_CUDA(cudaMemsetAsync(buf, 0, sizeof(double)*2*num_levels, st));
+    unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
+    lw_kernel<true><<<blocks, kSolverThreads, 0, st>>>(num_levels, w0, dw, nw, t_surf, temps, dens,
+                                                       tau_gas_dev, nullptr, emis_dev, buf,
+                                                       buf + num_levels);
+    GRT_CUDA(cudaGetLastError());
+    GRT_CUDA(cudaMemcpyAsync(up, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaMemcpyAsync(down, buf + num_levels, sizeof(double)*num_levels,
+                             cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
+                  double const *p_atm, double const *tau_gas_dev, double mu_dir, double mu_dif,
+                  double const *alb_dir_dev, double const *alb_dif_dev, double tsi,
+                  double const *solar_dev, double *up, double *down)
+{
+    if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));
+    LayerDensity dens;
+    number_densities(num_levels - 1, p_atm, &dens);
+    double *buf;
+    GRT_TRY(out_buffer(device, &buf));
+    GRT_CUDA(cudaMemsetAsync(buf, 0, sizeof(double)*2*num_levels, st));
+    GRT_TRY(launch_sw<true>(st, num_levels, w0, dw, nw, dens, nullptr, nullptr, tau_gas_dev,
+                            mu_dir, mu_dif, alb_dir_dev, alb_dif_dev, tsi, solar_dev, buf,
+                            buf + num_levels));
+    GRT_CUDA(cudaMemcpyAsync(up, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaMemcpyAsync(down, buf + num_levels, sizeof(double)*num_levels,
+                             cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+}  // extern "C"

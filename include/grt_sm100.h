@@ -1,0 +1,142 @@
+/* grt_sm100.h -- thin C ABI of the sm_100a CUDA layer (libgrt_sm100.so).
+ *
+ * Everything the C99 host library (include/gas_optics.h, longwave.h, shortwave.h,
+ * rayleigh.h, optics.h) needs from the GPU goes through these entry points:
+ * plain pointers and sizes only, no CUDA or C++ types.  Each group cites the
+ * reference interface it replaces (paths under the NOAA-GFDL/GRTCODE tree).
+ *
+ * Conventions: every function returns 0 on success or GRT_SM100_ERR (= 12,
+ * GRTCODE_GPU_ERR of utilities/src/return_codes.h:39); grt_last_error() gives
+ * the message.  Pointers named *_dev are device pointers obtained from
+ * grt_malloc(); all others are host pointers.  All work of one device is
+ * ordered on one library-owned CUDA stream; calls that return data to the host
+ * synchronise that stream before returning.
+ */
+#ifndef GRT_SM100_H_
+#define GRT_SM100_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GRT_SM100_ERR 12
+#define GRT_MAX_LAYERS 200   /* utilities/src/grtcode_config.h:52 */
+#define GRT_MAX_MOLS 53      /* gas-optics/src/molecules.h:86 */
+#define GRT_MAX_CFCS 21      /* gas-optics/src/cfcs.h:55 */
+#define GRT_MAX_CIAS 3       /* gas-optics/src/collision_induced_absorption.h:34 */
+#define GRT_NUM_CIA_SPECIES 2
+
+/* ---- device + memory: replaces the gmalloc/gfree/gmemset/gmemcpy macros of
+ * utilities/src/debug.h:311-348 and get_num_gpus of utilities/src/device.c:26. */
+int grt_device_count(int *count);
+int grt_device_name(int device, char *buf, int len);
+int grt_malloc(int device, void **ptr_dev, size_t bytes);
+int grt_free(int device, void *ptr_dev);
+int grt_memset(int device, void *ptr_dev, int value, size_t bytes);
+int grt_copy_to_device(int device, void *dst_dev, void const *src, size_t bytes);
+int grt_copy_to_host(int device, void *dst, void const *src_dev, size_t bytes);
+int grt_copy_on_device(int device, void *dst_dev, void const *src_dev, size_t bytes);
+int grt_synchronize(int device);
+/* The library's cudaStream_t for `device`, as an opaque pointer, so that a
+ * caller can record CUDA events on the stream the kernels run on. */
+int grt_stream_handle(int device, void **stream);
+/* Pinned host buffers for the batched drivers (no reference counterpart). */
+int grt_host_alloc(void **ptr, size_t bytes);
+int grt_host_free(void *ptr);
+/* Copy of the last error message of the calling thread. */
+int grt_last_error(char *buf, int len);
+
+/* ---- gas optics: replaces launch() of gas-optics/src/launch.c:40-226 and the
+ * device halves of create_gas_optics / add_molecule / add_cfc / add_cia
+ * (gas-optics/src/gas_optics.c:51-176, 219-279, 307-399). */
+typedef struct grt_gas grt_gas;
+
+int grt_gas_create(grt_gas **gas, int device, int num_levels, double w0, double dw,
+                   uint64_t num_wpoints);
+int grt_gas_destroy(grt_gas *gas);
+
+/* Upload one molecule's HITRAN lines (host SoA as filled by parse_hitran_file,
+ * gas-optics/src/parse_HITRAN_file.c:224-413; snn already scaled to 296 K) and
+ * its partition-sum table q_table[num_iso][nt] on temperatures tmin + k [K]
+ * (replaces inittips_d, gas-optics/src/tips2017.h:29). */
+int grt_gas_add_molecule(grt_gas *gas, int mol_id, double mass_g, int num_iso,
+                         uint64_t num_lines, int const *iso, double const *vnn,
+                         double const *snn, double const *yair, double const *yself,
+                         double const *en, double const *n_air, double const *delta,
+                         double const *q_table, int tmin, int nt);
+/* Continuum / cross-section tables already resampled to the spectral grid
+ * (water_vapor_continuum.c:32-122, ozone_continuum.c:31, cfcs.c:30,
+ * collision_induced_absorption.c:29); each array has num_wpoints entries. */
+int grt_gas_set_h2o_continuum(grt_gas *gas, double const *s296, double const *ckds,
+                              double const *f296, double const *ckdf);
+int grt_gas_set_o3_continuum(grt_gas *gas, double const *cross_section);
+int grt_gas_add_cfc(grt_gas *gas, int cfc_id, double const *cross_section);
+int grt_gas_add_cia(grt_gas *gas, int species0, int species1, double const *cross_section);
+
+/* One column: level pressure [atm] and temperature [K], mole fractions
+ * x_mol[GRT_MAX_MOLS][num_levels] (row = HITRAN id - 1), x_cfc[GRT_MAX_CFCS][num_levels]
+ * (row = cfc id), x_cia[GRT_NUM_CIA_SPECIES][num_levels]; writes (overwrites)
+ * tau_dev[num_layers][num_wpoints].  method follows enum OpticalDepthMethod
+ * (gas-optics/src/gas_optics.h:88-93); only line_sample (2) is implemented. */
+int grt_gas_optical_depth(grt_gas *gas, double const *p_atm, double const *t,
+                          double const *x_mol, double const *x_cfc, double const *x_cia,
+                          int method, double *tau_dev);
+
+/* Counters of the last grt_gas_optical_depth call (bench/roofline bookkeeping):
+ * out[0] = (line,layer) records inside the grid, out[1] = Voigt samples the
+ * reference would evaluate for them, out[2] = kernels launched,
+ * out[3] = records taking the pure-Lorentz branch. */
+int grt_gas_last_stats(grt_gas const *gas, uint64_t out[4]);
+
+/* ---- Rayleigh + optics mixing: replaces rayleigh_scattering
+ * (shortwave/src/rayleigh.c:100-144) and add_optics (utilities/src/optics.c:84-148). */
+int grt_rayleigh(int device, int num_layers, double w0, double dw, uint64_t num_wpoints,
+                 double const *p_atm, double *omega_dev, double *g_dev, double *tau_dev);
+int grt_add_optics(int device, uint64_t num_values, int num_optics,
+                   double const *const *g_dev, double const *const *omega_dev,
+                   double const *const *tau_dev, double *g_out_dev, double *omega_out_dev,
+                   double *tau_out_dev);
+
+/* ---- solvers: replace calculate_lw_fluxes (longwave/src/longwave.c:312-353) and
+ * calculate_sw_fluxes (shortwave/src/shortwave.c:506-547).  Spectral fluxes are
+ * written to device buffers [num_levels][num_wpoints]; the host library copies
+ * them out. */
+int grt_lw_fluxes(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
+                  double t_surf, double const *t_layers, double const *t_levels,
+                  double const *tau_dev, double const *omega_dev, double const *emis_dev,
+                  double *flux_up_dev, double *flux_down_dev);
+int grt_sw_fluxes(int device, int num_levels, uint64_t num_wpoints, double const *omega_dev,
+                  double const *g_dev, double const *tau_dev, double mu_dir, double mu_dif,
+                  double const *alb_dir_dev, double const *alb_dif_dev, double tsi,
+                  double const *solar_dev, double *flux_up_dev, double *flux_down_dev);
+
+/* ---- broadband integration: replaces the serial trapezoid loop of
+ * output_fluxes (framework/src/driver.c:302-319), for every level at once:
+ * out[level] = sum_{i<n-1} 0.5*(f[level][i] + f[level][i+1])*dw. */
+int grt_integrate_flux(int device, int num_levels, uint64_t num_wpoints, double dw,
+                       double const *flux_dev, double *out);
+
+/* ---- fused column solvers for the drivers (no spectral arrays leave the GPU):
+ * Rayleigh + optics mixing + solver + broadband integration in one kernel each;
+ * replaces the chain column_calculation -> add_optics -> calculate_*_fluxes ->
+ * output_fluxes (framework/src/driver.c:360-424).  up/down have num_levels entries. */
+int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
+                  double const *p_atm, double t_surf, double const *t_layers,
+                  double const *t_levels, double const *tau_gas_dev, double const *emis_dev,
+                  double *up, double *down);
+int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
+                  double const *p_atm, double const *tau_gas_dev, double mu_dir,
+                  double mu_dif, double const *alb_dir_dev, double const *alb_dif_dev,
+                  double tsi, double const *solar_dev, double *up, double *down);
+
+/* ---- measurement helper: sustained FP64 / FP32 FMA throughput of this GPU
+ * [TFLOP/s, FMA = 2 flop], the roofline denominator of the Voigt sweep. */
+int grt_measure_fma_peak(int device, double *fp64_tflops, double *fp32_tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

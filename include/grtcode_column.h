@@ -1,0 +1,32 @@
+/* ADDITIONS to the reference API (no counterpart there): fused per-column calls
+ * that keep every spectral array on the GPU and return broadband fluxes, i.e.
+ * what framework/src/driver.c:360-424 (column_calculation with -integrated)
+ * computes through rayleigh_scattering + add_optics + calculate_*_fluxes +
+ * output_fluxes.  `gas` is the Optics_t filled by calculate_optical_depth.
+ * Outputs: up/down broadband flux [W m-2] on every level (num_levels values). */
+#ifndef GRTCODE_COLUMN_H_
+#define GRTCODE_COLUMN_H_
+#include "gas_optics.h"
+#include "longwave.h"
+#include "shortwave.h"
+
+EXTERN int calculate_lw_column(Longwave_t * const lw, Optics_t const * const gas,
+                               fp_t * const pressure, fp_t const T_surf, fp_t * const T_layers,
+                               fp_t * const T_levels, fp_t * const emis, fp_t * const up,
+                               fp_t * const down);
+EXTERN int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const gas,
+                               fp_t * const pressure, fp_t const mu_dir, fp_t const mu_dif,
+                               fp_t * const sfc_alpha_dir, fp_t * const sfc_alpha_dif,
+                               fp_t const total_solar_irradiance, fp_t * const solar_flux,
+                               fp_t * const up, fp_t * const down);
+/* Trapezoid integral over wavenumber of a device flux array (level, wavenumber). */
+EXTERN int integrate_fluxes(Device_t const device, int const num_levels,
+                            SpectralGrid_t const * const grid, fp_t const * const flux_dev,
+                            fp_t * const out);
+/* Heating rate [K day-1] of each layer from broadband net fluxes
+ * (g/cp * d(F_net)/dp * 86400); pressure [mb] on levels. */
+EXTERN int heating_rates(int const num_levels, fp_t const * const pressure,
+                         fp_t const * const up, fp_t const * const down, fp_t * const rate);
+/* Counters of the last calculate_optical_depth call: see grt_gas_last_stats. */
+EXTERN int gas_optics_stats(GasOptics_t const * const gas_optics, uint64_t out[4]);
+#endif
