@@ -85,8 +85,10 @@ def load():
         raise FileNotFoundError(
             f"{LIB_CUDA} / {LIB_HOST} not built: run `python -c 'import __graft_entry__ as g; "
             "g.build()'` (there is no CPU fallback)")
-    _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
-    L = C.CDLL(LIB_HOST, mode=C.RTLD_GLOBAL)
+    # RTLD_LOCAL: the oracle libraries export the same public names (they are the
+    # reference); neither side may bind to the other's symbols.
+    _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_LOCAL)
+    L = C.CDLL(LIB_HOST, mode=C.RTLD_LOCAL)
     L.create_spectral_grid.argtypes = [C.POINTER(SpectralGrid), C.c_double, C.c_double, C.c_double]
     L.create_device.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.get_num_gpus.argtypes = [C.POINTER(C.c_int), C.c_int]
