@@ -1,0 +1,437 @@
+"""Benchmark of the line-by-line hot path on B200 (contract: see DESIGN.md section 6).
+
+    python bench.py --gpus N --steps K --warmup W            # this repository
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path
+
+One step = one clear-sky column of BASELINE config 2 (CIRC case 1, 54 layers,
+LW 1-3250 + SW 1-50000 cm-1 at 0.01 cm-1, 7 HITRAN molecules + continua + CIA +
+3 CFCs): optical depths on both grids, Rayleigh mixing, the LW and SW solvers and
+broadband integration.  metric = spectral points x layers / s of line-by-line tau.
+N > 1 (torchrun): every rank runs its own columns on its own GPU, no data-path
+collective (columns are independent: "weak" scaling); NCCL is used only for the
+barrier and the max-over-ranks of the device time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "spectral pts x layers / s (line-by-line tau, LW+SW column incl. solvers)"
+UNIT = "pts*layers/s"
+FLOP_PER_SAMPLE = 9.0        # 6 FP64 + 3 FP32 per far-wing Voigt sample
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scale", type=float, default=float(os.environ.get("GRT_BENCH_SCALE", "1")),
+                    help="shrink the line counts (development only; 1 = the BASELINE workload)")
+    ap.add_argument("--dw", type=float, default=float(os.environ.get("GRT_BENCH_DW", "0.01")))
+    ap.add_argument("--data", default=os.environ.get("GRT_BENCH_DATA", "/tmp/grt_bench"))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                smax.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                  "sw_power_cap"), f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(smax) if smax else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+class Engine:
+    """One rank's state: gas optics + solvers for both bands on one GPU, through the
+    reference-facing C API (grtcode_b200.api -> libgrtcode.so -> libgrt_sm100.so)."""
+
+    def __init__(self, api, bands, column, device: int):
+        from grtcode_b200 import workloads as W
+        self.api = api
+        self.device = device
+        self.levels = len(column.p)
+        self.parts = []
+        for band in bands:
+            ds = band.dataset
+            grid = api.spectral_grid(band.w0, band.wn, band.dw)
+            go = api.GasOptics(self.levels, grid, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm,
+                               device=device)
+            for m in W.MOLECULES:
+                go.add_molecule(m)
+            for c, path in ds.cfc.items():
+                go.add_cfc(c, path)
+            for (a, b), path in ds.cia.items():
+                go.add_cia(a, b, path)
+            gas = api.OpticsObject(self.levels - 1, grid, device)
+            n = int(grid.n)
+            part = dict(band=band, grid=grid, go=go, gas=gas, n=n)
+            if band.name.startswith("lw"):
+                part["solver"] = api.LongwaveSolver(self.levels, grid, device)
+                part["emis"] = pinned(api, n, column.emissivity)
+            else:
+                part["solver"] = api.ShortwaveSolver(self.levels, grid, device)
+                part["alb"] = pinned(api, n, column.albedo)
+                sol = api.solar_flux(grid, ds.solar)
+                part["solar"] = pinned(api, n, 0.)
+                part["solar"][:] = sol
+            self.parts.append(part)
+        self.launches = 0
+        self.last = {}
+
+    def step(self, col, upload_surface: bool):
+        """One column.  upload_surface=True is the end-to-end form: every host array the
+        API takes is passed (and copied to the GPU) again."""
+        out = {}
+        launches = 0
+        h2d = 0
+        for part in self.parts:
+            go = part["go"]
+            for m, v in col.ppmv.items():
+                go.set_ppmv("mol", m, v)
+            for c, v in col.cfc_ppmv.items():
+                if c in part["band"].dataset.cfc:
+                    go.set_ppmv("cfc", c, v)
+            for c, v in col.cia_ppmv.items():
+                go.set_ppmv("cia", c, v)
+            go.optical_depth(col.p, col.t, part["gas"])
+            st = go.stats()
+            launches += st["launches"]
+            h2d += 8*self.levels*(2 + 53 + 21 + 2)
+            name = part["band"].name[:2]
+            if name == "lw":
+                emis = part["emis"] if upload_surface else None
+                up, dn = part["solver"].column(part["gas"], col.p, col.t_surf, col.t_layer,
+                                               col.t, emis)
+                h2d += 8*part["n"] if upload_surface else 0
+            else:
+                alb = part["alb"] if upload_surface else None
+                up, dn = part["solver"].column(part["gas"], col.p, col.mu0, 0.5, alb, alb,
+                                               col.tsi, part["solar"] if upload_surface else None)
+                h2d += 2*8*part["n"] if upload_surface else 0
+            launches += 1
+            out[name] = (up, dn, st)
+        self.launches = launches
+        self.h2d = h2d
+        self.d2h = 2*2*8*self.levels + 2*32
+        self.last = out
+        return out
+
+
+def pinned(api, n: int, fill: float) -> np.ndarray:
+    """float64[n] in page-locked host memory (cudaMallocHost through the C ABI)."""
+    import ctypes as C
+    ptr = C.c_void_p()
+    if api.cuda_layer().grt_host_alloc(C.byref(ptr), 8*n) != 0:
+        raise RuntimeError("grt_host_alloc failed")
+    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,))
+    arr[:] = fill
+    return arr
+
+
+def cpu_reference_sample(args, col, threads=None, reps: int = 1):
+    """The reference's own CPU implementation (oracle/_ref, gcc -O3 -fopenmp; the C
+    restatement when that is absent) on a bounded sample of the workload: a 20 cm-1
+    window of each band with the band's mean number of Voigt samples per grid point.
+    Returns (pts*layers/s extrapolated to the full column, description dict)."""
+    from grtcode_b200 import workloads as W
+    from oracle import ref as R
+    from tests import parity
+    lw, sw = W.circ1_bands(args.dw, args.scale)
+    kind = "reference" if R.available() else "port"
+    samples = [W.cpu_sample_band(lw, 20., 700.), W.cpu_sample_band(sw, 20., 10000.)]
+    full_n = {"lw": lw.n, "sw": sw.n}
+    layers = len(col.p) - 1
+    est_full = 0.
+    detail = []
+    cores = None
+    for sb in samples:
+        W.materialise(sb, os.path.join(args.data, "cpu"), seed=11)
+        best = None
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            if kind == "reference":
+                res = parity.oracle_column(sb.dataset, sb.w0, sb.wn, sb.dw, col, W.MOLECULES,
+                                           threads=threads, solvers=False)
+                r = R.Ref(threads=threads)
+                cores = r.max_threads()
+                # solver for the band, as the driver would (rayleigh + add_optics + fluxes)
+                g = r.grid(sb.w0, sb.wn, sb.dw)
+                gas = R.RefOptics(r, layers, g)
+                gas.tau[:] = res["tau"]
+                ray = R.RefOptics(r, layers, g)
+                R.rayleigh(r, ray, col.p)
+                tot = R.add_optics(r, [gas, ray])
+                n = int(g.n)
+                if sb.name.startswith("lw"):
+                    up, dn = R.lw_fluxes(r, tot, col.t_surf, col.t_layer, col.t,
+                                         np.full(n, col.emissivity))
+                else:
+                    sol = R.solar_flux(r, g, sb.dataset.solar)
+                    alb = np.full(n, col.albedo)
+                    up, dn = R.sw_fluxes(r, tot, col.mu0, 0.5, alb, alb, col.tsi, sol)
+                R.broadband(up, sb.dw)
+                R.broadband(dn, sb.dw)
+                for o in (tot, ray, gas):
+                    o.close()
+            else:
+                from oracle import port as P
+                go = P.GasOptics(len(col.p), sb.w0, sb.wn, sb.dw, sb.dataset.hitran,
+                                 sb.dataset.h2o_ctm_dir, sb.dataset.o3_ctm)
+                for m in W.MOLECULES:
+                    go.add_molecule(m)
+                    go.set_ppmv("mol", m, col.ppmv[m])
+                go.optical_depth(col.p, col.t)
+                cores = os.cpu_count()
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        # setup (file parsing) is part of the reference call chain measured here, but it is
+        # a small share: ~2e4 lines per sample file.
+        key = sb.name[:2]
+        est_full += best*full_n[key]/sb.n
+        detail.append(f"{sb.name}: {sb.w0:g}-{sb.wn:g} cm-1 @ {sb.dw:g} ({sb.n} pts, "
+                      f"{sb.num_lines} lines) {best:.2f} s")
+    value = (lw.n + sw.n)*layers/est_full
+    sample = ("one CIRC-1 column on two 20 cm-1 windows with the full bands' mean Voigt samples "
+              "per grid point, scaled by grid points to the full LW+SW column; " + "; ".join(detail))
+    return value, {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from grtcode_b200 import workloads as W
+    col = W.circ1_column()
+    lw, sw = W.circ1_bands(args.dw, args.scale)
+    times = []
+    value = None
+    info = None
+    for it in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        value, info = cpu_reference_sample(args, W.perturbed(col, 0, it))
+        if it >= args.warmup:
+            times.append(time.perf_counter() - t0)
+        if it == 0 and args.warmup > 1:
+            # the sample is ~10 s of CPU work: one warm-up is enough to page everything in
+            pass
+    layers = len(col.p) - 1
+    # mean over the timed steps of the extrapolated full-column rate
+    ms = 1e3*float(np.mean(times)) if times else None
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic HITRAN-format line lists + CIRC-1 profile",
+            "config": workload_config(args, lw, sw, layers),
+            "cpu_baseline": info,
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def workload_config(args, lw, sw, layers):
+    return {"workload": "BASELINE config 2: CIRC case 1 clear-sky LW+SW, 7 HITRAN molecules + "
+                        "H2O/O3 continua + 3 CIA pairs + 3 CFCs, one column per step per GPU",
+            "layers": layers, "dw_cm-1": args.dw, "lw_points": lw.n, "sw_points": sw.n,
+            "lw_lines": lw.num_lines, "sw_lines": sw.num_lines, "line_scale": args.scale,
+            "method": "line_sample", "columns_per_step_per_gpu": 1,
+            "l2": "inputs larger than L2 (line records + tau > 2 GB per band)"}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from grtcode_b200 import api
+    from grtcode_b200 import workloads as W
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not api.libraries_present():
+        raise RuntimeError("libgrt_sm100.so / libgrtcode.so are not built; there is no fallback")
+    api.load()
+    if api.num_gpus() < 1:
+        raise RuntimeError("no CUDA device visible: this library has no CPU path")
+    device = local
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", device))
+
+    col0 = W.circ1_column()
+    lw, sw = W.circ1_bands(args.dw, args.scale)
+    # Synthetic line lists and tables: rank 0 of the node writes them, everyone reads.
+    if local == 0:
+        W.materialise(lw, args.data, seed=1)
+        W.materialise(sw, args.data, seed=2)
+    if world > 1:
+        dist.barrier()
+    if local != 0:
+        W.materialise(lw, args.data, seed=1)
+        W.materialise(sw, args.data, seed=2)
+    t_setup = time.perf_counter()
+    eng = Engine(api, (lw, sw), col0, device)
+    t_setup = time.perf_counter() - t_setup
+    layers = eng.levels - 1
+    pts_layers = (lw.n + sw.n)*layers
+
+    stream = torch.cuda.ExternalStream(api.stream_handle(device), device=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    def timed(upload: bool, first_step: int):
+        """K steps bracketed by barrier + synchronize; device time from CUDA events on the
+        library's stream; returns (max-over-ranks seconds, per-kernel stats of the run)."""
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        wing_ns = 0
+        wing_flop = 0.
+        kern = {"prep_ns": 0, "wing_ns": 0, "core_ns": 0}
+        barrier()
+        e0.record(stream)
+        for k in range(args.steps):
+            out = eng.step(W.perturbed(col0, rank, first_step + k), upload)
+            for name in ("lw", "sw"):
+                st = out[name][2]
+                wing_ns += st["wing_ns"]
+                wing_flop += FLOP_PER_SAMPLE*(st["samples"] - st["core_samples"])
+                for key in kern:
+                    kern[key] += st[key]
+        e1.record(stream)
+        barrier()
+        secs = e0.elapsed_time(e1)*1e-3
+        if world > 1:
+            t = torch.tensor([secs], device=f"cuda:{device}", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            secs = float(t.item())
+        return secs, wing_ns, wing_flop, kern, out
+
+    # warm-up (the first step also uploads the surface arrays the device-resident run reuses)
+    for k in range(max(args.warmup, 1)):
+        eng.step(W.perturbed(col0, rank, k), upload_surface=True)
+    barrier()
+
+    clocks = ClockSampler(device)
+    clocks.start()
+    secs, wing_ns, wing_flop, kern, out = timed(False, 100)
+    clk = clocks.stop()
+    launches = eng.launches*args.steps
+    secs_e2e, _, _, _, out_e2e = timed(True, 200)
+    h2d, d2h = eng.h2d, eng.d2h
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    value = world*pts_layers*args.steps/secs
+    e2e = world*pts_layers*args.steps/secs_e2e
+    fp64_peak, fp32_peak = api.measure_fma_peak(device)
+    launches_wing = 2*args.steps
+    achieved = wing_flop/(wing_ns*1e-9)/1e12 if wing_ns else None
+    samples_step = sum(out[n][2]["samples"] for n in ("lw", "sw"))
+    roofline = {
+        "bound": "fp64",
+        "kernel": "wing_sweep_kernel",
+        "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
+        "frac": achieved/fp64_peak if achieved else None,
+        "traffic": None,
+        "peak_source": "measured here: dependent-free DFMA chains, all SMs (grt_measure_fma_peak); "
+                       "MEASURED_PEAKS.json has no FP64 figure",
+        "flop_per_sample": FLOP_PER_SAMPLE,
+        "avg_launch_ms": wing_ns*1e-6/launches_wing if wing_ns else None,
+        "samples_per_s": (wing_flop/FLOP_PER_SAMPLE)/(wing_ns*1e-9) if wing_ns else None,
+        "fp32_peak": fp32_peak,
+        "kernel_share_of_step": {k: v*1e-9/secs for k, v in kern.items()},
+    }
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3*secs/args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic HITRAN-format line lists + CIRC-1 profile",
+            "config": workload_config(args, lw, sw, layers),
+            "clocks": clk,
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": 1e3*secs_e2e/args.steps},
+            "gpu_launches": launches,
+            "roofline": roofline,
+            "voigt_samples_per_step": samples_step,
+            "setup_s": t_setup,
+            "fluxes_W_m2": {"lw_up_toa": float(out["lw"][0][0]), "lw_dn_sfc": float(out["lw"][1][-1]),
+                            "sw_up_toa": float(out["sw"][0][0]), "sw_dn_sfc": float(out["sw"][1][-1])}}
+    if world == 1 and not args.no_cpu_baseline:
+        _, info = cpu_reference_sample(args, col0)
+        line["cpu_baseline"] = info
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

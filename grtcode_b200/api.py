@@ -139,6 +139,8 @@ def load():
     L.grt_tips_q.argtypes = [C.c_int, C.c_double, C.c_int]
     _cuda.grt_measure_fma_peak.argtypes = [C.c_int, _dbl_p, _dbl_p]
     _cuda.grt_synchronize.argtypes = [C.c_int]
+    _cuda.grt_selftest_arithmetic.argtypes = [C.c_int, C.c_ulonglong, C.c_ulonglong,
+                                              C.POINTER(C.c_ulonglong)]
     _cuda.grt_stream_handle.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     _cuda.grt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
     _cuda.grt_host_free.argtypes = [C.c_void_p]
@@ -190,6 +192,13 @@ def stream_handle(device: int) -> int:
     if cuda_layer().grt_stream_handle(device, C.byref(h)) != 0:
         raise RuntimeError("grt_stream_handle failed")
     return h.value or 0
+
+
+def selftest_arithmetic(n: int, seed: int = 1, device: int = 0) -> int:
+    bad = C.c_ulonglong(0)
+    if cuda_layer().grt_selftest_arithmetic(device, n, seed, C.byref(bad)) != 0:
+        raise RuntimeError("grt_selftest_arithmetic failed")
+    return int(bad.value)
 
 
 def measure_fma_peak(device: int = 0) -> tuple[float, float]:
@@ -306,9 +315,10 @@ class GasOptics:
         return n.value
 
     def stats(self) -> dict:
-        out = (C.c_uint64*4)()
+        out = (C.c_uint64*8)()
         _check(self.L.gas_optics_stats(C.byref(self.s), out), "gas_optics_stats")
-        return {"records": out[0], "samples": out[1], "launches": out[2], "lorentz": out[3]}
+        return {"records": out[0], "samples": out[1], "launches": out[2], "lorentz": out[3],
+                "prep_ns": out[4], "wing_ns": out[5], "core_ns": out[6], "core_samples": out[7]}
 
     def close(self):
         if self._live:
@@ -348,7 +358,8 @@ class LongwaveSolver:
         dn = np.empty(self.num_levels)
         _check(self.L.calculate_lw_column(C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)),
                                           float(t_surf), _dp(_f64(t_layers)), _dp(_f64(t_levels)),
-                                          _dp(_f64(emis)), _dp(up), _dp(dn)),
+                                          _dp(_f64(emis)) if emis is not None else None,
+                                          _dp(up), _dp(dn)),
                "calculate_lw_column")
         return up, dn
 
@@ -388,11 +399,15 @@ class ShortwaveSolver:
     def column(self, gas: OpticsObject, p_mb, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar):
         up = np.empty(self.num_levels)
         dn = np.empty(self.num_levels)
-        a1 = _f64(alb_dir)
-        a2 = a1 if alb_dif is alb_dir else _f64(alb_dif)
+        if alb_dir is None:
+            p1 = p2 = p3 = None
+        else:
+            a1 = _f64(alb_dir)
+            a2 = a1 if alb_dif is alb_dir else _f64(alb_dif)
+            p1, p2, p3 = _dp(a1), _dp(a2), _dp(_f64(solar))
         _check(self.L.calculate_sw_column(C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)),
-                                          float(mu_dir), float(mu_dif), _dp(a1), _dp(a2),
-                                          float(tsi), _dp(_f64(solar)), _dp(up), _dp(dn)),
+                                          float(mu_dir), float(mu_dif), p1, p2,
+                                          float(tsi), p3, _dp(up), _dp(dn)),
                "calculate_sw_column")
         return up, dn
 

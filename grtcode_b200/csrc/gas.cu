@@ -17,6 +17,7 @@
 // All molecules share one merged, centre-sorted line list.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <numeric>
 #include <vector>
 #include "common.cuh"
@@ -25,8 +26,6 @@
 namespace grt {
 
 constexpr int kMaxIso = 18;           // largest isotopologue count (molecules.c:48)
-constexpr int kSweepThreads = 256;
-constexpr int kStageRecs = 128;       // records staged per shared-memory chunk (4 KiB)
 
 struct Slot
 {
@@ -163,6 +162,12 @@ __global__ void column_prep_kernel(int const num_layers, ColumnInputs const in,
 }
 
 
+}  // namespace grt
+
+#include "sweep.cuh"
+
+namespace grt {
+
 struct PrepStats
 {
     unsigned long long records;   // (line, layer) pairs inside the grid
@@ -218,18 +223,30 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         r.repwid = repwid;
         r.y = y;
         double const sn = S*Ns;
+        float const yq = y*y;
+        r.a0 = (float)((double)yq + 0.5);                 // RFM_voigt.c:177-179
+        r.d0 = r.a0*r.a0;
+        r.d2 = (float)((double)(yq + yq) - 1.0);
         if (y >= kLorentzY)
         {
             r.xlim0 = 0.f;
+            r.xlim1 = 0.f;
             r.c = sn*(double)(repwid*y)/3.14159265358979323846;
         }
         else
         {
-            r.xlim0 = (float)sqrt((double)(15100.0f + y*(40.0f - y*3.6f)));
+            voigt_limits(y, &r.xlim0, &r.xlim1);
             r.c = sn*(double)(kRsqrpi*repwid);
+            if (!(y >= 1e-18f))
+            {
+                // Vanishing (or NaN) Y: far-wing values may be zero or subnormal; let
+                // the line-core kernel evaluate the whole window with the full routine.
+                r.xlim0 = __int_as_float(0x7f800000);
+                r.xlim1 = __int_as_float(0x7f800000);
+            }
         }
         double const fcd = floor((2.*((v - w0)/wres) + 1.)/2.);
-        if (fcd >= 0. && fcd < (double)nw && gamma == gamma && alpha == alpha)
+        if (fcd >= 0. && fcd < (double)nw)
         {
             int const fc = (int)fcd;
             r.fc = fc;
@@ -243,7 +260,7 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
             }
             else
             {
-                double const h = (double)r.xlim0/((double)repwid*wres);
+                double const h = (double)r.xlim1/((double)repwid*wres);
                 my_core = (unsigned long long)fmin(2.*h + 1., (double)(e - s + 1));
             }
         }
@@ -282,226 +299,6 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
 }
 
 
-struct SweepParams
-{
-    LineRec const *recs;       // [layers][num_lines]
-    double const *v0;          // sorted base centres (tile -> line range search)
-    uint64_t num_lines;
-    double w0;
-    double wres;
-    uint64_t nw;
-    int fsteps;
-    double margin;             // 25 cm-1 window + pressure shift + slack [cm-1]
-    int num_layers;
-    LayerView lay;
-    Tables tab;
-    double *tau;               // [layers][nw]
-};
-
-
-// 1/d for d > 0 to ~1 ulp without the IEEE division slow path: float seed +
-// two Newton steps in double.  Only used where the result feeds the double
-// accumulator (pure-Lorentz branch), never before a float rounding.
-__device__ __forceinline__ double fast_rcp(double const d)
-{
-    double r = (double)__frcp_rn(__double2float_rn(d));
-    double e = fma(-d, r, 1.0);
-    r = fma(r, e, r);
-    e = fma(-d, r, 1.0);
-    r = fma(r, e, r);
-    return r;
-}
-
-
-// K3: far-wing + pure-Lorentz gather.  Thread t of warp w owns grid points
-// tile_base + w*32*PTS + j*32 + lane, j = 0..PTS-1 (consecutive lanes ->
-// consecutive points -> coalesced stores; a line's window covers whole
-// 32-point chunks except at its two ends).
-template <int PTS>
-__global__ void __launch_bounds__(kSweepThreads)
-wing_sweep_kernel(SweepParams const p)
-{
-    __shared__ LineRec stage[kStageRecs];
-    __shared__ uint64_t range[2];
-    int const layer = blockIdx.y;
-    int const lane = threadIdx.x & 31;
-    int const warp = threadIdx.x >> 5;
-    int64_t const tile_base = (int64_t)blockIdx.x*(kSweepThreads*PTS);
-    int64_t const warp_base = tile_base + (int64_t)warp*(32*PTS);
-    int64_t const warp_last = warp_base + 32*PTS - 1;
-    int const F = p.fsteps;
-
-    if (threadIdx.x == 0)
-    {
-        // Lines whose +-F window can touch this tile: conservative range in the
-        // sorted base centres; the exact test uses each record's fc.
-        double const lo = p.w0 + (double)tile_base*p.wres - p.margin;
-        double const hi = p.w0 + (double)(tile_base + kSweepThreads*PTS)*p.wres + p.margin;
-        uint64_t a = 0, b = p.num_lines;
-        while (a < b) { uint64_t m = (a + b)/2; if (p.v0[m] < lo) a = m + 1; else b = m; }
-        range[0] = a;
-        b = p.num_lines;
-        while (a < b) { uint64_t m = (a + b)/2; if (p.v0[m] <= hi) a = m + 1; else b = m; }
-        range[1] = a;
-    }
-    __syncthreads();
-    uint64_t const first = range[0];
-    uint64_t const last = range[1];
-
-    double acc[PTS];
-    double fd[PTS];
-#pragma unroll
-    for (int j=0; j<PTS; ++j)
-    {
-        acc[j] = 0.;
-        fd[j] = (double)(warp_base + j*32 + lane);
-    }
-
-    LineRec const *recs = p.recs + (size_t)layer*p.num_lines;
-    for (uint64_t base=first; base<last; base+=kStageRecs)
-    {
-        int const cnt = (int)((last - base) < (uint64_t)kStageRecs ? (last - base) : kStageRecs);
-        __syncthreads();
-        {
-            // 256 threads x 16 B = 128 records.
-            int const idx = threadIdx.x >> 1;
-            if (idx < cnt)
-            {
-                reinterpret_cast<int4 *>(stage)[threadIdx.x] =
-                    reinterpret_cast<int4 const *>(recs + base)[threadIdx.x];
-            }
-        }
-        __syncthreads();
-        for (int r0=0; r0<cnt; r0+=32)
-        {
-            int const idx = r0 + lane;
-            int const fc_l = idx < cnt ? stage[idx].fc : kSkip;
-            bool const hit = (fc_l != kSkip) && ((int64_t)fc_l + F >= warp_base) &&
-                             ((int64_t)fc_l - F <= warp_last);
-            unsigned mask = __ballot_sync(0xffffffffu, hit);
-            while (mask)
-            {
-                int const b = __ffs(mask) - 1;
-                mask &= mask - 1;
-                LineRec const r = stage[r0 + b];
-                int64_t const s = r.fc - F < 0 ? 0 : r.fc - F;
-                int64_t const e = (uint64_t)(r.fc + F) >= p.nw ? (int64_t)p.nw - 1 : r.fc + F;
-                double const sd = (double)s;
-                double const dwno = __dadd_rn(__dmul_rn(sd, p.wres), p.w0);
-                double const repwid_d = (double)r.repwid;
-                float const yq = r.y*r.y;
-                if (r.y >= kLorentzY)
-                {
-#pragma unroll
-                    for (int j=0; j<PTS; ++j)
-                    {
-                        int64_t const cb = warp_base + j*32;
-                        if (cb <= e && cb + 31 >= s)
-                        {
-                            int64_t const f = cb + lane;
-                            float const xi = abscissa(dwno, fd[j] - sd, p.wres, r.v, repwid_d);
-                            double const d = (double)(xi*xi + yq);
-                            double const k = (f >= s && f <= e) ? fast_rcp(d) : 0.;
-                            acc[j] = fma(r.c, k, acc[j]);
-                        }
-                    }
-                }
-                else
-                {
-                    float const yrrtpi = r.y*kRsqrpi;
-#pragma unroll
-                    for (int j=0; j<PTS; ++j)
-                    {
-                        int64_t const cb = warp_base + j*32;
-                        if (cb <= e && cb + 31 >= s)
-                        {
-                            int64_t const f = cb + lane;
-                            float const xi = abscissa(dwno, fd[j] - sd, p.wres, r.v, repwid_d);
-                            float const xq = xi*xi;
-                            float const kf = yrrtpi/(xq + yq);
-                            bool const ok = (f >= s) && (f <= e) && (fabsf(xi) >= r.xlim0);
-                            acc[j] = fma(r.c, (double)(ok ? kf : 0.f), acc[j]);
-                        }
-                    }
-                }
-            }
-        }
-    }
-
-    // Epilogue: continua, CFCs, CIA (kernels.c:469-510, 585-630), one store.
-    int const L = p.num_layers;
-#pragma unroll
-    for (int j=0; j<PTS; ++j)
-    {
-        int64_t const f = warp_base + j*32 + lane;
-        if (f >= (int64_t)p.nw) continue;
-        double t = acc[j];
-        if (p.tab.h2o_slot >= 0)
-        {
-            double const tref = 296.;
-            double const T = p.lay.tavg[layer];
-            double const Ps = p.lay.ps[p.tab.h2o_slot*L + layer];
-            double const N = p.lay.ns[p.tab.h2o_slot*L + layer];
-            double const P = p.lay.pavg[layer];
-            double const CS = p.tab.h2o[0][f];
-            double const T0 = p.tab.h2o[1][f];
-            double const CF = p.tab.h2o[2][f];
-            double const T0F = p.tab.h2o[3][f];
-            t += N*(tref/T)*((CS*Ps*exp(T0*(tref - T))) + (CF*(P - Ps)*exp(T0F*(tref - T))));
-        }
-        if (p.tab.o3_slot >= 0)
-        {
-            t += p.lay.ns[p.tab.o3_slot*L + layer]*p.tab.o3[f];
-        }
-        for (int c=0; c<p.tab.num_cfcs; ++c)
-        {
-            t += p.lay.cfc[c*L + layer]*p.tab.cfc[c][f];
-        }
-        for (int c=0; c<p.tab.num_cias; ++c)
-        {
-            t += p.lay.cia[c*L + layer]*p.tab.cia[c][f];
-        }
-        p.tau[(size_t)layer*p.nw + f] = t;
-    }
-}
-
-
-// K3c: samples with |x| < XLIM0 of every Voigt-branch record.  Eight lanes
-// share one record and stride over its near-centre window; contributions are
-// scattered with double atomics (about 1 % of all samples at 0.1 cm-1).
-__global__ void __launch_bounds__(256)
-core_sweep_kernel(SweepParams const p)
-{
-    constexpr int G = 8;
-    uint64_t const rec_id = ((uint64_t)blockIdx.x*blockDim.x + threadIdx.x)/G;
-    int const sub = threadIdx.x & (G - 1);
-    int const layer = blockIdx.y;
-    if (rec_id >= p.num_lines) return;
-    LineRec const r = p.recs[(size_t)layer*p.num_lines + rec_id];
-    if (r.fc == kSkip || r.y >= kLorentzY) return;
-    int const F = p.fsteps;
-    int64_t const s = r.fc - F < 0 ? 0 : r.fc - F;
-    int64_t const e = (uint64_t)(r.fc + F) >= p.nw ? (int64_t)p.nw - 1 : r.fc + F;
-    double const repwid_d = (double)r.repwid;
-    // Half-width of the |x| < XLIM0 window in grid points, rounded up generously.
-    double const hd = (double)r.xlim0/(repwid_d*p.wres) + 2.;
-    int64_t const h = hd < (double)(2*F + 2) ? (int64_t)hd : (int64_t)(2*F + 2);
-    int64_t const a = r.fc - h < s ? s : r.fc - h;
-    int64_t const b = r.fc + h > e ? e : r.fc + h;
-    double const sd = (double)s;
-    double const dwno = __dadd_rn(__dmul_rn(sd, p.wres), p.w0);
-    double *tau = p.tau + (size_t)layer*p.nw;
-    for (int64_t f=a+sub; f<=b; f+=G)
-    {
-        float const xi = abscissa(dwno, (double)(f - s), p.wres, r.v, repwid_d);
-        if (fabsf(xi) < r.xlim0)
-        {
-            double const k = voigt_core(xi, r.y);
-            atomicAdd(&tau[f], r.c*k);
-        }
-    }
-}
-
 }  // namespace grt
 
 
@@ -521,6 +318,7 @@ struct grt_gas
     // merged host copy of the line list (kept until finalised)
     std::vector<double> h_v0, h_delta, h_s0, h_en, h_nair, h_yair, h_yself;
     std::vector<uint16_t> h_slotiso;
+    std::vector<double> h_sorted_v0;     // centres in device order (tile cost estimate)
     bool dirty = true;
     double max_abs_delta = 0.;
 
@@ -538,8 +336,16 @@ struct grt_gas
     LineRec *d_recs = nullptr;
     size_t recs_capacity = 0;
     PrepStats *d_stats = nullptr;
+    int *d_tile_order = nullptr;         // tiles by line count, heaviest first
+    unsigned int *d_work_counter = nullptr;
+    int num_tiles = 0;
+    unsigned *d_tile_first = nullptr;    // (inside the d_tile_order allocation)
+    unsigned *d_tile_last = nullptr;
+    int tiles_pts = 0;                   // PTS the work list was built for
+    double tiles_margin = 0.;            // margin [cm-1] it was built with
     std::vector<double *> owned_tables;
-    uint64_t stats[4] = {0, 0, 0, 0};
+    uint64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 
@@ -591,6 +397,7 @@ static int finalize_lines(grt_gas *g)
         maxd = std::max(maxd, std::fabs(g->h_delta[o]));
     }
     g->max_abs_delta = maxd;
+    g->h_sorted_v0.assign(packed.begin(), packed.begin() + n);
     if (g->d_lines) { GRT_CUDA(cudaFree(g->d_lines)); g->d_lines = nullptr; }
     if (g->d_slotiso) { GRT_CUDA(cudaFree(g->d_slotiso)); g->d_slotiso = nullptr; }
     if (g->d_tips) { GRT_CUDA(cudaFree(g->d_tips)); g->d_tips = nullptr; }
@@ -613,9 +420,55 @@ static int finalize_lines(grt_gas *g)
     g->num_lines = n;
     g->meta.tips = g->d_tips;
     g->dirty = false;
+    g->tiles_pts = 0;
     return 0;
 }
 
+
+// Work list of the persistent sweep: for every warp tile (32*PTS grid points) the range
+// of records whose window can reach it (binary searches in the sorted centres, with the
+// pressure-shift margin) and the tiles ordered by that count, heaviest first, so that
+// the dynamic scheduler ends with the cheap tiles (longest-processing-time-first).
+static int prepare_tiles(grt_gas *g, int pts, double margin)
+{
+    if (g->tiles_pts == pts && g->tiles_margin >= margin && g->d_tile_order != nullptr) return 0;
+    margin *= 1.25;   // head-room so that a slightly larger surface pressure does not rebuild
+    int const tile = 32*pts;
+    int const num_tiles = (int)((g->nw + tile - 1)/tile);
+    std::vector<double> const &v0 = g->h_sorted_v0;
+    std::vector<std::pair<uint64_t, int>> cost((size_t)num_tiles);
+    std::vector<unsigned> first((size_t)num_tiles), last((size_t)num_tiles);
+    for (int t=0; t<num_tiles; ++t)
+    {
+        double const lo = g->w0 + (double)t*tile*g->dw - margin;
+        double const hi = g->w0 + (double)(t + 1)*tile*g->dw + margin;
+        auto const a = std::lower_bound(v0.begin(), v0.end(), lo);
+        auto const b = std::upper_bound(v0.begin(), v0.end(), hi);
+        first[t] = (unsigned)(a - v0.begin());
+        last[t] = (unsigned)(b - v0.begin());
+        cost[t] = {(uint64_t)(b - a), t};
+    }
+    std::stable_sort(cost.begin(), cost.end(),
+                     [](auto const &x, auto const &y) { return x.first > y.first; });
+    std::vector<int> order((size_t)num_tiles);
+    for (int t=0; t<num_tiles; ++t) order[t] = cost[t].second;
+    if (g->d_tile_order) { GRT_CUDA(cudaFree(g->d_tile_order)); g->d_tile_order = nullptr; }
+    size_t const nt = (size_t)std::max(num_tiles, 1);
+    GRT_CUDA(cudaMalloc(&g->d_tile_order, sizeof(int)*3*nt));
+    g->d_tile_first = reinterpret_cast<unsigned *>(g->d_tile_order + nt);
+    g->d_tile_last = reinterpret_cast<unsigned *>(g->d_tile_order + 2*nt);
+    GRT_CUDA(cudaMemcpyAsync(g->d_tile_order, order.data(), sizeof(int)*num_tiles,
+                             cudaMemcpyHostToDevice, g->stream));
+    GRT_CUDA(cudaMemcpyAsync(g->d_tile_first, first.data(), sizeof(unsigned)*num_tiles,
+                             cudaMemcpyHostToDevice, g->stream));
+    GRT_CUDA(cudaMemcpyAsync(g->d_tile_last, last.data(), sizeof(unsigned)*num_tiles,
+                             cudaMemcpyHostToDevice, g->stream));
+    GRT_CUDA(cudaStreamSynchronize(g->stream));
+    g->num_tiles = num_tiles;
+    g->tiles_pts = pts;
+    g->tiles_margin = margin;
+    return 0;
+}
 
 extern "C" {
 
@@ -653,6 +506,8 @@ int grt_gas_create(grt_gas **gas, int device, int num_levels, double w0, double 
     GRT_CUDA(cudaMalloc(&g->d_layer, sizeof(double)*layer_doubles));
     GRT_CUDA(cudaMalloc(&g->d_inputs, sizeof(double)*input_doubles));
     GRT_CUDA(cudaMalloc(&g->d_stats, sizeof(PrepStats)));
+    GRT_CUDA(cudaMalloc(&g->d_work_counter, sizeof(unsigned int)));
+    for (int k=0; k<5; ++k) GRT_CUDA(cudaEventCreate(&g->ev[k]));
     *gas = g;
     return 0;
 }
@@ -669,7 +524,10 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_inputs);
     cudaFree(g->d_recs);
     cudaFree(g->d_stats);
+    cudaFree(g->d_tile_order);
+    cudaFree(g->d_work_counter);
     for (double *t : g->owned_tables) cudaFree(t);
+    for (int k=0; k<5; ++k) if (g->ev[k]) cudaEventDestroy(g->ev[k]);
     delete g;
     return 0;
 }
@@ -823,6 +681,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     double const cia_c = (atmtobarye*atmtobarye)/(kboltz*m_air*grav*2.);
 
     int launches = 0;
+    GRT_CUDA(cudaEventRecord(g->ev[0], st));
     column_prep_kernel<<<(L + 63)/64, 64, 0, st>>>(L, in, g->meta, lay, cia_c);
     ++launches;
 
@@ -855,42 +714,79 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
         ++launches;
     }
 
+    GRT_CUDA(cudaEventRecord(g->ev[1], st));
     SweepParams sp;
     sp.recs = g->d_recs;
-    sp.v0 = g->d_lines;
     sp.num_lines = N;
     sp.w0 = g->w0;
     sp.wres = g->dw;
-    sp.nw = g->nw;
+    sp.nw = (int)g->nw;
     sp.fsteps = fsteps;
     double pmax = 0.;
     for (int i=0; i<levels; ++i) pmax = std::max(pmax, std::fabs(p_atm[i]));
-    sp.margin = (double)fsteps*g->dw + 2.*g->dw + g->max_abs_delta*pmax + 1e-6;
+    double const margin = (double)fsteps*g->dw + 2.*g->dw + g->max_abs_delta*pmax + 1e-6;
     sp.num_layers = L;
     sp.lay = lay;
     sp.tab = g->tab;
     sp.tau = tau_dev;
 
-    // Points per thread: bigger tiles amortise per-line work at fine resolution.
-    if (g->dw < 0.05)
+    // Points per thread (PTS): 32*PTS points per warp.  Wider warps amortise the per-line
+    // work better; narrower ones waste fewer lanes at window ends and balance better.
+    int pts = (g->dw < 0.05) ? 8 : 4;
+    if (char const *env = getenv("GRT_SWEEP_PTS")) pts = atoi(env);
+    if (pts != 2 && pts != 4 && pts != 8) pts = 4;
+    GRT_TRY(prepare_tiles(g, pts, margin));
+    sp.num_tiles = g->num_tiles;
+    sp.tile_order = g->d_tile_order;
+    sp.tile_first = g->d_tile_first;
+    sp.tile_last = g->d_tile_last;
+    sp.work_counter = g->d_work_counter;
+    GRT_CUDA(cudaMemsetAsync(g->d_work_counter, 0, sizeof(unsigned int), st));
     {
-        constexpr int PTS = 8;
-        dim3 grid((unsigned)((g->nw + kSweepThreads*PTS - 1)/(kSweepThreads*PTS)), (unsigned)L);
-        wing_sweep_kernel<PTS><<<grid, kSweepThreads, 0, st>>>(sp);
-    }
-    else
-    {
-        constexpr int PTS = 4;
-        dim3 grid((unsigned)((g->nw + kSweepThreads*PTS - 1)/(kSweepThreads*PTS)), (unsigned)L);
-        wing_sweep_kernel<PTS><<<grid, kSweepThreads, 0, st>>>(sp);
+        // Persistent CTAs: one wave that fills every SM; work items are pulled from the
+        // counter, heaviest tiles first.
+        int const sms = sm_count(g->device);
+        int per_sm = 0;
+        unsigned const total = (unsigned)g->num_tiles*(unsigned)L;
+        if (pts == 2)
+        {
+            GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<2>,
+                                                                   kSweepThreads, 0));
+            unsigned const grid = std::min<unsigned>((total + 7)/8, (unsigned)(sms*std::max(per_sm, 1)));
+            wing_sweep_kernel<2><<<std::max(grid, 1u), kSweepThreads, 0, st>>>(sp);
+        }
+        else if (pts == 4)
+        {
+            GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<4>,
+                                                                   kSweepThreads, 0));
+            unsigned const grid = std::min<unsigned>((total + 7)/8, (unsigned)(sms*std::max(per_sm, 1)));
+            wing_sweep_kernel<4><<<std::max(grid, 1u), kSweepThreads, 0, st>>>(sp);
+        }
+        else
+        {
+            GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<8>,
+                                                                   kSweepThreads, 0));
+            unsigned const grid = std::min<unsigned>((total + 7)/8, (unsigned)(sms*std::max(per_sm, 1)));
+            wing_sweep_kernel<8><<<std::max(grid, 1u), kSweepThreads, 0, st>>>(sp);
+        }
     }
     ++launches;
+    GRT_CUDA(cudaEventRecord(g->ev[2], st));
     if (N > 0)
     {
-        dim3 grid((unsigned)((N*8 + 255)/256), (unsigned)L);
-        core_sweep_kernel<<<grid, 256, 0, st>>>(sp);
+        if (g->dw < 0.05)
+        {
+            dim3 grid((unsigned)((N*32 + 255)/256), (unsigned)L);
+            core_sweep_kernel<32><<<grid, 256, 0, st>>>(sp);
+        }
+        else
+        {
+            dim3 grid((unsigned)((N*8 + 255)/256), (unsigned)L);
+            core_sweep_kernel<8><<<grid, 256, 0, st>>>(sp);
+        }
         ++launches;
     }
+    GRT_CUDA(cudaEventRecord(g->ev[3], st));
     GRT_CUDA(cudaGetLastError());
     PrepStats hs;
     GRT_CUDA(cudaMemcpyAsync(&hs, g->d_stats, sizeof(PrepStats), cudaMemcpyDeviceToHost, st));
@@ -899,13 +795,19 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     g->stats[1] = hs.samples;
     g->stats[2] = (uint64_t)launches;
     g->stats[3] = hs.lorentz;
+    float ms[3] = {0.f, 0.f, 0.f};
+    for (int k=0; k<3; ++k) GRT_CUDA(cudaEventElapsedTime(&ms[k], g->ev[k], g->ev[k+1]));
+    g->stats[4] = (uint64_t)(ms[0]*1e6f);   // K0 + K1 [ns]
+    g->stats[5] = (uint64_t)(ms[1]*1e6f);   // K3 wing sweep [ns]
+    g->stats[6] = (uint64_t)(ms[2]*1e6f);   // K3c core sweep [ns]
+    g->stats[7] = hs.core;
     return 0;
 }
 
-int grt_gas_last_stats(grt_gas const *g, uint64_t out[4])
+int grt_gas_last_stats(grt_gas const *g, uint64_t out[8])
 {
     if (g == nullptr || out == nullptr) return fail("null argument");
-    for (int k=0; k<4; ++k) out[k] = g->stats[k];
+    for (int k=0; k<8; ++k) out[k] = g->stats[k];
     return 0;
 }
 

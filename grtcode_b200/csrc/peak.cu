@@ -66,3 +66,53 @@ extern "C" int grt_measure_fma_peak(int device, double *fp64_tflops, double *fp3
     GRT_TRY(grt::measure<float>(device, st, fp32_tflops));
     return 0;
 }
+
+// ---- self-tests of the arithmetic shortcuts of the sweep (voigt.cuh) -----------------
+#include "voigt.cuh"
+
+namespace grt {
+
+// div_exact vs IEEE division and widen_positive vs (double) on pseudo-random operands in
+// the ranges the sweep produces: a in [1e-19, 1e2], b in [1, 1e16].
+__global__ void selftest_kernel(unsigned long long n, unsigned long long seed,
+                                unsigned long long *bad)
+{
+    unsigned long long i = (unsigned long long)blockIdx.x*blockDim.x + threadIdx.x;
+    unsigned long long local = 0;
+    for (; i<n; i+=(unsigned long long)gridDim.x*blockDim.x)
+    {
+        unsigned long long z = seed + i*0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30))*0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27))*0x94D049BB133111EBull;
+        z ^= z >> 31;
+        unsigned const lo = (unsigned)z;
+        unsigned const hi = (unsigned)(z >> 32);
+        // random mantissas, exponents spread over the ranges above
+        float const a = __uint_as_float(((64u + lo%70u) << 23) | (hi & 0x7fffffu));
+        float const b = __uint_as_float(((127u + (lo >> 8)%54u) << 23) | ((hi >> 9) & 0x7fffffu) |
+                                        ((lo >> 20) & 0x1ffu));
+        float const q1 = div_exact(a, b);
+        float const q2 = __fdiv_rn(a, b);
+        if (__float_as_uint(q1) != __float_as_uint(q2)) ++local;
+        if (widen_positive(q2) != (double)q2) ++local;
+    }
+    if (local) atomicAdd(bad, local);
+}
+
+}  // namespace grt
+
+extern "C" int grt_selftest_arithmetic(int device, unsigned long long n, unsigned long long seed,
+                                       unsigned long long *mismatches)
+{
+    cudaStream_t st;
+    GRT_TRY(grt::stream_of(device, &st));
+    unsigned long long *d;
+    GRT_CUDA(cudaMalloc(&d, sizeof(*d)));
+    GRT_CUDA(cudaMemsetAsync(d, 0, sizeof(*d), st));
+    grt::selftest_kernel<<<grt::sm_count(device)*8, 256, 0, st>>>(n, seed, d);
+    GRT_CUDA(cudaGetLastError());
+    GRT_CUDA(cudaMemcpyAsync(mismatches, d, sizeof(*d), cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    GRT_CUDA(cudaFree(d));
+    return 0;
+}

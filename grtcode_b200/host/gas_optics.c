@@ -371,7 +371,7 @@ int get_num_molecules(GasOptics_t const * const gas_optics, int * const n)
     return GRTCODE_SUCCESS;
 }
 
-int gas_optics_stats(GasOptics_t const * const gas_optics, uint64_t out[4])
+int gas_optics_stats(GasOptics_t const * const gas_optics, uint64_t out[8])
 {
     REQUIRE_PTR(gas_optics);
     REQUIRE_PTR(out);

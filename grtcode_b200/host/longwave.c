@@ -80,7 +80,6 @@ int calculate_lw_column(Longwave_t * const lw, Optics_t const * const gas, fp_t 
     REQUIRE_PTR(pressure);
     REQUIRE_PTR(T_layers);
     REQUIRE_PTR(T_levels);
-    REQUIRE_PTR(emis);
     REQUIRE_PTR(up);
     REQUIRE_PTR(down);
     TRY(check_against_optics(lw, gas));
@@ -91,7 +90,10 @@ int calculate_lw_column(Longwave_t * const lw, Optics_t const * const gas, fp_t 
     {
         p_atm[i] = pressure[i]*mbtoatm;
     }
-    GPU(grt_copy_to_device(lw->device, lw->emissivity, emis, sizeof(fp_t)*lw->grid.n));
+    if (emis != NULL)
+    {
+        GPU(grt_copy_to_device(lw->device, lw->emissivity, emis, sizeof(fp_t)*lw->grid.n));
+    }
     GPU(grt_lw_column(lw->device, lw->num_levels, lw->grid.w0, lw->grid.dw, lw->grid.n, p_atm,
                       T_surf, T_layers, T_levels, gas->tau, lw->emissivity, up, down));
     return GRTCODE_SUCCESS;

@@ -104,9 +104,6 @@ int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const gas, fp_t
     REQUIRE_PTR(sw);
     REQUIRE_PTR(gas);
     REQUIRE_PTR(pressure);
-    REQUIRE_PTR(sfc_alpha_dir);
-    REQUIRE_PTR(sfc_alpha_dif);
-    REQUIRE_PTR(solar_flux);
     REQUIRE_PTR(up);
     REQUIRE_PTR(down);
     TRY(check_against_optics(sw, gas));
@@ -117,7 +114,10 @@ int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const gas, fp_t
     {
         p_atm[i] = pressure[i]*mbtoatm;
     }
-    TRY(upload_surface(sw, sfc_alpha_dir, sfc_alpha_dif, solar_flux));
+    if (sfc_alpha_dir != NULL && sfc_alpha_dif != NULL && solar_flux != NULL)
+    {
+        TRY(upload_surface(sw, sfc_alpha_dir, sfc_alpha_dif, solar_flux));
+    }
     GPU(grt_sw_column(sw->device, sw->num_levels, sw->grid.w0, sw->grid.dw, sw->grid.n, p_atm,
                       gas->tau, mu_dir, mu_dif, sw->sfc_alpha_dir, sw->sfc_alpha_dif,
                       total_solar_irradiance, sw->solar_flux, up, down));

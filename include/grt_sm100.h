@@ -88,8 +88,11 @@ int grt_gas_optical_depth(grt_gas *gas, double const *p_atm, double const *t,
 /* Counters of the last grt_gas_optical_depth call (bench/roofline bookkeeping):
  * out[0] = (line,layer) records inside the grid, out[1] = Voigt samples the
  * reference would evaluate for them, out[2] = kernels launched,
- * out[3] = records taking the pure-Lorentz branch. */
-int grt_gas_last_stats(grt_gas const *gas, uint64_t out[4]);
+ * out[3] = records taking the pure-Lorentz branch; device durations in ns measured
+ * with CUDA events on the library stream: out[4] = column + line preprocessing,
+ * out[5] = far-wing sweep kernel, out[6] = line-core kernel; out[7] = upper bound of
+ * the samples the line-core kernel evaluates. */
+int grt_gas_last_stats(grt_gas const *gas, uint64_t out[8]);
 
 /* ---- Rayleigh + optics mixing: replaces rayleigh_scattering
  * (shortwave/src/rayleigh.c:100-144) and add_optics (utilities/src/optics.c:84-148). */
@@ -135,6 +138,11 @@ int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t num
 /* ---- measurement helper: sustained FP64 / FP32 FMA throughput of this GPU
  * [TFLOP/s, FMA = 2 flop], the roofline denominator of the Voigt sweep. */
 int grt_measure_fma_peak(int device, double *fp64_tflops, double *fp32_tflops);
+
+/* ---- self-test: the sweep's division and float->double shortcuts against the IEEE
+ * operations on n pseudo-random operands; *mismatches must come back 0. */
+int grt_selftest_arithmetic(int device, unsigned long long n, unsigned long long seed,
+                            unsigned long long *mismatches);
 
 #ifdef __cplusplus
 }

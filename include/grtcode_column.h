@@ -3,7 +3,10 @@
  * what framework/src/driver.c:360-424 (column_calculation with -integrated)
  * computes through rayleigh_scattering + add_optics + calculate_*_fluxes +
  * output_fluxes.  `gas` is the Optics_t filled by calculate_optical_depth.
- * Outputs: up/down broadband flux [W m-2] on every level (num_levels values). */
+ * Outputs: up/down broadband flux [W m-2] on every level (num_levels values).
+ * The spectral surface arrays (emis; sfc_alpha_dir, sfc_alpha_dif, solar_flux) may be
+ * NULL, meaning "unchanged since the previous call": the copies already resident on
+ * the GPU are reused (a batched driver uploads them once per site). */
 #ifndef GRTCODE_COLUMN_H_
 #define GRTCODE_COLUMN_H_
 #include "gas_optics.h"
@@ -28,5 +31,5 @@ EXTERN int integrate_fluxes(Device_t const device, int const num_levels,
 EXTERN int heating_rates(int const num_levels, fp_t const * const pressure,
                          fp_t const * const up, fp_t const * const down, fp_t * const rate);
 /* Counters of the last calculate_optical_depth call: see grt_gas_last_stats. */
-EXTERN int gas_optics_stats(GasOptics_t const * const gas_optics, uint64_t out[4]);
+EXTERN int gas_optics_stats(GasOptics_t const * const gas_optics, uint64_t out[8]);
 #endif
