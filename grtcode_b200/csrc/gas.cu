@@ -220,30 +220,31 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         float const y = (float)((double)repwid*gamma);
         LineRec r;
         r.v = v;
-        r.repwid = repwid;
+        r.repwid = (double)repwid;
         r.y = y;
         double const sn = S*Ns;
         float const yq = y*y;
+        r.yq = yq;
+        r.yrrtpi = y*kRsqrpi;
         r.a0 = (float)((double)yq + 0.5);                 // RFM_voigt.c:177-179
         r.d0 = r.a0*r.a0;
         r.d2 = (float)((double)(yq + yq) - 1.0);
+        voigt_limits(y, &r.xlim0, &r.xlim1);
+        // Grid points farther than hw0 from fc have |x| >= XLIM0: |w_f - v| >=
+        // (|f - fc| - 1/2) wres, and 1.5 grid steps of slack cover the float rounding of x.
+        double const h0 = ceil((double)r.xlim0/((double)repwid*wres)) + 2.;
         if (y >= kLorentzY)
         {
-            r.xlim0 = 0.f;
-            r.xlim1 = 0.f;
+            r.hw0 = kHwLorentz;
             r.c = sn*(double)(repwid*y)/3.14159265358979323846;
         }
         else
         {
-            voigt_limits(y, &r.xlim0, &r.xlim1);
+            r.hw0 = h0 < (double)kHwMax ? (int)h0 : kHwMax;
             r.c = sn*(double)(kRsqrpi*repwid);
-            if (!(y >= 1e-18f))
-            {
-                // Vanishing (or NaN) Y: far-wing values may be zero or subnormal; let
-                // the line-core kernel evaluate the whole window with the full routine.
-                r.xlim0 = __int_as_float(0x7f800000);
-                r.xlim1 = __int_as_float(0x7f800000);
-            }
+            // Vanishing (or NaN) Y: far-wing values may be zero or subnormal; let
+            // the line-core kernel evaluate the whole window with the full routine.
+            if (!(y >= 1e-18f)) r.hw0 = kHwCoreOnly;
         }
         double const fcd = floor((2.*((v - w0)/wres) + 1.)/2.);
         if (fcd >= 0. && fcd < (double)nw)
@@ -262,6 +263,7 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
             {
                 double const h = (double)r.xlim1/((double)repwid*wres);
                 my_core = (unsigned long long)fmin(2.*h + 1., (double)(e - s + 1));
+                if (r.hw0 == kHwCoreOnly) my_core = my_samples;
             }
         }
         else
@@ -467,6 +469,30 @@ static int prepare_tiles(grt_gas *g, int pts, double margin)
     g->num_tiles = num_tiles;
     g->tiles_pts = pts;
     g->tiles_margin = margin;
+    return 0;
+}
+
+// Persistent CTAs: one wave that fills every SM; work items are pulled from the counter.
+template <int PTS, int NL>
+static int launch_wing(SweepParams const &sp, int const sms, cudaStream_t const st)
+{
+    using Cfg = SweepConfig<PTS, NL>;
+    static bool configured = false;
+    if (!configured)
+    {
+        GRT_CUDA(cudaFuncSetAttribute(wing_sweep_kernel<PTS, NL>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+        configured = true;
+    }
+    int per_sm = 0;
+    GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<PTS, NL>,
+                                                           kSweepThreads, Cfg::kSmemBytes));
+    int const groups = (sp.num_layers + NL - 1)/NL;
+    unsigned const total = (unsigned)sp.num_tiles*(unsigned)groups;
+    unsigned const grid = std::min<unsigned>((total + kSweepWarps - 1)/kSweepWarps,
+                                             (unsigned)(sms*std::max(per_sm, 1)));
+    wing_sweep_kernel<PTS, NL><<<std::max(grid, 1u), kSweepThreads, Cfg::kSmemBytes, st>>>(sp);
+    GRT_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -730,11 +756,16 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     sp.tab = g->tab;
     sp.tau = tau_dev;
 
-    // Points per thread (PTS): 32*PTS points per warp.  Wider warps amortise the per-line
-    // work better; narrower ones waste fewer lanes at window ends and balance better.
+    // Points per thread (PTS): 32*PTS points per warp; NL layers per work item.  Wider
+    // tiles amortise the per-line work better; narrower ones waste fewer lanes at window
+    // ends and balance better.  More layers per item amortise the grid abscissae.
     int pts = (g->dw < 0.05) ? 8 : 4;
+    int nl = 1;
     if (char const *env = getenv("GRT_SWEEP_PTS")) pts = atoi(env);
+    if (char const *env = getenv("GRT_SWEEP_NL")) nl = atoi(env);
     if (pts != 2 && pts != 4 && pts != 8) pts = 4;
+    if (nl != 1 && nl != 2 && nl != 4) nl = 1;
+    if (pts == 8 && nl == 4) nl = 2;
     GRT_TRY(prepare_tiles(g, pts, margin));
     sp.num_tiles = g->num_tiles;
     sp.tile_order = g->d_tile_order;
@@ -743,32 +774,20 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     sp.work_counter = g->d_work_counter;
     GRT_CUDA(cudaMemsetAsync(g->d_work_counter, 0, sizeof(unsigned int), st));
     {
-        // Persistent CTAs: one wave that fills every SM; work items are pulled from the
-        // counter, heaviest tiles first.
         int const sms = sm_count(g->device);
-        int per_sm = 0;
-        unsigned const total = (unsigned)g->num_tiles*(unsigned)L;
-        if (pts == 2)
+        int rc = 0;
+        switch (pts*10 + nl)
         {
-            GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<2>,
-                                                                   kSweepThreads, 0));
-            unsigned const grid = std::min<unsigned>((total + 7)/8, (unsigned)(sms*std::max(per_sm, 1)));
-            wing_sweep_kernel<2><<<std::max(grid, 1u), kSweepThreads, 0, st>>>(sp);
+            case 21: rc = launch_wing<2, 1>(sp, sms, st); break;
+            case 22: rc = launch_wing<2, 2>(sp, sms, st); break;
+            case 24: rc = launch_wing<2, 4>(sp, sms, st); break;
+            case 41: rc = launch_wing<4, 1>(sp, sms, st); break;
+            case 42: rc = launch_wing<4, 2>(sp, sms, st); break;
+            case 44: rc = launch_wing<4, 4>(sp, sms, st); break;
+            case 81: rc = launch_wing<8, 1>(sp, sms, st); break;
+            default: rc = launch_wing<8, 2>(sp, sms, st); break;
         }
-        else if (pts == 4)
-        {
-            GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<4>,
-                                                                   kSweepThreads, 0));
-            unsigned const grid = std::min<unsigned>((total + 7)/8, (unsigned)(sms*std::max(per_sm, 1)));
-            wing_sweep_kernel<4><<<std::max(grid, 1u), kSweepThreads, 0, st>>>(sp);
-        }
-        else
-        {
-            GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<8>,
-                                                                   kSweepThreads, 0));
-            unsigned const grid = std::min<unsigned>((total + 7)/8, (unsigned)(sms*std::max(per_sm, 1)));
-            wing_sweep_kernel<8><<<std::max(grid, 1u), kSweepThreads, 0, st>>>(sp);
-        }
+        GRT_TRY(rc);
     }
     ++launches;
     GRT_CUDA(cudaEventRecord(g->ev[2], st));

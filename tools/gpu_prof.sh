@@ -1,0 +1,10 @@
+#!/bin/bash
+# ncu full capture of the sweep kernels on a quarter-scale config 2 (shorter launches:
+# the 470 ms SW launch of the full workload overflows ncu's counters).
+mkdir -p gpurun_out
+BENCH="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --scale 0.25"
+$BENCH > gpurun_out/plain_q.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:sweep -s 4 -c 4 \
+    -f -o gpurun_out/prof_sweep_q $BENCH > gpurun_out/ncu_q.log 2>&1
+tail -2 gpurun_out/ncu_q.log
+grep '^{' gpurun_out/plain_q.log | cut -c1-400
