@@ -220,7 +220,7 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         float const y = (float)((double)repwid*gamma);
         LineRec r;
         r.v = v;
-        r.repwid = (double)repwid;
+        r.repwid = repwid;
         r.y = y;
         double const sn = S*Ns;
         float const yq = y*y;
@@ -232,7 +232,18 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         voigt_limits(y, &r.xlim0, &r.xlim1);
         // Grid points farther than hw0 from fc have |x| >= XLIM0: |w_f - v| >=
         // (|f - fc| - 1/2) wres, and 1.5 grid steps of slack cover the float rounding of x.
-        double const h0 = ceil((double)r.xlim0/((double)repwid*wres)) + 2.;
+        double const step = (double)repwid*wres;          // x per grid point
+        double const h0 = ceil((double)r.xlim0/step) + 2.;
+        // Conservative 16-bit companions for chunk classification near the centre: every
+        // point with |f - fc| < hw0in has |x| < XLIM0, every point with |f - fc| > hw1
+        // has |x| >= XLIM1 (so chunks between them are pure Humlicek region 1).
+        double h0in = floor((double)r.xlim0/step) - 2.;
+        double h1 = ceil((double)r.xlim1/step) + 2.;
+        if (!(h0in >= 0.)) h0in = 0.;
+        if (!(h0in <= 65535.)) h0in = 65535.;
+        if (!(h1 >= 0.)) h1 = 65535.;
+        if (!(h1 <= 65535.)) h1 = 65535.;
+        r.hw1_hw0in = (unsigned)h1 | ((unsigned)h0in << 16);
         if (y >= kLorentzY)
         {
             r.hw0 = kHwLorentz;
@@ -431,10 +442,10 @@ static int finalize_lines(grt_gas *g)
 // of records whose window can reach it (binary searches in the sorted centres, with the
 // pressure-shift margin) and the tiles ordered by that count, heaviest first, so that
 // the dynamic scheduler ends with the cheap tiles (longest-processing-time-first).
-static int prepare_tiles(grt_gas *g, int pts, double margin)
+static int prepare_tiles(grt_gas *g, int pts, double margin, double shift)
 {
     if (g->tiles_pts == pts && g->tiles_margin >= margin && g->d_tile_order != nullptr) return 0;
-    margin *= 1.25;   // head-room so that a slightly larger surface pressure does not rebuild
+    margin += 0.25*shift;   // head-room so that a slightly larger surface pressure does not rebuild
     int const tile = 32*pts;
     int const num_tiles = (int)((g->nw + tile - 1)/tile);
     std::vector<double> const &v0 = g->h_sorted_v0;
@@ -766,7 +777,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     if (pts != 2 && pts != 4 && pts != 8) pts = 4;
     if (nl != 1 && nl != 2 && nl != 4) nl = 1;
     if (pts == 8 && nl == 4) nl = 2;
-    GRT_TRY(prepare_tiles(g, pts, margin));
+    GRT_TRY(prepare_tiles(g, pts, margin, g->max_abs_delta*pmax));
     sp.num_tiles = g->num_tiles;
     sp.tile_order = g->d_tile_order;
     sp.tile_first = g->d_tile_first;

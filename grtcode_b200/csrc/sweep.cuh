@@ -90,20 +90,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t const mbar, uint32_t const pa
 }
 
 
-// 1/d for d > 0 to ~1 ulp without the IEEE division slow path: float seed + two
-// Newton steps in double.  Only used where the result feeds the double accumulator
-// (pure-Lorentz branch), never before a float rounding.  d_f > 0 is a normal float.
+// 1/d for d > 0 to 2^-45 relative without the IEEE division: float seed (2^-23) + one
+// Newton step in double.  Only used where the result feeds the double accumulator
+// (pure-Lorentz branch; the parity tolerance on tau is 1e-9), never before a float
+// rounding.  d_f > 0 is a normal float.
 __device__ __forceinline__ double fast_rcp_of_float(float const d_f)
 {
     float r0;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(d_f));
     double const d = widen_positive(d_f);
-    double r = widen_positive(r0);
-    double e = fma(-d, r, 1.0);
-    r = fma(r, e, r);
-    e = fma(-d, r, 1.0);
-    r = fma(r, e, r);
-    return r;
+    double const r = widen_positive(r0);
+    double const e = fma(-d, r, 1.0);
+    return fma(r, e, r);
 }
 
 
@@ -123,128 +121,226 @@ __device__ __forceinline__ float abscissa_from(double const t2, double const v, 
     return __double2float_rn(__dmul_rn(__dsub_rn(t2, v), repwid));
 }
 
-
-// One line of one layer against the warp's 32*PTS points.
+// What the warp knows about its work item while it walks the lines.
 template <int PTS>
-__device__ __forceinline__ void accumulate_line(LineRec const *rec, SweepParams const &p,
-                                                int const warp_base, int const lane,
-                                                GridCache<PTS> &gc, double (&acc)[PTS])
+struct TileCtx
 {
-    // hot part of the record: three broadcast loads
-    double2 const vc = *reinterpret_cast<double2 const *>(&rec->v);
-    float4 const q = *reinterpret_cast<float4 const *>(&rec->repwid);
-    int4 const fh = *reinterpret_cast<int4 const *>(&rec->fc);   // fc, hw0, y, xlim0
-    int const fc = fh.x;
-    int const hw0 = fh.y;
-    int const warp_last = warp_base + 32*PTS - 1;
-    int const F = p.fsteps;
-    if (fc == kSkip || fc + F < warp_base || fc - F > warp_last || hw0 == kHwCoreOnly) return;
-    double const v = vc.x;
-    double const c = vc.y;
-    double const repwid = __hiloint2double(__float_as_int(q.y), __float_as_int(q.x));
-    float const yq = q.z;
-    float const yrrtpi = q.w;
-    int const s = max(fc - F, 0);
-    int const e = min(fc + F, p.nw - 1);
+    int warp_base;
+    int warp_last;
+    int lane;
+    int fsteps;
+    int nw;
+    double w0;
+    double wres;
+    double lane_pt;            // (double)(warp_base + lane)
+};
+
+// (double)k for 0 <= k < 2^31 on the FP64 pipe instead of the conversion unit.
+__device__ __forceinline__ double int_to_double(int const k)
+{
+    return __dsub_rn(__hiloint2double(0x43300000, k), 4503599627370496.0);
+}
+
+template <int PTS>
+__device__ __forceinline__ void refresh_grid(GridCache<PTS> &gc, TileCtx<PTS> const &t, int const s)
+{
     if (s != gc.s)
     {
         gc.s = s;
-        double const dwno = __dadd_rn(__dmul_rn((double)s, p.wres), p.w0);
-        double const i0 = (double)(warp_base + lane - s);
+        double const sd = int_to_double(s);
+        double const dwno = __dadd_rn(__dmul_rn(sd, t.wres), t.w0);
+        double const i0 = __dsub_rn(t.lane_pt, sd);     // exact
 #pragma unroll
         for (int j=0; j<PTS; ++j)
         {
-            gc.t2[j] = __dadd_rn(dwno, __dmul_rn(i0 + (double)(32*j), p.wres));
+            gc.t2[j] = __dadd_rn(dwno, __dmul_rn(i0 + (double)(32*j), t.wres));
         }
     }
-    bool const covered = (s <= warp_base) && (e >= warp_last);
-    bool const far = (hw0 >= 0) && ((warp_base - fc > hw0) || (fc - warp_last > hw0));
-    if (far)
+}
+
+// Line classes of the gather, decided once per (line, tile) by the lane that owns the
+// line in the staged batch.
+enum LineClass { kClsNone = 0, kClsFast, kClsFarEdge, kClsNear, kClsLorentzFull, kClsLorentzEdge };
+
+__device__ __forceinline__ double far_wing(double const t2, double2 const A, double const repwid,
+                                           float const yq, float const yrrtpi)
+{
+    float const xi = abscissa_from(t2, A.x, repwid);
+    return widen_positive(div_exact(yrrtpi, xi*xi + yq));
+}
+
+// kClsFast: the tile lies wholly inside the line's window and wholly in its far wing:
+// no predicates, PTS independent dependency chains in flight.
+template <int PTS>
+__device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileCtx<PTS> const &t,
+                                          GridCache<PTS> &gc, double (&acc)[PTS])
+{
+    refresh_grid<PTS>(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
+    double const repwid = widen_positive(B.x);
+#pragma unroll
+    for (int j=0; j<PTS; ++j)
     {
-        if (covered)
-        {
-            // Every lane of every chunk is a far-wing sample: no predicates, PTS
-            // independent dependency chains in flight.
-#pragma unroll
-            for (int j=0; j<PTS; ++j)
-            {
-                float const xi = abscissa_from(gc.t2[j], v, repwid);
-                float const kf = div_exact(yrrtpi, xi*xi + yq);
-                acc[j] = fma(c, widen_positive(kf), acc[j]);
-            }
-        }
-        else
-        {
-            // A window end falls inside the tile (kernels.c:435-437).
-#pragma unroll
-            for (int j=0; j<PTS; ++j)
-            {
-                int const cb = warp_base + j*32;
-                if (cb <= e && cb + 31 >= s)
-                {
-                    int const f = cb + lane;
-                    float const xi = abscissa_from(gc.t2[j], v, repwid);
-                    float const kf = div_exact(yrrtpi, xi*xi + yq);
-                    if (f >= s && f <= e) acc[j] = fma(c, widen_positive(kf), acc[j]);
-                }
-            }
-        }
+        acc[j] = fma(A.y, far_wing(gc.t2[j], A, repwid, B.y, B.z), acc[j]);
     }
-    else if (hw0 == kHwLorentz)
+}
+
+// Pure-Lorentz lines (Y >= 70.55, RFM_voigt.c:97-106).  FULL: the window covers the tile.
+template <int PTS, bool FULL>
+__device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
+                                             TileCtx<PTS> const &t, GridCache<PTS> &gc,
+                                             double (&acc)[PTS])
+{
+    int const fc = __float_as_int(B.w);
+    int const s = max(fc - t.fsteps, 0);
+    int const e = min(fc + t.fsteps, t.nw - 1);
+    refresh_grid<PTS>(gc, t, s);
+    double const repwid = widen_positive(B.x);
+    int const f0 = t.warp_base + t.lane;
+#pragma unroll
+    for (int j=0; j<PTS; ++j)
     {
+        int const f = f0 + 32*j;
+        float const xi = abscissa_from(gc.t2[j], A.x, repwid);
+        double const k = fast_rcp_of_float(xi*xi + B.y);
+        if (FULL || ((f >= s) && (f <= e))) acc[j] = fma(A.y, k, acc[j]);
+    }
+}
+
+
+// kClsFarEdge: far wing only, but a window end falls inside the tile
+// (kernels.c:435-437).  kClsNear: the tile overlaps the line's |x| < XLIM0 core, so lanes
+// may hold far-wing, Humlicek region-1 (RFM_voigt.c:172-183) or line-core samples (the
+// latter are skipped here and left to core_sweep_kernel).  Both are branch-free over the
+// PTS chunks -- every lane evaluates the candidate formulas and selects -- so that PTS
+// independent dependency chains stay in flight; the per-lane float comparisons are the
+// reference's own (RFM_voigt.c:166,172).
+template <int PTS, bool NEAR>
+__device__ __forceinline__ void line_general(LineRec const *rec, TileCtx<PTS> const &t,
+                                             GridCache<PTS> &gc, double (&acc)[PTS])
+{
+    double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
+    float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
+    int const fc = __float_as_int(B.w);
+    int const s = max(fc - t.fsteps, 0);
+    int const e = min(fc + t.fsteps, t.nw - 1);
+    refresh_grid<PTS>(gc, t, s);
+    double const repwid = widen_positive(B.x);
+    float const yq = B.y;
+    float const yrrtpi = B.z;
+    int const f0 = t.warp_base + t.lane;
+    if (NEAR)
+    {
+        float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
+        float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, -
 #pragma unroll
         for (int j=0; j<PTS; ++j)
         {
-            int const cb = warp_base + j*32;
-            if (cb <= e && cb + 31 >= s)
-            {
-                int const f = cb + lane;
-                float const xi = abscissa_from(gc.t2[j], v, repwid);
-                double const r = fast_rcp_of_float(xi*xi + yq);
-                if (f >= s && f <= e) acc[j] = fma(c, r, acc[j]);
-            }
+            int const f = f0 + 32*j;
+            float const xi = abscissa_from(gc.t2[j], A.x, repwid);
+            float const ax = fabsf(xi);
+            float const xq = ax*ax;
+            bool const isfar = ax >= C.z;
+            bool const isr1 = !isfar && (ax >= C.w);
+            float const kfar = div_exact(yrrtpi, xq + yq);
+            float const kr1 = voigt_region1(xq, C.y, D.x, D.y, D.z);
+            float const kf = isr1 ? kr1 : kfar;
+            if ((f >= s) && (f <= e) && (isfar || isr1)) acc[j] = fma(A.y, widen_positive(kf), acc[j]);
         }
     }
     else
     {
-        // The tile is near the line centre: chunks may hold far-wing, region-1 and
-        // line-core samples (the latter are skipped here).
-        float4 const a = *reinterpret_cast<float4 const *>(&rec->xlim1);   // xlim1, a0, d0, d2
-        float const y = __int_as_float(fh.z);
-        float const xlim0 = __int_as_float(fh.w);
-        float const xlim1 = a.x;
-        float const a0 = a.y;
-        float2 const d = make_float2(a.z, a.w);
 #pragma unroll
         for (int j=0; j<PTS; ++j)
         {
-            int const cb = warp_base + j*32;
-            if (cb <= e && cb + 31 >= s)
+            int const f = f0 + 32*j;
+            double const k = far_wing(gc.t2[j], A, repwid, yq, yrrtpi);
+            if ((f >= s) && (f <= e)) acc[j] = fma(A.y, k, acc[j]);
+        }
+    }
+}
+
+
+// One staged batch (cnt <= 32 records of one layer) against the warp's tile.  Lane b
+// classifies record b; the classes are then walked as bit masks, the dominant one
+// (kClsFast) with the next record's vectors prefetched while the current one computes.
+template <int PTS>
+__device__ __forceinline__ void process_batch(LineRec const *stage, int const cnt,
+                                              TileCtx<PTS> const &t, GridCache<PTS> &gc,
+                                              double (&acc)[PTS])
+{
+    int cls = kClsNone;
+    if (t.lane < cnt)
+    {
+        int const fc = stage[t.lane].fc;
+        int const hw0 = stage[t.lane].hw0;
+        bool const hit = (fc != kSkip) && (fc + t.fsteps >= t.warp_base) &&
+                         (fc - t.fsteps <= t.warp_last) && (hw0 != kHwCoreOnly);
+        if (hit)
+        {
+            int const s = max(fc - t.fsteps, 0);
+            int const e = min(fc + t.fsteps, t.nw - 1);
+            bool const covered = (s <= t.warp_base) && (e >= t.warp_last);
+            bool const far = (hw0 >= 0) && ((t.warp_base - fc > hw0) || (fc - t.warp_last > hw0));
+            if (hw0 == kHwLorentz)
             {
-                int const f = cb + lane;
-                float const xi = abscissa_from(gc.t2[j], v, repwid);
-                float const ax = fabsf(xi);
-                float const xq = ax*ax;
-                bool const in = (f >= s) && (f <= e);
-                bool const isfar = ax >= xlim0;
-                bool const isr1 = !isfar && (ax >= xlim1);
-                float kf;
-                if (__all_sync(0xffffffffu, isfar || !in))
-                {
-                    kf = div_exact(yrrtpi, xq + yq);
-                }
-                else if (__all_sync(0xffffffffu, isr1 || !in))
-                {
-                    kf = voigt_region1(xq, y, a0, d.x, d.y);
-                }
-                else
-                {
-                    kf = div_exact(yrrtpi, xq + yq);
-                    if (isr1) kf = voigt_region1(xq, y, a0, d.x, d.y);
-                }
-                if (in && (isfar || isr1)) acc[j] = fma(c, widen_positive(kf), acc[j]);
+                cls = covered ? kClsLorentzFull : kClsLorentzEdge;
+            }
+            else
+            {
+                cls = far ? (covered ? kClsFast : kClsFarEdge) : kClsNear;
             }
         }
+    }
+    unsigned m = __ballot_sync(0xffffffffu, cls == kClsFast);
+    if (m)
+    {
+        int b = __ffs(m) - 1;
+        m &= m - 1;
+        double2 A = *reinterpret_cast<double2 const *>(&stage[b].v);
+        float4 B = *reinterpret_cast<float4 const *>(&stage[b].repwid);
+        for (;;)
+        {
+            bool const more = m != 0;
+            int const bn = more ? __ffs(m) - 1 : b;
+            m &= m - 1;
+            double2 const An = *reinterpret_cast<double2 const *>(&stage[bn].v);
+            float4 const Bn = *reinterpret_cast<float4 const *>(&stage[bn].repwid);
+            line_fast<PTS>(A, B, t, gc, acc);
+            if (!more) break;
+            A = An;
+            B = Bn;
+            b = bn;
+        }
+    }
+    m = __ballot_sync(0xffffffffu, cls == kClsFarEdge);
+    while (m)
+    {
+        int const b = __ffs(m) - 1;
+        m &= m - 1;
+        line_general<PTS, false>(stage + b, t, gc, acc);
+    }
+    m = __ballot_sync(0xffffffffu, cls == kClsNear);
+    while (m)
+    {
+        int const b = __ffs(m) - 1;
+        m &= m - 1;
+        line_general<PTS, true>(stage + b, t, gc, acc);
+    }
+    m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull);
+    while (m)
+    {
+        int const b = __ffs(m) - 1;
+        m &= m - 1;
+        line_lorentz<PTS, true>(*reinterpret_cast<double2 const *>(&stage[b].v),
+                                *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc, acc);
+    }
+    m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge);
+    while (m)
+    {
+        int const b = __ffs(m) - 1;
+        m &= m - 1;
+        line_lorentz<PTS, false>(*reinterpret_cast<double2 const *>(&stage[b].v),
+                                 *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc, acc);
     }
 }
 
@@ -314,6 +410,15 @@ wing_sweep_kernel(SweepParams const p)
 #pragma unroll
             for (int j=0; j<PTS; ++j) acc[l][j] = 0.;
         }
+        TileCtx<PTS> tc;
+        tc.warp_base = warp_base;
+        tc.warp_last = warp_base + 32*PTS - 1;
+        tc.lane = lane;
+        tc.fsteps = p.fsteps;
+        tc.nw = p.nw;
+        tc.w0 = p.w0;
+        tc.wres = p.wres;
+        tc.lane_pt = (double)(warp_base + lane);
         GridCache<PTS> gc;
         gc.s = INT32_MIN;
 #pragma unroll
@@ -343,13 +448,10 @@ wing_sweep_kernel(SweepParams const p)
             phase ^= 1u << st;
             int const cnt = (int)min(32u, last - (first + 32u*(unsigned)k));
             LineRec const *stage = reinterpret_cast<LineRec const *>(ring + st*Cfg::kStageBytes);
-            for (int b=0; b<cnt; ++b)
-            {
 #pragma unroll
-                for (int l=0; l<NL; ++l)
-                {
-                    if (l < nl) accumulate_line<PTS>(stage + l*32 + b, p, warp_base, lane, gc, acc[l]);
-                }
+            for (int l=0; l<NL; ++l)
+            {
+                if (l < nl) process_batch<PTS>(stage + l*32, cnt, tc, gc, acc[l]);
             }
             __syncwarp();
             if (lane == 0 && k + 2 < nb)
@@ -417,17 +519,18 @@ core_sweep_kernel(SweepParams const p)
     int const layer = blockIdx.y;
     if (rec_id >= p.num_lines) return;
     LineRec const *rp = p.recs + (size_t)layer*p.num_lines + rec_id;
-    int4 const fh = *reinterpret_cast<int4 const *>(&rp->fc);   // fc, hw0, y, xlim0
-    int const fc = fh.x;
-    int const hw0 = fh.y;
+    float4 const B = *reinterpret_cast<float4 const *>(&rp->repwid);   // repwid, yq, yrrtpi, fc
+    float4 const C = *reinterpret_cast<float4 const *>(&rp->hw0);      // hw0, y, xlim0, xlim1
+    int const fc = __float_as_int(B.w);
+    int const hw0 = __float_as_int(C.x);
     if (fc == kSkip || hw0 == kHwLorentz) return;
-    float const y = __int_as_float(fh.z);
-    float const xlim0 = __int_as_float(fh.w);
-    float const xlim1 = rp->xlim1;
+    float const y = C.y;
+    float const xlim0 = C.z;
+    float const xlim1 = C.w;
     bool const flagged = hw0 == kHwCoreOnly;
     if (!flagged && xlim1 <= 0.f) return;
     double2 const vc = *reinterpret_cast<double2 const *>(&rp->v);
-    double const repwid = rp->repwid;
+    double const repwid = (double)B.x;
     int const F = p.fsteps;
     int const s = max(fc - F, 0);
     int const e = min(fc + F, p.nw - 1);

@@ -4,8 +4,8 @@ mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
 tail -4 gpurun_out/pytest_gpu.log
-for v in "8 1" "8 2" "4 2" "4 4"; do
-  set -- $v
+for v in ${GRT_VARIANTS:-8:1 8:2 4:1}; do
+  set -- ${v/:/ }
   GRT_SWEEP_PTS=$1 GRT_SWEEP_NL=$2 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/bench_pts$1_nl$2.log 2>&1
   echo "PTS=$1 NL=$2 exit $?"
   grep '^{' gpurun_out/bench_pts$1_nl$2.log | python -c "
@@ -15,7 +15,7 @@ for l in sys.stdin:
     print('  ms/step %.1f value %.3e samples/s %.3e shares %s' % (d['ms_per_step'], d['value'], r['samples_per_s'], r['kernel_share_of_step']))
 "
 done
-GRT_SWEEP_PTS=4 GRT_SWEEP_NL=1 timeout 300 python tools/profile_c1.py 2>&1 | tail -1
-GRT_SWEEP_PTS=4 GRT_SWEEP_NL=2 timeout 300 python tools/profile_c1.py 2>&1 | tail -1
-GRT_SWEEP_PTS=4 GRT_SWEEP_NL=4 timeout 300 python tools/profile_c1.py 2>&1 | tail -1
-GRT_SWEEP_PTS=2 GRT_SWEEP_NL=4 timeout 300 python tools/profile_c1.py 2>&1 | tail -1
+for v in ${GRT_C1_VARIANTS:-4:1 2:1}; do
+  set -- ${v/:/ }
+  GRT_SWEEP_PTS=$1 GRT_SWEEP_NL=$2 timeout 300 python tools/profile_c1.py 2>&1 | tail -1
+done
