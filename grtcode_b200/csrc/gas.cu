@@ -804,16 +804,8 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     GRT_CUDA(cudaEventRecord(g->ev[2], st));
     if (N > 0)
     {
-        if (g->dw < 0.05)
-        {
-            dim3 grid((unsigned)((N*32 + 255)/256), (unsigned)L);
-            core_sweep_kernel<32><<<grid, 256, 0, st>>>(sp);
-        }
-        else
-        {
-            dim3 grid((unsigned)((N*8 + 255)/256), (unsigned)L);
-            core_sweep_kernel<8><<<grid, 256, 0, st>>>(sp);
-        }
+        dim3 grid((unsigned)((N + 127)/128), (unsigned)L);
+        core_sweep_kernel<<<grid, 128, 0, st>>>(sp);
         ++launches;
     }
     GRT_CUDA(cudaEventRecord(g->ev[3], st));

@@ -507,15 +507,16 @@ wing_sweep_kernel(SweepParams const p)
 
 
 // K3c: samples with |x| < XLIM1 (Humlicek regions 2, 3 and CPF12) of every Voigt-branch
-// record, plus every sample of the rare records flagged kHwCoreOnly.  G lanes share
-// one record and stride over its near-centre window; contributions are scattered with
-// double atomics.
-template <int G>
-__global__ void __launch_bounds__(256)
+// record, plus every sample of the rare records flagged kHwCoreOnly.  One thread per
+// record walks outwards from the line centre (fc, fc-1, fc+1, ...): the records of a warp
+// are neighbours in the centre-sorted list, so at the same distance their |x| -- and
+// with it the branch of RFM_voigt.c:172-277 they take -- mostly agree and the warp stays
+// converged inside the expensive CPF12 sums.  Contributions are scattered with double
+// atomics (a few per cent of all samples).
+__global__ void __launch_bounds__(128)
 core_sweep_kernel(SweepParams const p)
 {
-    uint64_t const rec_id = ((uint64_t)blockIdx.x*blockDim.x + threadIdx.x)/G;
-    int const sub = threadIdx.x & (G - 1);
+    uint64_t const rec_id = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     int const layer = blockIdx.y;
     if (rec_id >= p.num_lines) return;
     LineRec const *rp = p.recs + (size_t)layer*p.num_lines + rec_id;
@@ -537,17 +538,21 @@ core_sweep_kernel(SweepParams const p)
     // Half-width of the |x| < xlim1 window in grid points, rounded up generously.
     double const hd = flagged ? (double)(2*F + 2) : (double)xlim1/(repwid*p.wres) + 2.;
     int const h = hd < (double)(2*F + 2) ? (int)hd : 2*F + 2;
-    int const lo = max(fc - h, s);
-    int const hi = min(fc + h, e);
     double const dwno = __dadd_rn(__dmul_rn((double)s, p.wres), p.w0);
     double *tau = p.tau + (size_t)layer*p.nw;
-    for (int f=lo+sub; f<=hi; f+=G)
+    for (int d=0; d<=h; ++d)
     {
-        float const xi = abscissa(dwno, (double)(f - s), p.wres, vc.x, repwid);
-        if (flagged || fabsf(xi) < xlim1)
+#pragma unroll
+        for (int side=0; side<2; ++side)
         {
-            double const k = voigt_core(xi, y, xlim0, xlim1);
-            atomicAdd(&tau[f], vc.y*k);
+            int const f = side ? fc + d : fc - d;
+            if ((side == 1 && d == 0) || f < s || f > e) continue;
+            float const xi = abscissa(dwno, (double)(f - s), p.wres, vc.x, repwid);
+            if (flagged || fabsf(xi) < xlim1)
+            {
+                double const k = voigt_core(xi, y, xlim0, xlim1);
+                atomicAdd(&tau[f], vc.y*k);
+            }
         }
     }
 }
