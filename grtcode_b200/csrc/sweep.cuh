@@ -351,7 +351,7 @@ struct SweepConfig
     static constexpr int kStageBytes = NL*32*(int)sizeof(LineRec);
     static constexpr int kSmemBytes = kSweepWarps*2*kStageBytes + kSweepWarps*2*8;
     // registers: PTS*NL accumulators + PTS cached abscissae, all double
-    static constexpr int kMinBlocks = (PTS*NL <= 8) ? 2 : 1;
+    static constexpr int kMinBlocks = (PTS*NL <= 4) ? 3 : ((PTS*NL <= 8) ? 2 : 1);
 };
 
 
