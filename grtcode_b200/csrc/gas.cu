@@ -484,27 +484,41 @@ static int prepare_tiles(grt_gas *g, int pts, double margin, double shift)
 }
 
 // Persistent CTAs: one wave that fills every SM; work items are pulled from the counter.
-template <int PTS, int NL>
-static int launch_wing(SweepParams const &sp, int const sms, cudaStream_t const st)
+// TBL kernels carry the fl(i*wres) table behind the record rings in shared memory.
+constexpr int kMaxTableBytes = 64*1024;
+
+template <int PTS, int NL, bool TBL>
+static int launch_wing_impl(SweepParams const &sp, int const sms, cudaStream_t const st)
 {
     using Cfg = SweepConfig<PTS, NL>;
     static bool configured = false;
     if (!configured)
     {
-        GRT_CUDA(cudaFuncSetAttribute(wing_sweep_kernel<PTS, NL>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+        GRT_CUDA(cudaFuncSetAttribute(wing_sweep_kernel<PTS, NL, TBL>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      Cfg::kRingBytes + (TBL ? kMaxTableBytes : 0)));
         configured = true;
     }
+    int const smem = Cfg::kRingBytes + (TBL ? 8*sweep_table_entries<PTS>(sp.fsteps) : 0);
     int per_sm = 0;
-    GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<PTS, NL>,
-                                                           kSweepThreads, Cfg::kSmemBytes));
+    GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<PTS, NL, TBL>,
+                                                           kSweepThreads, smem));
     int const groups = (sp.num_layers + NL - 1)/NL;
     unsigned const total = (unsigned)sp.num_tiles*(unsigned)groups;
     unsigned const grid = std::min<unsigned>((total + kSweepWarps - 1)/kSweepWarps,
                                              (unsigned)(sms*std::max(per_sm, 1)));
-    wing_sweep_kernel<PTS, NL><<<std::max(grid, 1u), kSweepThreads, Cfg::kSmemBytes, st>>>(sp);
+    wing_sweep_kernel<PTS, NL, TBL><<<std::max(grid, 1u), kSweepThreads, smem, st>>>(sp);
     GRT_CUDA(cudaGetLastError());
     return 0;
+}
+
+template <int PTS, int NL>
+static int launch_wing(SweepParams const &sp, int const sms, cudaStream_t const st)
+{
+    bool table = 8*sweep_table_entries<PTS>(sp.fsteps) <= kMaxTableBytes;
+    if (char const *env = getenv("GRT_SWEEP_TABLE")) table = table && atoi(env) != 0;
+    return table ? launch_wing_impl<PTS, NL, true>(sp, sms, st)
+                 : launch_wing_impl<PTS, NL, false>(sp, sms, st);
 }
 
 extern "C" {
@@ -775,8 +789,8 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     if (char const *env = getenv("GRT_SWEEP_PTS")) pts = atoi(env);
     if (char const *env = getenv("GRT_SWEEP_NL")) nl = atoi(env);
     if (pts != 2 && pts != 4 && pts != 8) pts = 4;
-    if (nl != 1 && nl != 2 && nl != 4) nl = 1;
-    if (pts == 8 && nl == 4) nl = 2;
+    if (nl != 1 && nl != 2) nl = 1;
+    if (pts == 2) nl = 1;
     GRT_TRY(prepare_tiles(g, pts, margin, g->max_abs_delta*pmax));
     sp.num_tiles = g->num_tiles;
     sp.tile_order = g->d_tile_order;
@@ -790,11 +804,8 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
         switch (pts*10 + nl)
         {
             case 21: rc = launch_wing<2, 1>(sp, sms, st); break;
-            case 22: rc = launch_wing<2, 2>(sp, sms, st); break;
-            case 24: rc = launch_wing<2, 4>(sp, sms, st); break;
             case 41: rc = launch_wing<4, 1>(sp, sms, st); break;
             case 42: rc = launch_wing<4, 2>(sp, sms, st); break;
-            case 44: rc = launch_wing<4, 4>(sp, sms, st); break;
             case 81: rc = launch_wing<8, 1>(sp, sms, st); break;
             default: rc = launch_wing<8, 2>(sp, sms, st); break;
         }

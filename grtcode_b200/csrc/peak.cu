@@ -95,6 +95,18 @@ __global__ void selftest_kernel(unsigned long long n, unsigned long long seed,
         float const q2 = __fdiv_rn(a, b);
         if (__float_as_uint(q1) != __float_as_uint(q2)) ++local;
         if (widen_positive(q2) != (double)q2) ++local;
+        // the packed (FFMA2) sequence, the second half fed with the swapped-mantissa pair
+        float const a2 = __uint_as_float(((64u + hi%70u) << 23) | (lo & 0x7fffffu));
+        float const b2 = __uint_as_float(((127u + (hi >> 8)%54u) << 23) | ((lo >> 9) & 0x7fffffu));
+        float p1, p2;
+        unpack2(div_exact2(pack2(a, a2), pack2(b, b2)), p1, p2);
+        if (__float_as_uint(p1) != __float_as_uint(q2)) ++local;
+        if (__float_as_uint(p2) != __float_as_uint(__fdiv_rn(a2, b2))) ++local;
+        // x*x + yq must round twice (RFM_voigt.c:166,170): the packed add of scalar products
+        float s1, s2;
+        unpack2(add2(mul2_unfused(pack2(a, a2), pack2(a, a2)), pack2(b, b2)), s1, s2);
+        if (__float_as_uint(s1) != __float_as_uint(__fadd_rn(__fmul_rn(a, a), b))) ++local;
+        if (__float_as_uint(s2) != __float_as_uint(__fadd_rn(__fmul_rn(a2, a2), b2))) ++local;
     }
     if (local) atomicAdd(bad, local);
 }

@@ -122,7 +122,6 @@ __device__ __forceinline__ float abscissa_from(double const t2, double const v, 
 }
 
 // What the warp knows about its work item while it walks the lines.
-template <int PTS>
 struct TileCtx
 {
     int warp_base;
@@ -133,6 +132,7 @@ struct TileCtx
     double w0;
     double wres;
     double lane_pt;            // (double)(warp_base + lane)
+    uint32_t iw_lane;          // shared-memory address of iw[warp_base + lane] (TBL kernels)
 };
 
 // (double)k for 0 <= k < 2^31 on the FP64 pipe instead of the conversion unit.
@@ -141,59 +141,128 @@ __device__ __forceinline__ double int_to_double(int const k)
     return __dsub_rn(__hiloint2double(0x43300000, k), 4503599627370496.0);
 }
 
-template <int PTS>
-__device__ __forceinline__ void refresh_grid(GridCache<PTS> &gc, TileCtx<PTS> const &t, int const s)
+__device__ __forceinline__ double lds_f64(uint32_t const addr)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+
+// TBL: fl(i*wres) comes from the block's shared-memory table iw[] (i = f - s is a small
+// integer: 0 <= i <= 2*fsteps inside a window), so a refresh is one LDS + one DADD per
+// point instead of three FP64 operations.
+template <int PTS, bool TBL>
+__device__ __forceinline__ void refresh_grid(GridCache<PTS> &gc, TileCtx const &t, int const s)
 {
     if (s != gc.s)
     {
         gc.s = s;
         double const sd = int_to_double(s);
         double const dwno = __dadd_rn(__dmul_rn(sd, t.wres), t.w0);
-        double const i0 = __dsub_rn(t.lane_pt, sd);     // exact
-#pragma unroll
-        for (int j=0; j<PTS; ++j)
+        if (TBL)
         {
-            gc.t2[j] = __dadd_rn(dwno, __dmul_rn(i0 + (double)(32*j), t.wres));
+            uint32_t const a = t.iw_lane - 8u*(uint32_t)s;
+#pragma unroll
+            for (int j=0; j<PTS; ++j) gc.t2[j] = __dadd_rn(dwno, lds_f64(a + 256u*(uint32_t)j));
+        }
+        else
+        {
+            double const i0 = __dsub_rn(t.lane_pt, sd);     // exact
+#pragma unroll
+            for (int j=0; j<PTS; ++j)
+            {
+                gc.t2[j] = __dadd_rn(dwno, __dmul_rn(i0 + (double)(32*j), t.wres));
+            }
         }
     }
 }
 
 // Line classes of the gather, decided once per (line, tile) by the lane that owns the
 // line in the staged batch.
-enum LineClass { kClsNone = 0, kClsFast, kClsFarEdge, kClsNear, kClsLorentzFull, kClsLorentzEdge };
+enum LineClass { kClsNone = 0, kClsFast, kClsFarEdge, kClsR1, kClsNear, kClsLorentzFull,
+                 kClsLorentzEdge };
 
-__device__ __forceinline__ double far_wing(double const t2, double2 const A, double const repwid,
-                                           float const yq, float const yrrtpi)
+__device__ __forceinline__ f32x2 abscissa2(double const t2a, double const t2b, double const v,
+                                           double const repwid)
 {
-    float const xi = abscissa_from(t2, A.x, repwid);
-    return widen_positive(div_exact(yrrtpi, xi*xi + yq));
+    return pack2(abscissa_from(t2a, v, repwid), abscissa_from(t2b, v, repwid));
+}
+
+// Far wing K = YRRTPI/(XQ + YQ) (RFM_voigt.c:168-171) for two samples.
+__device__ __forceinline__ f32x2 far_wing2(f32x2 const xq, f32x2 const yq2, f32x2 const yr2)
+{
+    return div_exact2(yr2, add2(xq, yq2));
+}
+
+// Humlicek region 1 (RFM_voigt.c:172-183) for two samples, per-line constants hoisted.
+__device__ __forceinline__ f32x2 region1_2(f32x2 const xq, f32x2 const y2, f32x2 const a0,
+                                           f32x2 const d0, f32x2 const d2)
+{
+    f32x2 const den = add2(d0, mul2_unfused(xq, add2(d2, xq)));
+    f32x2 const D = div_exact2(pack2(kRsqrpi, kRsqrpi), den);
+    return mul2(mul2(D, y2), add2(a0, xq));
+}
+
+__device__ __forceinline__ void accumulate2(double &a0, double &a1, double const c, f32x2 const k)
+{
+    float k0, k1;
+    unpack2(k, k0, k1);
+    a0 = fma(c, widen_positive(k0), a0);
+    a1 = fma(c, widen_positive(k1), a1);
 }
 
 // kClsFast: the tile lies wholly inside the line's window and wholly in its far wing:
-// no predicates, PTS independent dependency chains in flight.
-template <int PTS>
-__device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileCtx<PTS> const &t,
+// no predicates, PTS independent dependency chains in flight, two samples per packed op.
+template <int PTS, bool TBL>
+__device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileCtx const &t,
                                           GridCache<PTS> &gc, double (&acc)[PTS])
 {
-    refresh_grid<PTS>(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
+    refresh_grid<PTS, TBL>(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
     double const repwid = widen_positive(B.x);
+    f32x2 const yq2 = pack2(B.y, B.y);
+    f32x2 const yr2 = pack2(B.z, B.z);
 #pragma unroll
-    for (int j=0; j<PTS; ++j)
+    for (int j=0; j<PTS; j+=2)
     {
-        acc[j] = fma(A.y, far_wing(gc.t2[j], A, repwid, B.y, B.z), acc[j]);
+        f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
+        accumulate2(acc[j], acc[j+1], A.y, far_wing2(mul2_unfused(xi, xi), yq2, yr2));
+    }
+}
+
+// kClsR1: the tile lies wholly inside the window and every point has
+// XLIM1 <= |x| < XLIM0 (wide Doppler cores of the shortwave): region 1 only.
+template <int PTS, bool TBL>
+__device__ __forceinline__ void line_r1(LineRec const *rec, TileCtx const &t, GridCache<PTS> &gc,
+                                        double (&acc)[PTS])
+{
+    double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
+    float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
+    float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
+    float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, -
+    refresh_grid<PTS, TBL>(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
+    double const repwid = widen_positive(B.x);
+    f32x2 const y2 = pack2(C.y, C.y);
+    f32x2 const a0 = pack2(D.x, D.x);
+    f32x2 const d0 = pack2(D.y, D.y);
+    f32x2 const d2 = pack2(D.z, D.z);
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
+        accumulate2(acc[j], acc[j+1], A.y, region1_2(mul2_unfused(xi, xi), y2, a0, d0, d2));
     }
 }
 
 // Pure-Lorentz lines (Y >= 70.55, RFM_voigt.c:97-106).  FULL: the window covers the tile.
-template <int PTS, bool FULL>
+template <int PTS, bool TBL, bool FULL>
 __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
-                                             TileCtx<PTS> const &t, GridCache<PTS> &gc,
+                                             TileCtx const &t, GridCache<PTS> &gc,
                                              double (&acc)[PTS])
 {
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    refresh_grid<PTS>(gc, t, s);
+    refresh_grid<PTS, TBL>(gc, t, s);
     double const repwid = widen_positive(B.x);
     int const f0 = t.warp_base + t.lane;
 #pragma unroll
@@ -214,8 +283,8 @@ __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
 // PTS chunks -- every lane evaluates the candidate formulas and selects -- so that PTS
 // independent dependency chains stay in flight; the per-lane float comparisons are the
 // reference's own (RFM_voigt.c:166,172).
-template <int PTS, bool NEAR>
-__device__ __forceinline__ void line_general(LineRec const *rec, TileCtx<PTS> const &t,
+template <int PTS, bool TBL, bool NEAR>
+__device__ __forceinline__ void line_general(LineRec const *rec, TileCtx const &t,
                                              GridCache<PTS> &gc, double (&acc)[PTS])
 {
     double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
@@ -223,38 +292,67 @@ __device__ __forceinline__ void line_general(LineRec const *rec, TileCtx<PTS> co
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    refresh_grid<PTS>(gc, t, s);
+    refresh_grid<PTS, TBL>(gc, t, s);
     double const repwid = widen_positive(B.x);
-    float const yq = B.y;
-    float const yrrtpi = B.z;
+    f32x2 const yq2 = pack2(B.y, B.y);
+    f32x2 const yr2 = pack2(B.z, B.z);
     int const f0 = t.warp_base + t.lane;
     if (NEAR)
     {
         float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
         float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, -
+        f32x2 const y2 = pack2(C.y, C.y);
+        f32x2 const a0 = pack2(D.x, D.x);
+        f32x2 const d0 = pack2(D.y, D.y);
+        f32x2 const d2 = pack2(D.z, D.z);
 #pragma unroll
-        for (int j=0; j<PTS; ++j)
+        for (int j=0; j<PTS; j+=2)
         {
-            int const f = f0 + 32*j;
-            float const xi = abscissa_from(gc.t2[j], A.x, repwid);
-            float const ax = fabsf(xi);
-            float const xq = ax*ax;
-            bool const isfar = ax >= C.z;
-            bool const isr1 = !isfar && (ax >= C.w);
-            float const kfar = div_exact(yrrtpi, xq + yq);
-            float const kr1 = voigt_region1(xq, C.y, D.x, D.y, D.z);
-            float const kf = isr1 ? kr1 : kfar;
-            if ((f >= s) && (f <= e) && (isfar || isr1)) acc[j] = fma(A.y, widen_positive(kf), acc[j]);
+            f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
+            f32x2 const xq = mul2_unfused(xi, xi);
+            f32x2 const kfar = far_wing2(xq, yq2, yr2);
+            f32x2 const kr1 = region1_2(xq, y2, a0, d0, d2);
+            float x0, x1, kf0, kf1, kr0, kr1s;
+            unpack2(xi, x0, x1);
+            unpack2(kfar, kf0, kf1);
+            unpack2(kr1, kr0, kr1s);
+            {
+                int const f = f0 + 32*j;
+                float const ax = fabsf(x0);
+                bool const isfar = ax >= C.z;
+                bool const isr1 = !isfar && (ax >= C.w);
+                float const kf = isr1 ? kr0 : kf0;
+                if ((f >= s) && (f <= e) && (isfar || isr1))
+                {
+                    acc[j] = fma(A.y, widen_positive(kf), acc[j]);
+                }
+            }
+            {
+                int const f = f0 + 32*(j + 1);
+                float const ax = fabsf(x1);
+                bool const isfar = ax >= C.z;
+                bool const isr1 = !isfar && (ax >= C.w);
+                float const kf = isr1 ? kr1s : kf1;
+                if ((f >= s) && (f <= e) && (isfar || isr1))
+                {
+                    acc[j+1] = fma(A.y, widen_positive(kf), acc[j+1]);
+                }
+            }
         }
     }
     else
     {
 #pragma unroll
-        for (int j=0; j<PTS; ++j)
+        for (int j=0; j<PTS; j+=2)
         {
-            int const f = f0 + 32*j;
-            double const k = far_wing(gc.t2[j], A, repwid, yq, yrrtpi);
-            if ((f >= s) && (f <= e)) acc[j] = fma(A.y, k, acc[j]);
+            f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
+            f32x2 const k = far_wing2(mul2_unfused(xi, xi), yq2, yr2);
+            float k0, k1;
+            unpack2(k, k0, k1);
+            int const fa = f0 + 32*j;
+            int const fb = fa + 32;
+            if ((fa >= s) && (fa <= e)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
+            if ((fb >= s) && (fb <= e)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
         }
     }
 }
@@ -263,9 +361,9 @@ __device__ __forceinline__ void line_general(LineRec const *rec, TileCtx<PTS> co
 // One staged batch (cnt <= 32 records of one layer) against the warp's tile.  Lane b
 // classifies record b; the classes are then walked as bit masks, the dominant one
 // (kClsFast) with the next record's vectors prefetched while the current one computes.
-template <int PTS>
+template <int PTS, bool TBL>
 __device__ __forceinline__ void process_batch(LineRec const *stage, int const cnt,
-                                              TileCtx<PTS> const &t, GridCache<PTS> &gc,
+                                              TileCtx const &t, GridCache<PTS> &gc,
                                               double (&acc)[PTS])
 {
     int cls = kClsNone;
@@ -280,14 +378,25 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
             int const s = max(fc - t.fsteps, 0);
             int const e = min(fc + t.fsteps, t.nw - 1);
             bool const covered = (s <= t.warp_base) && (e >= t.warp_last);
-            bool const far = (hw0 >= 0) && ((t.warp_base - fc > hw0) || (fc - t.warp_last > hw0));
+            // nearest and farthest tile point from the line centre, in grid steps
+            int const dlo = max(max(t.warp_base - fc, fc - t.warp_last), 0);
+            int const dhi = max(fc - t.warp_base, t.warp_last - fc);
+            bool const far = (hw0 >= 0) && (dlo > hw0);
             if (hw0 == kHwLorentz)
             {
                 cls = covered ? kClsLorentzFull : kClsLorentzEdge;
             }
+            else if (far)
+            {
+                cls = covered ? kClsFast : kClsFarEdge;
+            }
             else
             {
-                cls = far ? (covered ? kClsFast : kClsFarEdge) : kClsNear;
+                unsigned const hh = stage[t.lane].hw1_hw0in;
+                int const hw1 = (int)(hh & 0xffffu);
+                int const hw0in = (int)(hh >> 16);
+                bool const r1 = covered && (dhi < hw0in) && (dlo > hw1) && (hw1 < 65535);
+                cls = r1 ? kClsR1 : kClsNear;
             }
         }
     }
@@ -305,42 +414,43 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
             m &= m - 1;
             double2 const An = *reinterpret_cast<double2 const *>(&stage[bn].v);
             float4 const Bn = *reinterpret_cast<float4 const *>(&stage[bn].repwid);
-            line_fast<PTS>(A, B, t, gc, acc);
+            line_fast<PTS, TBL>(A, B, t, gc, acc);
             if (!more) break;
             A = An;
             B = Bn;
             b = bn;
         }
     }
+    m = __ballot_sync(0xffffffffu, cls == kClsR1);
+    while (m)
+    {
+        int const b = __ffs(m) - 1;
+        m &= m - 1;
+        line_r1<PTS, TBL>(stage + b, t, gc, acc);
+    }
     m = __ballot_sync(0xffffffffu, cls == kClsFarEdge);
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
-        line_general<PTS, false>(stage + b, t, gc, acc);
+        line_general<PTS, TBL, false>(stage + b, t, gc, acc);
     }
     m = __ballot_sync(0xffffffffu, cls == kClsNear);
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
-        line_general<PTS, true>(stage + b, t, gc, acc);
+        line_general<PTS, TBL, true>(stage + b, t, gc, acc);
     }
-    m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull);
+    m = __ballot_sync(0xffffffffu, cls >= kClsLorentzFull);
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
-        line_lorentz<PTS, true>(*reinterpret_cast<double2 const *>(&stage[b].v),
-                                *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc, acc);
-    }
-    m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge);
-    while (m)
-    {
-        int const b = __ffs(m) - 1;
-        m &= m - 1;
-        line_lorentz<PTS, false>(*reinterpret_cast<double2 const *>(&stage[b].v),
-                                 *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc, acc);
+        // window ends inside the tile are predicated per point
+        line_lorentz<PTS, TBL, false>(*reinterpret_cast<double2 const *>(&stage[b].v),
+                                      *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc,
+                                      acc);
     }
 }
 
@@ -349,17 +459,25 @@ template <int PTS, int NL>
 struct SweepConfig
 {
     static constexpr int kStageBytes = NL*32*(int)sizeof(LineRec);
-    static constexpr int kSmemBytes = kSweepWarps*2*kStageBytes + kSweepWarps*2*8;
+    static constexpr int kRingBytes = kSweepWarps*2*kStageBytes + kSweepWarps*2*8;
+    static constexpr int kTablePad = 32*PTS;       // iw[] covers i in [-kTablePad, 2F + kTablePad]
     // registers: PTS*NL accumulators + PTS cached abscissae, all double
     static constexpr int kMinBlocks = (PTS*NL <= 4) ? 3 : ((PTS*NL <= 8) ? 2 : 1);
 };
 
+// Entries of the fl(i*wres) table for a kernel with tiles of 32*PTS points.
+template <int PTS>
+__host__ __device__ constexpr int sweep_table_entries(int const fsteps)
+{
+    return 2*fsteps + 2*32*PTS + 2;
+}
+
 
 // Warp-granular persistent gather: every WARP pulls its own (32*PTS points, NL layers)
 // work item from the global counter and streams the records of its lines through a
-// warp-private shared-memory ring: no block-wide barrier anywhere, so a warp never
-// waits for a neighbour whose lines are denser.
-template <int PTS, int NL>
+// warp-private shared-memory ring: no block-wide barrier after the prologue, so a warp
+// never waits for a neighbour whose lines are denser.
+template <int PTS, int NL, bool TBL>
 __global__ void __launch_bounds__(kSweepThreads, SweepConfig<PTS, NL>::kMinBlocks)
 wing_sweep_kernel(SweepParams const p)
 {
@@ -379,6 +497,17 @@ wing_sweep_kernel(SweepParams const p)
         mbar_init(mb0, 1);
         mbar_init(mb1, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    double *iw = reinterpret_cast<double *>(smem_raw + Cfg::kRingBytes);
+    if (TBL)
+    {
+        // iw[k] = fl((k - pad)*wres): the product of RFM_voigt.c:165 for every sample index.
+        int const entries = sweep_table_entries<PTS>(p.fsteps);
+        for (int k=threadIdx.x; k<entries; k+=kSweepThreads)
+        {
+            iw[k] = __dmul_rn((double)(k - Cfg::kTablePad), p.wres);
+        }
+        __syncthreads();
     }
     __syncwarp();
     unsigned phase = 0;        // bit k = parity the next wait on stage k expects
@@ -410,7 +539,7 @@ wing_sweep_kernel(SweepParams const p)
 #pragma unroll
             for (int j=0; j<PTS; ++j) acc[l][j] = 0.;
         }
-        TileCtx<PTS> tc;
+        TileCtx tc;
         tc.warp_base = warp_base;
         tc.warp_last = warp_base + 32*PTS - 1;
         tc.lane = lane;
@@ -419,6 +548,7 @@ wing_sweep_kernel(SweepParams const p)
         tc.w0 = p.w0;
         tc.wres = p.wres;
         tc.lane_pt = (double)(warp_base + lane);
+        tc.iw_lane = smem_u32(iw) + 8u*(uint32_t)(warp_base + lane + Cfg::kTablePad);
         GridCache<PTS> gc;
         gc.s = INT32_MIN;
 #pragma unroll
@@ -451,7 +581,7 @@ wing_sweep_kernel(SweepParams const p)
 #pragma unroll
             for (int l=0; l<NL; ++l)
             {
-                if (l < nl) process_batch<PTS>(stage + l*32, cnt, tc, gc, acc[l]);
+                if (l < nl) process_batch<PTS, TBL>(stage + l*32, cnt, tc, gc, acc[l]);
             }
             __syncwarp();
             if (lane == 0 && k + 2 < nb)
