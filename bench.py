@@ -347,6 +347,7 @@ def run_ours(args):
         wing_ns = 0
         wing_flop = 0.
         kern = {"prep_ns": 0, "wing_ns": 0, "core_ns": 0}
+        band_ms = {}
         barrier()
         e0.record(stream)
         for k in range(args.steps):
@@ -357,6 +358,8 @@ def run_ours(args):
                 wing_flop += FLOP_PER_SAMPLE*(st["samples"] - st["core_samples"])
                 for key in kern:
                     kern[key] += st[key]
+                    band_ms[f"{name}_{key[:-3]}"] = band_ms.get(f"{name}_{key[:-3]}", 0.) + \
+                        st[key]*1e-6/args.steps
         e1.record(stream)
         barrier()
         secs = e0.elapsed_time(e1)*1e-3
@@ -364,6 +367,7 @@ def run_ours(args):
             t = torch.tensor([secs], device=f"cuda:{device}", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             secs = float(t.item())
+        kern = dict(kern, band_ms=band_ms)
         return secs, wing_ns, wing_flop, kern, out
 
     # warm-up (the first step also uploads the surface arrays the device-resident run reuses)
@@ -401,7 +405,8 @@ def run_ours(args):
         "avg_launch_ms": wing_ns*1e-6/launches_wing if wing_ns else None,
         "samples_per_s": (wing_flop/FLOP_PER_SAMPLE)/(wing_ns*1e-9) if wing_ns else None,
         "fp32_peak": fp32_peak,
-        "kernel_share_of_step": {k: v*1e-9/secs for k, v in kern.items()},
+        "kernel_share_of_step": {k: v*1e-9/secs for k, v in kern.items() if k != "band_ms"},
+        "kernel_ms_per_step": {k: round(v, 3) for k, v in kern["band_ms"].items()},
     }
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3*secs/args.steps, "higher_is_better": True,

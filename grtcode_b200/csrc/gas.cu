@@ -788,9 +788,9 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     int nl = 1;
     if (char const *env = getenv("GRT_SWEEP_PTS")) pts = atoi(env);
     if (char const *env = getenv("GRT_SWEEP_NL")) nl = atoi(env);
-    if (pts != 2 && pts != 4 && pts != 8) pts = 4;
+    if (pts != 2 && pts != 4 && pts != 8 && pts != 16) pts = 4;
     if (nl != 1 && nl != 2) nl = 1;
-    if (pts == 2) nl = 1;
+    if (pts == 2 || pts == 16) nl = 1;
     GRT_TRY(prepare_tiles(g, pts, margin, g->max_abs_delta*pmax));
     sp.num_tiles = g->num_tiles;
     sp.tile_order = g->d_tile_order;
@@ -807,6 +807,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
             case 41: rc = launch_wing<4, 1>(sp, sms, st); break;
             case 42: rc = launch_wing<4, 2>(sp, sms, st); break;
             case 81: rc = launch_wing<8, 1>(sp, sms, st); break;
+            case 161: rc = launch_wing<16, 1>(sp, sms, st); break;
             default: rc = launch_wing<8, 2>(sp, sms, st); break;
         }
         GRT_TRY(rc);

@@ -105,20 +105,52 @@ __device__ __forceinline__ double fast_rcp_of_float(float const d_f)
 }
 
 
-// Per-warp state of the sample abscissae: t2[j] = fl(dwno(s) + fl(i*wres)) for the
-// lane's PTS points and the window start s it was computed for.
-template <int PTS>
+// Per-warp cache of the sample abscissae for kernels without the shared-memory table:
+// t2[j] = fl(dwno(s) + fl(i*wres)) for the lane's PTS points and the window start s it
+// was computed for.  (Empty for TBL kernels, which rebuild t2 from the table per line:
+// fewer than one line in three shares its window start with its predecessor.)
+template <int PTS, bool TBL>
 struct GridCache
 {
     int s;
     double t2[PTS];
 };
 
+#ifndef GRT_TBL_CACHE
+#define GRT_TBL_CACHE 1
+#endif
+
+#if !GRT_TBL_CACHE
+template <int PTS>
+struct GridCache<PTS, true>
+{
+};
+#endif
+
+template <int PTS, bool TBL>
+__device__ __forceinline__ void reset_cache(GridCache<PTS, TBL> &gc)
+{
+    gc.s = INT32_MIN;
+#pragma unroll
+    for (int j=0; j<PTS; ++j) gc.t2[j] = 0.;
+}
+
+#if !GRT_TBL_CACHE
+template <int PTS>
+__device__ __forceinline__ void reset_cache(GridCache<PTS, true> &)
+{
+}
+#endif
+
 // (float)((t2 - v)*REPWID): the last two double roundings and the float rounding of
 // RFM_voigt.c:165.
 __device__ __forceinline__ float abscissa_from(double const t2, double const v, double const repwid)
 {
+#if GRT_DBG_NOF2F     // timing experiment only (wrong results): no FP64->FP32 conversion
+    return __int_as_float(__double2hiint(__dmul_rn(__dsub_rn(t2, v), repwid)));
+#else
     return __double2float_rn(__dmul_rn(__dsub_rn(t2, v), repwid));
+#endif
 }
 
 // What the warp knows about its work item while it walks the lines.
@@ -148,25 +180,66 @@ __device__ __forceinline__ double lds_f64(uint32_t const addr)
     return v;
 }
 
-// TBL: fl(i*wres) comes from the block's shared-memory table iw[] (i = f - s is a small
-// integer: 0 <= i <= 2*fsteps inside a window), so a refresh is one LDS + one DADD per
-// point instead of three FP64 operations.
+// The grid wavenumbers of the lane's points as one line sees them (they depend on the
+// line through its window start s only).  TBL: fl(i*wres) comes from the block's
+// shared-memory table iw[] (i = f - s is a small integer: 0 <= i <= 2*fsteps inside a
+// window), one LDS + one DADD per point.  Otherwise three FP64 operations per point,
+// cached in registers across lines that share s.
 template <int PTS, bool TBL>
-__device__ __forceinline__ void refresh_grid(GridCache<PTS> &gc, TileCtx const &t, int const s)
+struct LineGrid;
+
+#if GRT_TBL_CACHE
+template <int PTS>
+struct LineGrid<PTS, true>
 {
-    if (s != gc.s)
+    GridCache<PTS, true> &gc;
+    __device__ __forceinline__ LineGrid(GridCache<PTS, true> &c, TileCtx const &t, int const s)
+        : gc(c)
     {
-        gc.s = s;
-        double const sd = int_to_double(s);
-        double const dwno = __dadd_rn(__dmul_rn(sd, t.wres), t.w0);
-        if (TBL)
+        if (s != gc.s)
         {
+            gc.s = s;
+            double const dwno = __dadd_rn(__dmul_rn(int_to_double(s), t.wres), t.w0);
             uint32_t const a = t.iw_lane - 8u*(uint32_t)s;
 #pragma unroll
             for (int j=0; j<PTS; ++j) gc.t2[j] = __dadd_rn(dwno, lds_f64(a + 256u*(uint32_t)j));
         }
-        else
+    }
+    __device__ __forceinline__ double t2(int const j) const
+    {
+        return gc.t2[j];
+    }
+};
+#else
+template <int PTS>
+struct LineGrid<PTS, true>
+{
+    double dwno;
+    uint32_t a;
+    __device__ __forceinline__ LineGrid(GridCache<PTS, true> &, TileCtx const &t, int const s)
+    {
+        dwno = __dadd_rn(__dmul_rn(int_to_double(s), t.wres), t.w0);
+        a = t.iw_lane - 8u*(uint32_t)s;
+    }
+    __device__ __forceinline__ double t2(int const j) const
+    {
+        return __dadd_rn(dwno, lds_f64(a + 256u*(uint32_t)j));
+    }
+};
+#endif
+
+template <int PTS>
+struct LineGrid<PTS, false>
+{
+    GridCache<PTS, false> &gc;
+    __device__ __forceinline__ LineGrid(GridCache<PTS, false> &c, TileCtx const &t, int const s)
+        : gc(c)
+    {
+        if (s != gc.s)
         {
+            gc.s = s;
+            double const sd = int_to_double(s);
+            double const dwno = __dadd_rn(__dmul_rn(sd, t.wres), t.w0);
             double const i0 = __dsub_rn(t.lane_pt, sd);     // exact
 #pragma unroll
             for (int j=0; j<PTS; ++j)
@@ -175,7 +248,11 @@ __device__ __forceinline__ void refresh_grid(GridCache<PTS> &gc, TileCtx const &
             }
         }
     }
-}
+    __device__ __forceinline__ double t2(int const j) const
+    {
+        return gc.t2[j];
+    }
+};
 
 // Line classes of the gather, decided once per (line, tile) by the lane that owns the
 // line in the staged batch.
@@ -215,16 +292,16 @@ __device__ __forceinline__ void accumulate2(double &a0, double &a1, double const
 // no predicates, PTS independent dependency chains in flight, two samples per packed op.
 template <int PTS, bool TBL>
 __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileCtx const &t,
-                                          GridCache<PTS> &gc, double (&acc)[PTS])
+                                          GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
-    refresh_grid<PTS, TBL>(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
+    LineGrid<PTS, TBL> const grid(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
+        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
         accumulate2(acc[j], acc[j+1], A.y, far_wing2(mul2_unfused(xi, xi), yq2, yr2));
     }
 }
@@ -232,14 +309,14 @@ __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileC
 // kClsR1: the tile lies wholly inside the window and every point has
 // XLIM1 <= |x| < XLIM0 (wide Doppler cores of the shortwave): region 1 only.
 template <int PTS, bool TBL>
-__device__ __forceinline__ void line_r1(LineRec const *rec, TileCtx const &t, GridCache<PTS> &gc,
-                                        double (&acc)[PTS])
+__device__ __forceinline__ void line_r1(LineRec const *rec, TileCtx const &t,
+                                        GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
     double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
     float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
     float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
     float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, -
-    refresh_grid<PTS, TBL>(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
+    LineGrid<PTS, TBL> const grid(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
     double const repwid = widen_positive(B.x);
     f32x2 const y2 = pack2(C.y, C.y);
     f32x2 const a0 = pack2(D.x, D.x);
@@ -248,7 +325,7 @@ __device__ __forceinline__ void line_r1(LineRec const *rec, TileCtx const &t, Gr
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
+        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
         accumulate2(acc[j], acc[j+1], A.y, region1_2(mul2_unfused(xi, xi), y2, a0, d0, d2));
     }
 }
@@ -256,103 +333,131 @@ __device__ __forceinline__ void line_r1(LineRec const *rec, TileCtx const &t, Gr
 // Pure-Lorentz lines (Y >= 70.55, RFM_voigt.c:97-106).  FULL: the window covers the tile.
 template <int PTS, bool TBL, bool FULL>
 __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
-                                             TileCtx const &t, GridCache<PTS> &gc,
+                                             TileCtx const &t, GridCache<PTS, TBL> &gc,
                                              double (&acc)[PTS])
 {
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    refresh_grid<PTS, TBL>(gc, t, s);
+    LineGrid<PTS, TBL> const grid(gc, t, s);
     double const repwid = widen_positive(B.x);
     int const f0 = t.warp_base + t.lane;
 #pragma unroll
     for (int j=0; j<PTS; ++j)
     {
         int const f = f0 + 32*j;
-        float const xi = abscissa_from(gc.t2[j], A.x, repwid);
+        float const xi = abscissa_from(grid.t2(j), A.x, repwid);
         double const k = fast_rcp_of_float(xi*xi + B.y);
         if (FULL || ((f >= s) && (f <= e))) acc[j] = fma(A.y, k, acc[j]);
     }
 }
 
 
-// kClsFarEdge: far wing only, but a window end falls inside the tile
-// (kernels.c:435-437).  kClsNear: the tile overlaps the line's |x| < XLIM0 core, so lanes
-// may hold far-wing, Humlicek region-1 (RFM_voigt.c:172-183) or line-core samples (the
-// latter are skipped here and left to core_sweep_kernel).  Both are branch-free over the
-// PTS chunks -- every lane evaluates the candidate formulas and selects -- so that PTS
-// independent dependency chains stay in flight; the per-lane float comparisons are the
-// reference's own (RFM_voigt.c:166,172).
-template <int PTS, bool TBL, bool NEAR>
-__device__ __forceinline__ void line_general(LineRec const *rec, TileCtx const &t,
-                                             GridCache<PTS> &gc, double (&acc)[PTS])
+// kClsFarEdge: far wing only, but a window end falls inside the tile (kernels.c:435-437):
+// the far-wing arithmetic with a per-point window predicate.
+template <int PTS, bool TBL>
+__device__ __forceinline__ void line_far_edge(LineRec const *rec, TileCtx const &t,
+                                              GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
     double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
     float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    refresh_grid<PTS, TBL>(gc, t, s);
+    LineGrid<PTS, TBL> const grid(gc, t, s);
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
     int const f0 = t.warp_base + t.lane;
-    if (NEAR)
-    {
-        float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
-        float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, -
-        f32x2 const y2 = pack2(C.y, C.y);
-        f32x2 const a0 = pack2(D.x, D.x);
-        f32x2 const d0 = pack2(D.y, D.y);
-        f32x2 const d2 = pack2(D.z, D.z);
 #pragma unroll
-        for (int j=0; j<PTS; j+=2)
+    for (int j=0; j<PTS; j+=2)
+    {
+        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        f32x2 const k = far_wing2(mul2_unfused(xi, xi), yq2, yr2);
+        float k0, k1;
+        unpack2(k, k0, k1);
+        int const fa = f0 + 32*j;
+        int const fb = fa + 32;
+        if ((fa >= s) && (fa <= e)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
+        if ((fb >= s) && (fb <= e)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+    }
+}
+
+// kClsNear: the tile overlaps the line's |x| < XLIM0 neighbourhood, so its points may be
+// far-wing, Humlicek region-1 (RFM_voigt.c:172-183) or line-core samples (the latter are
+// skipped here and left to core_sweep_kernel).  Every pair of 32-point chunks is
+// dispatched warp-uniformly from the record's conservative half-widths: all far wing,
+// all inside XLIM0 (region 1 where |x| >= XLIM1), or mixed (both formulas, per-lane
+// select with the reference's own float comparisons, RFM_voigt.c:166,172).
+template <int PTS, bool TBL>
+__device__ __forceinline__ void line_near(LineRec const *rec, TileCtx const &t,
+                                          GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+{
+    double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
+    float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
+    float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
+    float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, hw1_hw0in
+    int const fc = __float_as_int(B.w);
+    int const hw0 = __float_as_int(C.x);
+    int const hw0in = (int)(__float_as_uint(D.w) >> 16);
+    int const s = max(fc - t.fsteps, 0);
+    int const e = min(fc + t.fsteps, t.nw - 1);
+    LineGrid<PTS, TBL> const grid(gc, t, s);
+    double const repwid = widen_positive(B.x);
+    f32x2 const yq2 = pack2(B.y, B.y);
+    f32x2 const yr2 = pack2(B.z, B.z);
+    f32x2 const y2 = pack2(C.y, C.y);
+    f32x2 const a0 = pack2(D.x, D.x);
+    f32x2 const d0 = pack2(D.y, D.y);
+    f32x2 const d2 = pack2(D.z, D.z);
+    int const f0 = t.warp_base + t.lane;
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        int const cb = t.warp_base + 32*j;            // the pair covers [cb, cb + 63]
+        int const dlo = max(max(cb - fc, fc - (cb + 63)), 0);
+        int const dhi = max(fc - cb, cb + 63 - fc);
+        int const fa = f0 + 32*j;
+        int const fb = fa + 32;
+        bool const ina = (fa >= s) && (fa <= e);
+        bool const inb = (fb >= s) && (fb <= e);
+        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        f32x2 const xq = mul2_unfused(xi, xi);
+        float x0, x1;
+        unpack2(xi, x0, x1);
+        if (dlo > hw0)
         {
-            f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
-            f32x2 const xq = mul2_unfused(xi, xi);
-            f32x2 const kfar = far_wing2(xq, yq2, yr2);
-            f32x2 const kr1 = region1_2(xq, y2, a0, d0, d2);
-            float x0, x1, kf0, kf1, kr0, kr1s;
-            unpack2(xi, x0, x1);
-            unpack2(kfar, kf0, kf1);
-            unpack2(kr1, kr0, kr1s);
+            float k0, k1;
+            unpack2(far_wing2(xq, yq2, yr2), k0, k1);
+            if (ina) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
+            if (inb) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+        }
+        else if (dhi < hw0in)
+        {
+            float k0, k1;
+            unpack2(region1_2(xq, y2, a0, d0, d2), k0, k1);
+            if (ina && (fabsf(x0) >= C.w)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
+            if (inb && (fabsf(x1) >= C.w)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+        }
+        else
+        {
+            float kf0, kf1, kr0, kr1;
+            unpack2(far_wing2(xq, yq2, yr2), kf0, kf1);
+            unpack2(region1_2(xq, y2, a0, d0, d2), kr0, kr1);
             {
-                int const f = f0 + 32*j;
                 float const ax = fabsf(x0);
                 bool const isfar = ax >= C.z;
                 bool const isr1 = !isfar && (ax >= C.w);
                 float const kf = isr1 ? kr0 : kf0;
-                if ((f >= s) && (f <= e) && (isfar || isr1))
-                {
-                    acc[j] = fma(A.y, widen_positive(kf), acc[j]);
-                }
+                if (ina && (isfar || isr1)) acc[j] = fma(A.y, widen_positive(kf), acc[j]);
             }
             {
-                int const f = f0 + 32*(j + 1);
                 float const ax = fabsf(x1);
                 bool const isfar = ax >= C.z;
                 bool const isr1 = !isfar && (ax >= C.w);
-                float const kf = isr1 ? kr1s : kf1;
-                if ((f >= s) && (f <= e) && (isfar || isr1))
-                {
-                    acc[j+1] = fma(A.y, widen_positive(kf), acc[j+1]);
-                }
+                float const kf = isr1 ? kr1 : kf1;
+                if (inb && (isfar || isr1)) acc[j+1] = fma(A.y, widen_positive(kf), acc[j+1]);
             }
-        }
-    }
-    else
-    {
-#pragma unroll
-        for (int j=0; j<PTS; j+=2)
-        {
-            f32x2 const xi = abscissa2(gc.t2[j], gc.t2[j+1], A.x, repwid);
-            f32x2 const k = far_wing2(mul2_unfused(xi, xi), yq2, yr2);
-            float k0, k1;
-            unpack2(k, k0, k1);
-            int const fa = f0 + 32*j;
-            int const fb = fa + 32;
-            if ((fa >= s) && (fa <= e)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
-            if ((fb >= s) && (fb <= e)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
         }
     }
 }
@@ -363,7 +468,7 @@ __device__ __forceinline__ void line_general(LineRec const *rec, TileCtx const &
 // (kClsFast) with the next record's vectors prefetched while the current one computes.
 template <int PTS, bool TBL>
 __device__ __forceinline__ void process_batch(LineRec const *stage, int const cnt,
-                                              TileCtx const &t, GridCache<PTS> &gc,
+                                              TileCtx const &t, GridCache<PTS, TBL> &gc,
                                               double (&acc)[PTS])
 {
     int cls = kClsNone;
@@ -433,21 +538,29 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
-        line_general<PTS, TBL, false>(stage + b, t, gc, acc);
+        line_far_edge<PTS, TBL>(stage + b, t, gc, acc);
     }
     m = __ballot_sync(0xffffffffu, cls == kClsNear);
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
-        line_general<PTS, TBL, true>(stage + b, t, gc, acc);
+        line_near<PTS, TBL>(stage + b, t, gc, acc);
     }
-    m = __ballot_sync(0xffffffffu, cls >= kClsLorentzFull);
+    m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull);
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
-        // window ends inside the tile are predicated per point
+        line_lorentz<PTS, TBL, true>(*reinterpret_cast<double2 const *>(&stage[b].v),
+                                     *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc,
+                                     acc);
+    }
+    m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge);
+    while (m)
+    {
+        int const b = __ffs(m) - 1;
+        m &= m - 1;
         line_lorentz<PTS, TBL, false>(*reinterpret_cast<double2 const *>(&stage[b].v),
                                       *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc,
                                       acc);
@@ -460,16 +573,18 @@ struct SweepConfig
 {
     static constexpr int kStageBytes = NL*32*(int)sizeof(LineRec);
     static constexpr int kRingBytes = kSweepWarps*2*kStageBytes + kSweepWarps*2*8;
-    static constexpr int kTablePad = 32*PTS;       // iw[] covers i in [-kTablePad, 2F + kTablePad]
     // registers: PTS*NL accumulators + PTS cached abscissae, all double
-    static constexpr int kMinBlocks = (PTS*NL <= 4) ? 3 : ((PTS*NL <= 8) ? 2 : 1);
+    static constexpr int kMinBlocks = (PTS*NL <= 8) ? 3 : ((PTS*NL <= 16) ? 2 : 1);
 };
 
-// Entries of the fl(i*wres) table for a kernel with tiles of 32*PTS points.
+// Entries of the fl(i*wres) table for a kernel with tiles of 32*PTS points: i = f - s runs
+// over [0, 2*fsteps] inside a window; points of an edge tile beyond the window end read up
+// to one tile further (real entries), points before the window start read below the table,
+// into the record rings (any bit pattern: those samples are predicated off).
 template <int PTS>
 __host__ __device__ constexpr int sweep_table_entries(int const fsteps)
 {
-    return 2*fsteps + 2*32*PTS + 2;
+    return 2*fsteps + 32*PTS + 1;
 }
 
 
@@ -501,11 +616,11 @@ wing_sweep_kernel(SweepParams const p)
     double *iw = reinterpret_cast<double *>(smem_raw + Cfg::kRingBytes);
     if (TBL)
     {
-        // iw[k] = fl((k - pad)*wres): the product of RFM_voigt.c:165 for every sample index.
+        // iw[k] = fl(k*wres): the product of RFM_voigt.c:165 for every sample index.
         int const entries = sweep_table_entries<PTS>(p.fsteps);
         for (int k=threadIdx.x; k<entries; k+=kSweepThreads)
         {
-            iw[k] = __dmul_rn((double)(k - Cfg::kTablePad), p.wres);
+            iw[k] = __dmul_rn((double)k, p.wres);
         }
         __syncthreads();
     }
@@ -548,11 +663,9 @@ wing_sweep_kernel(SweepParams const p)
         tc.w0 = p.w0;
         tc.wres = p.wres;
         tc.lane_pt = (double)(warp_base + lane);
-        tc.iw_lane = smem_u32(iw) + 8u*(uint32_t)(warp_base + lane + Cfg::kTablePad);
-        GridCache<PTS> gc;
-        gc.s = INT32_MIN;
-#pragma unroll
-        for (int j=0; j<PTS; ++j) gc.t2[j] = 0.;
+        tc.iw_lane = smem_u32(iw) + 8u*(uint32_t)(warp_base + lane);
+        GridCache<PTS, TBL> gc;
+        reset_cache(gc);
 
         // Lane 0 issues the copies of batch k (32 records of each of the nl layers).
         auto issue = [&](int const k, uint32_t const sb, uint32_t const mb)

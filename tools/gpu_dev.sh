@@ -12,7 +12,7 @@ for v in ${GRT_VARIANTS:-8:1 8:2 4:1}; do
 import json,sys
 for l in sys.stdin:
     d=json.loads(l); r=d['roofline']
-    print('  ms/step %.1f value %.3e samples/s %.3e shares %s' % (d['ms_per_step'], d['value'], r['samples_per_s'], r['kernel_share_of_step']))
+    print('  ms/step %.1f value %.3e samples/s %.3e shares %s' % (d['ms_per_step'], d['value'], r['samples_per_s'], r.get('kernel_ms_per_step', r['kernel_share_of_step'])))
 "
 done
 for v in ${GRT_C1_VARIANTS:-4:1 2:1}; do

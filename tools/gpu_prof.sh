@@ -4,7 +4,9 @@
 mkdir -p gpurun_out
 BENCH="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --scale 0.25"
 $BENCH > gpurun_out/plain_q.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:sweep -s 4 -c 4 \
+ncu --set full --clock-control none --import-source on -k regex:wing_sweep -s 2 -c 2 \
     -f -o gpurun_out/prof_sweep_q $BENCH > gpurun_out/ncu_q.log 2>&1
-tail -2 gpurun_out/ncu_q.log
+ncu --set full --clock-control none --import-source on -k regex:core_sweep -s 3 -c 1 \
+    -f -o gpurun_out/prof_core_q $BENCH > gpurun_out/ncu_core_q.log 2>&1
+tail -2 gpurun_out/ncu_q.log; tail -2 gpurun_out/ncu_core_q.log
 grep '^{' gpurun_out/plain_q.log | cut -c1-400
