@@ -99,93 +99,6 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-class Engine:
-    """One rank's state: gas optics + solvers for both bands on one GPU, through the
-    reference-facing C API (grtcode_b200.api -> libgrtcode.so -> libgrt_sm100.so)."""
-
-    def __init__(self, api, bands, column, device: int):
-        from grtcode_b200 import workloads as W
-        self.api = api
-        self.device = device
-        self.levels = len(column.p)
-        self.parts = []
-        for band in bands:
-            ds = band.dataset
-            grid = api.spectral_grid(band.w0, band.wn, band.dw)
-            go = api.GasOptics(self.levels, grid, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm,
-                               device=device)
-            for m in W.MOLECULES:
-                go.add_molecule(m)
-            for c, path in ds.cfc.items():
-                go.add_cfc(c, path)
-            for (a, b), path in ds.cia.items():
-                go.add_cia(a, b, path)
-            gas = api.OpticsObject(self.levels - 1, grid, device)
-            n = int(grid.n)
-            part = dict(band=band, grid=grid, go=go, gas=gas, n=n)
-            if band.name.startswith("lw"):
-                part["solver"] = api.LongwaveSolver(self.levels, grid, device)
-                part["emis"] = pinned(api, n, column.emissivity)
-            else:
-                part["solver"] = api.ShortwaveSolver(self.levels, grid, device)
-                part["alb"] = pinned(api, n, column.albedo)
-                sol = api.solar_flux(grid, ds.solar)
-                part["solar"] = pinned(api, n, 0.)
-                part["solar"][:] = sol
-            self.parts.append(part)
-        self.launches = 0
-        self.last = {}
-
-    def step(self, col, upload_surface: bool):
-        """One column.  upload_surface=True is the end-to-end form: every host array the
-        API takes is passed (and copied to the GPU) again."""
-        out = {}
-        launches = 0
-        h2d = 0
-        for part in self.parts:
-            go = part["go"]
-            for m, v in col.ppmv.items():
-                go.set_ppmv("mol", m, v)
-            for c, v in col.cfc_ppmv.items():
-                if c in part["band"].dataset.cfc:
-                    go.set_ppmv("cfc", c, v)
-            for c, v in col.cia_ppmv.items():
-                go.set_ppmv("cia", c, v)
-            go.optical_depth(col.p, col.t, part["gas"])
-            st = go.stats()
-            launches += st["launches"]
-            h2d += 8*self.levels*(2 + 53 + 21 + 2)
-            name = part["band"].name[:2]
-            if name == "lw":
-                emis = part["emis"] if upload_surface else None
-                up, dn = part["solver"].column(part["gas"], col.p, col.t_surf, col.t_layer,
-                                               col.t, emis)
-                h2d += 8*part["n"] if upload_surface else 0
-            else:
-                alb = part["alb"] if upload_surface else None
-                up, dn = part["solver"].column(part["gas"], col.p, col.mu0, 0.5, alb, alb,
-                                               col.tsi, part["solar"] if upload_surface else None)
-                h2d += 2*8*part["n"] if upload_surface else 0
-            launches += 1
-            out[name] = (up, dn, st)
-        self.launches = launches
-        self.h2d = h2d
-        self.d2h = 2*2*8*self.levels + 2*32
-        self.last = out
-        return out
-
-
-def pinned(api, n: int, fill: float) -> np.ndarray:
-    """float64[n] in page-locked host memory (cudaMallocHost through the C ABI)."""
-    import ctypes as C
-    ptr = C.c_void_p()
-    if api.cuda_layer().grt_host_alloc(C.byref(ptr), 8*n) != 0:
-        raise RuntimeError("grt_host_alloc failed")
-    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,))
-    arr[:] = fill
-    return arr
-
-
 def cpu_reference_sample(args, col, threads=None, reps: int = 1):
     """The reference's own CPU implementation (oracle/_ref, gcc -O3 -fopenmp; the C
     restatement when that is absent) on a bounded sample of the workload: a 20 cm-1
@@ -327,7 +240,8 @@ def run_ours(args):
         W.materialise(lw, args.data, seed=1)
         W.materialise(sw, args.data, seed=2)
     t_setup = time.perf_counter()
-    eng = Engine(api, (lw, sw), col0, device)
+    from grtcode_b200.column_engine import ColumnEngine
+    eng = ColumnEngine((lw, sw), col0, device, W.MOLECULES)
     t_setup = time.perf_counter() - t_setup
     layers = eng.levels - 1
     pts_layers = (lw.n + sw.n)*layers

@@ -121,6 +121,12 @@ def load():
                                       _dbl_p, _dbl_p, _dbl_p, _dbl_p]
     L.calculate_lw_column.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), _dbl_p, C.c_double,
                                       _dbl_p, _dbl_p, _dbl_p, _dbl_p, _dbl_p]
+    L.calculate_lw_column_window.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), _dbl_p,
+                                             C.c_double, _dbl_p, _dbl_p, _dbl_p, C.c_uint64,
+                                             C.c_uint64, _dbl_p, _dbl_p]
+    L.calculate_sw_column_window.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), _dbl_p,
+                                             C.c_double, C.c_double, _dbl_p, _dbl_p, C.c_double,
+                                             _dbl_p, C.c_uint64, C.c_uint64, _dbl_p, _dbl_p]
     L.create_shortwave.argtypes = [C.POINTER(Shortwave), C.c_int, C.POINTER(SpectralGrid),
                                    C.POINTER(C.c_int)]
     L.destroy_shortwave.argtypes = [C.POINTER(Shortwave)]
@@ -353,14 +359,16 @@ class LongwaveSolver:
                "calculate_lw_fluxes")
         return up, dn
 
-    def column(self, gas: OpticsObject, p_mb, t_surf, t_layers, t_levels, emis):
+    def column(self, gas: OpticsObject, p_mb, t_surf, t_layers, t_levels, emis, window=None):
+        """Broadband fluxes of one column; window = (first, last) grid indices restricts
+        the integration (spectral split with halo points)."""
         up = np.empty(self.num_levels)
         dn = np.empty(self.num_levels)
-        _check(self.L.calculate_lw_column(C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)),
-                                          float(t_surf), _dp(_f64(t_layers)), _dp(_f64(t_levels)),
-                                          _dp(_f64(emis)) if emis is not None else None,
-                                          _dp(up), _dp(dn)),
-               "calculate_lw_column")
+        first, last = window if window is not None else (0, self.n - 1)
+        _check(self.L.calculate_lw_column_window(
+            C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)), float(t_surf), _dp(_f64(t_layers)),
+            _dp(_f64(t_levels)), _dp(_f64(emis)) if emis is not None else None, first, last,
+            _dp(up), _dp(dn)), "calculate_lw_column")
         return up, dn
 
     def close(self):
@@ -396,7 +404,8 @@ class ShortwaveSolver:
                "calculate_sw_fluxes")
         return up, dn
 
-    def column(self, gas: OpticsObject, p_mb, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar):
+    def column(self, gas: OpticsObject, p_mb, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar,
+               window=None):
         up = np.empty(self.num_levels)
         dn = np.empty(self.num_levels)
         if alb_dir is None:
@@ -405,10 +414,10 @@ class ShortwaveSolver:
             a1 = _f64(alb_dir)
             a2 = a1 if alb_dif is alb_dir else _f64(alb_dif)
             p1, p2, p3 = _dp(a1), _dp(a2), _dp(_f64(solar))
-        _check(self.L.calculate_sw_column(C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)),
-                                          float(mu_dir), float(mu_dif), p1, p2,
-                                          float(tsi), p3, _dp(up), _dp(dn)),
-               "calculate_sw_column")
+        first, last = window if window is not None else (0, self.n - 1)
+        _check(self.L.calculate_sw_column_window(
+            C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)), float(mu_dir), float(mu_dif), p1, p2,
+            float(tsi), p3, first, last, _dp(up), _dp(dn)), "calculate_sw_column")
         return up, dn
 
     def close(self):

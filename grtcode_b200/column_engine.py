@@ -1,0 +1,125 @@
+"""One GPU's worth of the hot path behind the reference-facing C API.
+
+A ``ColumnEngine`` owns, for every spectral band it is given, a ``GasOptics_t``, an
+``Optics_t`` for the gas optical depths and the band's solver (``Longwave_t`` for a band
+whose name starts with "lw", ``Shortwave_t`` otherwise) and runs columns through them in
+the order the reference's ``column_calculation`` does (framework/src/driver.c:360-600):
+set abundances -> calculate_optical_depth -> Rayleigh + add_optics + fluxes + broadband
+integration (the last three fused in ``calculate_{lw,sw}_column``).
+
+Everything goes through grtcode_b200.api -> libgrtcode.so -> libgrt_sm100.so; there is
+no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import api as _api
+
+
+def pinned(n: int, fill: float) -> np.ndarray:
+    """float64[n] in page-locked host memory (cudaMallocHost through the C ABI)."""
+    ptr = C.c_void_p()
+    if _api.cuda_layer().grt_host_alloc(C.byref(ptr), 8*n) != 0:
+        raise RuntimeError("grt_host_alloc failed")
+    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,))
+    arr[:] = fill
+    return arr
+
+
+class ColumnEngine:
+    """bands: objects with name, w0, wn, dw and a materialised ``dataset`` (synth.Dataset).
+    line_window: optional {band name: (min, max)} passed to add_molecule, the reference's
+    own way of restricting the lines a GasOptics_t loads (gas_optics.h:117-119).
+    windows: optional {band name: (first, last)} integration windows (spectral split).
+    solar_override: optional {band name: float64[n]} incident solar spectrum to use
+    instead of create_solar_flux on the band's own grid."""
+
+    def __init__(self, bands, column, device: int, molecules, line_window=None, windows=None,
+                 solar_override=None):
+        api = _api
+        api.load()
+        self.device = device
+        self.levels = len(column.p)
+        self.parts = []
+        for band in bands:
+            ds = band.dataset
+            grid = api.spectral_grid(band.w0, band.wn, band.dw)
+            go = api.GasOptics(self.levels, grid, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm,
+                               device=device)
+            win = (line_window or {}).get(band.name, (None, None))
+            for m in molecules:
+                go.add_molecule(m, *win)
+            for c, path in ds.cfc.items():
+                go.add_cfc(c, path)
+            for (a, b), path in ds.cia.items():
+                go.add_cia(a, b, path)
+            gas = api.OpticsObject(self.levels - 1, grid, device)
+            n = int(grid.n)
+            part = dict(band=band, grid=grid, go=go, gas=gas, n=n,
+                        window=(windows or {}).get(band.name))
+            if band.name.startswith("lw"):
+                part["solver"] = api.LongwaveSolver(self.levels, grid, device)
+                part["emis"] = pinned(n, column.emissivity)
+            else:
+                part["solver"] = api.ShortwaveSolver(self.levels, grid, device)
+                part["alb"] = pinned(n, column.albedo)
+                sol = (solar_override or {}).get(band.name)
+                if sol is None:
+                    sol = api.solar_flux(grid, ds.solar)
+                part["solar"] = pinned(n, 0.)
+                part["solar"][:] = sol
+            self.parts.append(part)
+        self.launches = 0
+        self.h2d = 0
+        self.d2h = 0
+        self.last = {}
+
+    def step(self, col, upload_surface: bool):
+        """One column.  upload_surface=True is the end-to-end form: every host array the
+        API takes is passed (and copied to the GPU) again.  Returns
+        {"lw"/"sw": (flux_up[levels], flux_down[levels], kernel stats)} in W m-2."""
+        out = {}
+        launches = 0
+        h2d = 0
+        for part in self.parts:
+            go = part["go"]
+            for m, v in col.ppmv.items():
+                go.set_ppmv("mol", m, v)
+            for c, v in col.cfc_ppmv.items():
+                if c in part["band"].dataset.cfc:
+                    go.set_ppmv("cfc", c, v)
+            for c, v in col.cia_ppmv.items():
+                go.set_ppmv("cia", c, v)
+            go.optical_depth(col.p, col.t, part["gas"])
+            st = go.stats()
+            launches += st["launches"]
+            h2d += 8*self.levels*(2 + 53 + 21 + 2)
+            name = part["band"].name[:2]
+            if name == "lw":
+                emis = part["emis"] if upload_surface else None
+                up, dn = part["solver"].column(part["gas"], col.p, col.t_surf, col.t_layer,
+                                               col.t, emis, window=part["window"])
+                h2d += 8*part["n"] if upload_surface else 0
+            else:
+                alb = part["alb"] if upload_surface else None
+                up, dn = part["solver"].column(part["gas"], col.p, col.mu0, 0.5, alb, alb,
+                                               col.tsi, part["solar"] if upload_surface else None,
+                                               window=part["window"])
+                h2d += 2*8*part["n"] if upload_surface else 0
+            launches += 1
+            out[name] = (up, dn, st)
+        self.launches = launches
+        self.h2d = h2d
+        self.d2h = 2*2*8*self.levels + 2*32
+        self.last = out
+        return out
+
+    def close(self):
+        for part in self.parts:
+            part["solver"].close()
+            part["gas"].close()
+            part["go"].close()
+        self.parts = []

@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(kSolverThreads)
 lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const nw,
           double const t_surf, LevelTemps const temps, LayerDensity const dens,
           double const *tau, double const *omega, double const *emis, double *flux_up,
-          double *flux_down)
+          double *flux_down, uint64_t const first, uint64_t const last)
 {
     __shared__ double warp_sums[kSolverThreads/32];
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
@@ -149,8 +149,10 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     double weight = 0.;
     if (FUSED)
     {
-        weight = live ? ((ii == 0 || ii == nw - 1) ? 0.5*dw : dw) : 0.;
-        if (nw == 1) weight = 0.;
+        // trapezoid weights of output_fluxes over the integration window [first, last]
+        weight = (live && ii >= first && ii <= last) ? ((ii == first || ii == last) ? 0.5*dw : dw)
+                                                     : 0.;
+        if (first == last) weight = 0.;
     }
 
     auto layer_tau = [&](int const j) -> double
@@ -311,7 +313,7 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
           LayerDensity const dens, double const *omega_in, double const *g_in,
           double const *tau_in, double const mu_dir, double const mu_dif,
           double const *alb_dir, double const *alb_dif, double const tsi, double const *solar,
-          double *flux_up, double *flux_down)
+          double *flux_up, double *flux_down, uint64_t const first, uint64_t const last)
 {
     __shared__ double warp_sums[kSolverThreads/32];
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
@@ -372,8 +374,10 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     double weight = 0.;
     if (FUSED)
     {
-        weight = live ? ((ii == 0 || ii == nw - 1) ? 0.5*dw : dw) : 0.;
-        if (nw == 1) weight = 0.;
+        // trapezoid weights of output_fluxes over the integration window [first, last]
+        weight = (live && ii >= first && ii <= last) ? ((ii == first || ii == last) ? 0.5*dw : dw)
+                                                     : 0.;
+        if (first == last) weight = 0.;
     }
     double dir_beam = 1.;
     double dif_beam = 0.;
@@ -472,20 +476,20 @@ static int launch_sw(cudaStream_t st, int num_levels, double w0, double dw, uint
                      LayerDensity const &dens, double const *omega, double const *g,
                      double const *tau, double mu_dir, double mu_dif, double const *alb_dir,
                      double const *alb_dif, double tsi, double const *solar, double *up,
-                     double *down)
+                     double *down, uint64_t first, uint64_t last)
 {
     unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
     if (num_levels - 1 <= 64)
     {
         sw_kernel<64, FUSED><<<blocks, kSolverThreads, 0, st>>>(
             num_levels, w0, dw, nw, dens, omega, g, tau, mu_dir, mu_dif, alb_dir, alb_dif, tsi,
-            solar, up, down);
+            solar, up, down, first, last);
     }
     else
     {
         sw_kernel<GRT_MAX_LAYERS, FUSED><<<blocks, kSolverThreads, 0, st>>>(
             num_levels, w0, dw, nw, dens, omega, g, tau, mu_dir, mu_dif, alb_dir, alb_dif, tsi,
-            solar, up, down);
+            solar, up, down, first, last);
     }
     GRT_CUDA(cudaGetLastError());
     return 0;
@@ -542,7 +546,7 @@ int grt_lw_fluxes(int device, int num_levels, double w0, double dw, uint64_t nw,
     unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
     lw_kernel<false><<<blocks, kSolverThreads, 0, st>>>(num_levels, w0, dw, nw, t_surf, temps,
                                                         dens, tau_dev, omega_dev, emis_dev,
-                                                        flux_up_dev, flux_down_dev);
+                                                        flux_up_dev, flux_down_dev, 0, nw - 1);
     GRT_CUDA(cudaGetLastError());
     return 0;
 }
@@ -558,7 +562,7 @@ int grt_sw_fluxes(int device, int num_levels, uint64_t nw, double const *omega_d
     LayerDensity dens{};
     return launch_sw<false>(st, num_levels, 0., 0., nw, dens, omega_dev, g_dev, tau_dev, mu_dir,
                             mu_dif, alb_dir_dev, alb_dif_dev, tsi, solar_dev, flux_up_dev,
-                            flux_down_dev);
+                            flux_down_dev, 0, nw - 1);
 }
 
 int grt_integrate_flux(int device, int num_levels, uint64_t nw, double dw,
@@ -583,8 +587,9 @@ int grt_integrate_flux(int device, int num_levels, uint64_t nw, double dw,
 int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
                   double const *p_atm, double t_surf, double const *t_layers,
                   double const *t_levels, double const *tau_gas_dev, double const *emis_dev,
-                  double *up, double *down)
+                  uint64_t first, uint64_t last, double *up, double *down)
 {
+    if (first > last || last >= nw) return fail("integration window outside the grid");
     if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
     cudaStream_t st;
     GRT_TRY(stream_of(device, &st));
@@ -599,7 +604,7 @@ int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
     unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
     lw_kernel<true><<<blocks, kSolverThreads, 0, st>>>(num_levels, w0, dw, nw, t_surf, temps, dens,
                                                        tau_gas_dev, nullptr, emis_dev, buf,
-                                                       buf + num_levels);
+                                                       buf + num_levels, first, last);
     GRT_CUDA(cudaGetLastError());
     GRT_CUDA(cudaMemcpyAsync(up, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
     GRT_CUDA(cudaMemcpyAsync(down, buf + num_levels, sizeof(double)*num_levels,
@@ -611,8 +616,10 @@ int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
 int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
                   double const *p_atm, double const *tau_gas_dev, double mu_dir, double mu_dif,
                   double const *alb_dir_dev, double const *alb_dif_dev, double tsi,
-                  double const *solar_dev, double *up, double *down)
+                  double const *solar_dev, uint64_t first, uint64_t last, double *up,
+                  double *down)
 {
+    if (first > last || last >= nw) return fail("integration window outside the grid");
     if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
     cudaStream_t st;
     GRT_TRY(stream_of(device, &st));
@@ -623,7 +630,7 @@ int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
     GRT_CUDA(cudaMemsetAsync(buf, 0, sizeof(double)*2*num_levels, st));
     GRT_TRY(launch_sw<true>(st, num_levels, w0, dw, nw, dens, nullptr, nullptr, tau_gas_dev,
                             mu_dir, mu_dif, alb_dir_dev, alb_dif_dev, tsi, solar_dev, buf,
-                            buf + num_levels));
+                            buf + num_levels, first, last));
     GRT_CUDA(cudaMemcpyAsync(up, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
     GRT_CUDA(cudaMemcpyAsync(down, buf + num_levels, sizeof(double)*num_levels,
                              cudaMemcpyDeviceToHost, st));

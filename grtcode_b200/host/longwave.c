@@ -71,9 +71,10 @@ int calculate_lw_fluxes(Longwave_t * const lw, Optics_t const * const optics, fp
     return GRTCODE_SUCCESS;
 }
 
-int calculate_lw_column(Longwave_t * const lw, Optics_t const * const gas, fp_t * const pressure,
-                        fp_t const T_surf, fp_t * const T_layers, fp_t * const T_levels,
-                        fp_t * const emis, fp_t * const up, fp_t * const down)
+int calculate_lw_column_window(Longwave_t * const lw, Optics_t const * const gas,
+                               fp_t * const pressure, fp_t const T_surf, fp_t * const T_layers,
+                               fp_t * const T_levels, fp_t * const emis, uint64_t const first,
+                               uint64_t const last, fp_t * const up, fp_t * const down)
 {
     REQUIRE_PTR(lw);
     REQUIRE_PTR(gas);
@@ -83,6 +84,11 @@ int calculate_lw_column(Longwave_t * const lw, Optics_t const * const gas, fp_t 
     REQUIRE_PTR(up);
     REQUIRE_PTR(down);
     TRY(check_against_optics(lw, gas));
+    if (first > last || last >= lw->grid.n)
+    {
+        FAIL(GRTCODE_RANGE_ERR, "integration window [%llu, %llu] outside the grid of %llu points.",
+             (unsigned long long)first, (unsigned long long)last, (unsigned long long)lw->grid.n);
+    }
     fp_t const mbtoatm = 0.000986923f; /* rayleigh.c:104 */
     fp_t p_atm[MAX_NUM_LEVELS];
     int i;
@@ -95,6 +101,20 @@ int calculate_lw_column(Longwave_t * const lw, Optics_t const * const gas, fp_t 
         GPU(grt_copy_to_device(lw->device, lw->emissivity, emis, sizeof(fp_t)*lw->grid.n));
     }
     GPU(grt_lw_column(lw->device, lw->num_levels, lw->grid.w0, lw->grid.dw, lw->grid.n, p_atm,
-                      T_surf, T_layers, T_levels, gas->tau, lw->emissivity, up, down));
+                      T_surf, T_layers, T_levels, gas->tau, lw->emissivity, first, last, up, down));
     return GRTCODE_SUCCESS;
+}
+
+int calculate_lw_column(Longwave_t * const lw, Optics_t const * const gas, fp_t * const pressure,
+                        fp_t const T_surf, fp_t * const T_layers, fp_t * const T_levels,
+                        fp_t * const emis, fp_t * const up, fp_t * const down)
+{
+    REQUIRE_PTR(lw);
+    int const rc = calculate_lw_column_window(lw, gas, pressure, T_surf, T_layers, T_levels, emis,
+                                              0, lw->grid.n - 1, up, down);
+    if (rc != GRTCODE_SUCCESS)
+    {
+        grt_error_frame(__FILE__, __LINE__);
+    }
+    return rc;
 }

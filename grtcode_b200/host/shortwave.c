@@ -96,10 +96,12 @@ int calculate_sw_fluxes(Shortwave_t * const sw, Optics_t const * const optics, f
     return GRTCODE_SUCCESS;
 }
 
-int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const gas, fp_t * const pressure,
-                        fp_t const mu_dir, fp_t const mu_dif, fp_t * const sfc_alpha_dir,
-                        fp_t * const sfc_alpha_dif, fp_t const total_solar_irradiance,
-                        fp_t * const solar_flux, fp_t * const up, fp_t * const down)
+int calculate_sw_column_window(Shortwave_t * const sw, Optics_t const * const gas,
+                               fp_t * const pressure, fp_t const mu_dir, fp_t const mu_dif,
+                               fp_t * const sfc_alpha_dir, fp_t * const sfc_alpha_dif,
+                               fp_t const total_solar_irradiance, fp_t * const solar_flux,
+                               uint64_t const first, uint64_t const last, fp_t * const up,
+                               fp_t * const down)
 {
     REQUIRE_PTR(sw);
     REQUIRE_PTR(gas);
@@ -107,6 +109,11 @@ int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const gas, fp_t
     REQUIRE_PTR(up);
     REQUIRE_PTR(down);
     TRY(check_against_optics(sw, gas));
+    if (first > last || last >= sw->grid.n)
+    {
+        FAIL(GRTCODE_RANGE_ERR, "integration window [%llu, %llu] outside the grid of %llu points.",
+             (unsigned long long)first, (unsigned long long)last, (unsigned long long)sw->grid.n);
+    }
     fp_t const mbtoatm = 0.000986923f;
     fp_t p_atm[MAX_NUM_LEVELS];
     int i;
@@ -120,8 +127,24 @@ int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const gas, fp_t
     }
     GPU(grt_sw_column(sw->device, sw->num_levels, sw->grid.w0, sw->grid.dw, sw->grid.n, p_atm,
                       gas->tau, mu_dir, mu_dif, sw->sfc_alpha_dir, sw->sfc_alpha_dif,
-                      total_solar_irradiance, sw->solar_flux, up, down));
+                      total_solar_irradiance, sw->solar_flux, first, last, up, down));
     return GRTCODE_SUCCESS;
+}
+
+int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const gas, fp_t * const pressure,
+                        fp_t const mu_dir, fp_t const mu_dif, fp_t * const sfc_alpha_dir,
+                        fp_t * const sfc_alpha_dif, fp_t const total_solar_irradiance,
+                        fp_t * const solar_flux, fp_t * const up, fp_t * const down)
+{
+    REQUIRE_PTR(sw);
+    int const rc = calculate_sw_column_window(sw, gas, pressure, mu_dir, mu_dif, sfc_alpha_dir,
+                                              sfc_alpha_dif, total_solar_irradiance, solar_flux,
+                                              0, sw->grid.n - 1, up, down);
+    if (rc != GRTCODE_SUCCESS)
+    {
+        grt_error_frame(__FILE__, __LINE__);
+    }
+    return rc;
 }
 
 int rayleigh_scattering(Optics_t * const optics, fp_t * const pressure)

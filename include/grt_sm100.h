@@ -125,15 +125,18 @@ int grt_integrate_flux(int device, int num_levels, uint64_t num_wpoints, double 
 /* ---- fused column solvers for the drivers (no spectral arrays leave the GPU):
  * Rayleigh + optics mixing + solver + broadband integration in one kernel each;
  * replaces the chain column_calculation -> add_optics -> calculate_*_fluxes ->
- * output_fluxes (framework/src/driver.c:360-424).  up/down have num_levels entries. */
+ * output_fluxes (framework/src/driver.c:360-424).  up/down have num_levels entries.
+ * [first, last] is the index range of the trapezoid integration (0, num_wpoints - 1 for
+ * the whole grid; a sub-range when the grid carries halo points of a spectral split). */
 int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
                   double const *p_atm, double t_surf, double const *t_layers,
                   double const *t_levels, double const *tau_gas_dev, double const *emis_dev,
-                  double *up, double *down);
+                  uint64_t first, uint64_t last, double *up, double *down);
 int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
                   double const *p_atm, double const *tau_gas_dev, double mu_dir,
                   double mu_dif, double const *alb_dir_dev, double const *alb_dif_dev,
-                  double tsi, double const *solar_dev, double *up, double *down);
+                  double tsi, double const *solar_dev, uint64_t first, uint64_t last,
+                  double *up, double *down);
 
 /* ---- measurement helper: sustained FP64 / FP32 FMA throughput of this GPU
  * [TFLOP/s, FMA = 2 flop], the roofline denominator of the Voigt sweep. */

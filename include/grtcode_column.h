@@ -22,6 +22,22 @@ EXTERN int calculate_sw_column(Shortwave_t * const sw, Optics_t const * const ga
                                fp_t * const sfc_alpha_dir, fp_t * const sfc_alpha_dif,
                                fp_t const total_solar_irradiance, fp_t * const solar_flux,
                                fp_t * const up, fp_t * const down);
+/* The same with the broadband integration restricted to grid points [first, last]
+ * (trapezoid end weights at first and last): a rank of a spectral split computes on its
+ * chunk plus a 25 cm-1 halo -- so that lines centred next to the chunk contribute -- and
+ * integrates only the points it owns. */
+EXTERN int calculate_lw_column_window(Longwave_t * const lw, Optics_t const * const gas,
+                                      fp_t * const pressure, fp_t const T_surf,
+                                      fp_t * const T_layers, fp_t * const T_levels,
+                                      fp_t * const emis, uint64_t const first,
+                                      uint64_t const last, fp_t * const up, fp_t * const down);
+EXTERN int calculate_sw_column_window(Shortwave_t * const sw, Optics_t const * const gas,
+                                      fp_t * const pressure, fp_t const mu_dir,
+                                      fp_t const mu_dif, fp_t * const sfc_alpha_dir,
+                                      fp_t * const sfc_alpha_dif,
+                                      fp_t const total_solar_irradiance,
+                                      fp_t * const solar_flux, uint64_t const first,
+                                      uint64_t const last, fp_t * const up, fp_t * const down);
 /* Trapezoid integral over wavenumber of a device flux array (level, wavenumber). */
 EXTERN int integrate_fluxes(Device_t const device, int const num_levels,
                             SpectralGrid_t const * const grid, fp_t const * const flux_dev,

@@ -29,7 +29,8 @@ def build_dataset(root, w0, wn, lines, seed, cfcs=(), cias=()):
     return synth.make_dataset(root, w0, wn, lines, seed=seed, cfcs=cfcs, cias=cias)
 
 
-def oracle_column(ds, w0, wn, dw, col, molecules, use_ctm=True, threads=None, solvers=True):
+def oracle_column(ds, w0, wn, dw, col, molecules, use_ctm=True, threads=None, solvers=True,
+                  line_window=(None, None)):
     """Reference pipeline on the host: tau_gas, then (optionally) LW + SW fluxes."""
     r = R.Ref(threads=threads)
     g = r.grid(w0, wn, dw)
@@ -37,7 +38,7 @@ def oracle_column(ds, w0, wn, dw, col, molecules, use_ctm=True, threads=None, so
     go = R.RefGasOptics(r, levels, g, ds.hitran, ds.h2o_ctm_dir if use_ctm else None,
                         ds.o3_ctm if use_ctm else None)
     for m in molecules:
-        go.add_molecule(m)
+        go.add_molecule(m, *line_window)
     for c, path in ds.cfc.items():
         go.add_cfc(c, path)
     for (a, b), path in ds.cia.items():
@@ -74,14 +75,15 @@ def oracle_column(ds, w0, wn, dw, col, molecules, use_ctm=True, threads=None, so
     return out
 
 
-def gpu_column(ds, w0, wn, dw, col, molecules, use_ctm=True, solvers=True, device=0):
+def gpu_column(ds, w0, wn, dw, col, molecules, use_ctm=True, solvers=True, device=0,
+               line_window=(None, None)):
     """Same pipeline through libgrtcode.so (the reference's C API on the GPU)."""
     g = api.spectral_grid(w0, wn, dw)
     levels = len(col.p)
     go = api.GasOptics(levels, g, ds.hitran, ds.h2o_ctm_dir if use_ctm else None,
                        ds.o3_ctm if use_ctm else None, device=device)
     for m in molecules:
-        go.add_molecule(m)
+        go.add_molecule(m, *line_window)
     for c, path in ds.cfc.items():
         go.add_cfc(c, path)
     for (a, b), path in ds.cia.items():

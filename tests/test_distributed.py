@@ -1,0 +1,120 @@
+"""Multi-rank host logic on CPU: world size 2, gloo backend.
+
+Covers the block partition of columns, the spectral split (chunks share end points, carry
+a cut-off halo, and their sub-grids have exactly the expected number of points when built
+by the host library), and the one collective of the path -- the SUM all-reduce of partial
+broadband integrals -- against the unsplit trapezoid sum (framework/src/driver.c:302-319).
+No CUDA call is made here; the GPU counterpart is tests/test_gpu_parity.py.
+"""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from grtcode_b200 import parallel as P
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_column_shards_cover_every_column_once():
+    for cols, world in ((1800, 8), (1800, 7), (65341, 8), (5, 8), (1, 1)):
+        seen = []
+        for r in range(world):
+            seen.extend(P.shard_columns(cols, world, r))
+        assert seen == list(range(cols))
+        sizes = [len(P.shard_columns(cols, world, r)) for r in range(world)]
+        assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        P.shard_columns(10, 2, 2)
+
+
+@pytest.mark.parametrize("w0,wn,dw,world", [(1., 50000., 0.01, 8), (1., 3250., 0.1, 2),
+                                            (1., 3000., 0.1, 3), (500., 700., 0.1, 4)])
+def test_spectral_chunks_tile_the_grid(w0, wn, dw, world):
+    n = P.grid_size(w0, wn, dw)
+    chunks = P.split_spectral_range(w0, wn, dw, world)
+    assert chunks[0].first == 0 and chunks[-1].last == n - 1
+    halo = int(np.ceil(np.float32(25.)/dw)) + 1
+    for a, b in zip(chunks[:-1], chunks[1:]):
+        assert a.last == b.first                      # shared seam point
+    for c in chunks:
+        assert c.lo == max(c.first - halo, 0) and c.hi == min(c.last + halo, n - 1)
+        first, last = c.window
+        assert 0 <= first < last <= c.n - 1
+        assert abs(c.w_lo - (w0 + c.lo*dw)) < 1e-9
+    sizes = [c.last - c.first for c in chunks]
+    assert sum(sizes) == n - 1 and max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        P.split_spectral_range(1., 1.5, 0.1, 8)
+
+
+def test_chunk_grids_have_the_expected_size_in_the_host_library(built):
+    """create_spectral_grid (spectral_grid.c:61) on (w_lo, wn_arg, dw) gives hi - lo + 1
+    points for every chunk of the config-4 split, and w(i) lands on the global grid."""
+    api = built
+    api.load()
+    for w0, wn, dw, world in ((1., 50000., 0.01, 8), (1., 3250., 0.1, 4)):
+        for c in P.split_spectral_range(w0, wn, dw, world):
+            g = api.spectral_grid(c.w_lo, c.wn_arg, dw)
+            assert int(g.n) == c.n
+            assert abs((g.w0 + (c.n - 1)*dw) - (w0 + c.hi*dw)) < 1e-6*dw
+
+
+def _planck_like(w):
+    return w**3/np.expm1(w/600.) + 50.*np.exp(-0.5*((w - 667.)/8.)**2)
+
+
+def _worker(rank: int, world: int, port: int, tmp: str):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        w0, wn, dw, levels = 1., 3250., 0.1, 7
+        n = P.grid_size(w0, wn, dw)
+        ch = P.split_spectral_range(w0, wn, dw, world)[rank]
+        # synthetic spectral fluxes on the rank's own (halo-carrying) grid
+        w = ch.w_lo + np.arange(ch.n)*dw
+        scale = 1. + 0.1*np.arange(levels)[:, None]
+        up_spec = scale*_planck_like(w)[None, :]
+        dn_spec = 0.5*scale*_planck_like(w)[None, :]
+        first, last = ch.window
+        up, dn = P.reduce_broadband(P.trapezoid(up_spec[:, first:last + 1], dw),
+                                    P.trapezoid(dn_spec[:, first:last + 1], dw))
+        wg = w0 + np.arange(n)*dw
+        want_up = P.trapezoid(scale*_planck_like(wg)[None, :], dw)
+        np.testing.assert_allclose(up, want_up, rtol=1e-12)
+        np.testing.assert_allclose(dn, 0.5*want_up, rtol=1e-12)
+
+        # column sharding: each rank fills its block, rank 0 gathers all 11 columns
+        cols = 11
+        mine = P.shard_columns(cols, world, rank)
+        local = np.array([[c, 10.*c + 1.] for c in mine], dtype=np.float64).reshape(len(mine), 2)
+        allc = P.gather_columns(local, cols)
+        if rank == 0:
+            assert allc.shape == (cols, 2)
+            np.testing.assert_array_equal(allc[:, 0], np.arange(cols))
+            np.testing.assert_array_equal(allc[:, 1], 10.*np.arange(cols) + 1.)
+        else:
+            assert allc is None
+        open(os.path.join(tmp, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_reduce_and_gather_over_gloo(tmp_path):
+    import torch.multiprocessing as mp
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))
+
+
+def test_single_process_reduce_is_the_identity():
+    up, dn = P.reduce_broadband(np.arange(4.), np.arange(4.) + 1.)
+    np.testing.assert_array_equal(up, np.arange(4.))
+    np.testing.assert_array_equal(dn, np.arange(4.) + 1.)
