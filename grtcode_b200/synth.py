@@ -142,6 +142,8 @@ def make_dataset(root: str, w0: float, wn: float, lines: dict[int, int], seed: i
         write_csv(os.path.join(ds.h2o_ctm_dir, "CKDS.csv"), x, [tself, zero, zero], "x,a,b,c")
         write_csv(os.path.join(ds.h2o_ctm_dir, "CKDF.csv"), x, [tfor, zero, zero], "x,a,b,c")
         xo = np.arange(max(w0, 400.), min(wn, 45000.) + 5., 5.)
+        if len(xo) < 2:      # window outside the table's range: two points, as above
+            xo = np.array([w0, wn + 5.])
         o3 = 1e-21*np.exp(-((xo - 1040.)/60.)**2) + 4e-21*np.exp(-((xo - 16600.)/2500.)**2) \
             + 1e-18*np.exp(-((xo - 39000.)/3000.)**2)
         write_csv(ds.o3_ctm, xo, [o3])
