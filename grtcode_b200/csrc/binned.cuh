@@ -1,0 +1,439 @@
+// K3b: the two binned optical-depth methods of the reference,
+//   wavenumber_sweep = calc_optical_depth_bin_sweep  (gas-optics/src/kernels.c:177-304)
+//   line_sweep       = calc_optical_depth_line_sweep (gas-optics/src/kernels.c:308-406)
+// followed by interpolate / interpolate_last_bin (kernels.c:514-581), on the RFM-style two
+// meshes of create_spectral_bins (spectral_bin.c:30-96): 1 cm-1 bins; lines near a bin
+// ("local") are evaluated on every grid point of the bin, lines within 25 bins ("remote")
+// on the bin's three interpolation points, whose sum over all molecules is interpolated
+// quadratically (clamped at zero) onto the grid points.
+//
+// The reference scatters per line (line_sweep, with atomics) or walks bins with per-layer
+// sorted lines (bin_sweep).  Here both are ONE gather kernel: a block owns one (bin, layer),
+// finds -- per molecule, by binary searches in the molecule's centre-sorted lines of that
+// layer -- the index ranges of its local and remote lines, accumulates them in registers /
+// shared memory, interpolates its own three remote sums, adds the continua, CFC and CIA
+// terms and stores tau once.  No atomics on global memory, no second pass over tau.
+//
+// Which lines are local and which remote decides values at the 1e-3 level, so the range
+// logic follows the reference literally, including bracket()'s behaviour when the value
+// lies outside the array (kernel_utils.c:26-76: left = 0, right = size - 1, error ignored
+// by the callers).  Reads of uninitialised or out-of-bounds memory in the reference (empty
+// sub-arrays handed to bracket, bin index n reached by a line at the very end of the grid)
+// have no defined result; this kernel takes the empty range there.
+#pragma once
+#include "voigt.cuh"
+
+namespace grt {
+
+constexpr int kBinThreads = 128;
+constexpr int kNip = 3;                 // spectral_bin-internal.h:30
+
+struct BinGeometry
+{
+    double w0;
+    double wres;
+    unsigned long long num_wpoints;
+    unsigned long long n;               // number of bins
+    int ppb;
+    int last_ppb;
+    int do_interp;
+    int do_last_interp;
+};
+
+struct BinParams
+{
+    LineRec const *recs;                // [layers][num_lines], molecule-major line order
+    double const *vs;                   // [layers][num_lines] centres sorted per (molecule, layer)
+    unsigned const *perm;               // [layers][num_lines] record index of each sorted entry
+    unsigned long long num_lines;
+    int num_slots;
+    unsigned slot_off[GRT_MAX_MOLS + 1];
+    int num_layers;
+    int method;                         // 0 wavenumber_sweep, 1 line_sweep
+    BinGeometry bins;
+    LayerView lay;
+    Tables tab;
+    double *tau;                        // [layers][num_wpoints]
+    unsigned long long *evals;          // Voigt evaluations (bench bookkeeping)
+};
+
+// create_spectral_bins (spectral_bin.c:40-56).
+inline BinGeometry make_bins(double const w0, unsigned long long const n, double const wres,
+                             double const width)
+{
+    BinGeometry b;
+    b.w0 = w0;
+    b.wres = wres;
+    b.num_wpoints = n;
+    b.ppb = (int)(floor(width/wres) + 1);
+    b.do_interp = b.ppb > 3 ? 1 : 0;
+    b.last_ppb = (int)(n % (unsigned long long)b.ppb);
+    b.last_ppb = b.last_ppb == 0 ? b.ppb : b.last_ppb;
+    b.do_last_interp = b.last_ppb > 3 ? 1 : 0;
+    b.n = n/(unsigned long long)b.ppb;
+    if (b.ppb != b.last_ppb) b.n++;
+    return b;
+}
+
+// Left-most grid index of bin i and the number of grid points in it (spectral_bin.c:75-80).
+__device__ __forceinline__ unsigned long long bin_left(BinGeometry const &b, unsigned long long const i)
+{
+    return i*(unsigned long long)b.ppb;
+}
+
+__device__ __forceinline__ int bin_points(BinGeometry const &b, unsigned long long const i)
+{
+    return i < b.n - 1 ? b.ppb : b.last_ppb;
+}
+
+// bins.w[i*NIP + k] (spectral_bin.c:81-83).
+__device__ __forceinline__ double bin_w(BinGeometry const &b, unsigned long long const i, int const k)
+{
+    double const first = __dadd_rn(b.w0, __dmul_rn((double)((unsigned long long)b.ppb*i), b.wres));
+    if (k == 0) return first;
+    double const last = __dadd_rn(first, __dmul_rn((double)(bin_points(b, i) - 1), b.wres));
+    if (k == kNip - 1) return last;
+    return __dmul_rn(0.5, __dadd_rn(first, last));
+}
+
+// bins.w[idx] for a flat index.
+__device__ __forceinline__ double bin_w_flat(BinGeometry const &b, unsigned long long const idx)
+{
+    return bin_w(b, idx/kNip, (int)(idx % kNip));
+}
+
+// bracket (kernel_utils.c:26-76), literally.  Out of range: l = 0, r = size - 1.
+__device__ void bracket_dev(unsigned long long const size, double const *a, double const val,
+                            unsigned long long *left, unsigned long long *right)
+{
+    unsigned long long l = 0;
+    unsigned long long r = size - 1;
+    if (val < a[l] || val > a[r])
+    {
+        *left = l;
+        *right = r;
+        return;
+    }
+    if (a[l] == val)
+    {
+        r = l;
+    }
+    else if (a[r] == val)
+    {
+        l = r;
+    }
+    else
+    {
+        while (r - l > 1)
+        {
+            unsigned long long const mid = l + (r - l)/2;
+            if (a[mid] == val)
+            {
+                l = mid;
+                r = mid;
+                break;
+            }
+            else if (val > a[mid])
+            {
+                l = mid;
+            }
+            else
+            {
+                r = mid;
+            }
+        }
+    }
+    *left = l;
+    *right = r;
+}
+
+// Index ranges [lo, hi) into one molecule's sorted lines of one layer.
+struct BinRanges
+{
+    unsigned long long loc_lo, loc_hi;     // local lines
+    unsigned long long rl_lo, rl_hi;       // remote lines below the local ones
+    unsigned long long rr_lo, rr_hi;       // remote lines above
+};
+
+// calc_optical_depth_bin_sweep's bookkeeping for bin j (kernels.c:195-300).
+__device__ void ranges_bin_sweep(BinGeometry const &b, unsigned long long const j,
+                                 unsigned long long const n, double const *v, BinRanges *out)
+{
+    BinRanges R = {0, 0, 0, 0, 0, 0};
+    unsigned long long const none = ~0ull;
+    unsigned long long nbin = 1;
+    double const leftw = j > nbin ? bin_w_flat(b, kNip*(j - nbin)) : bin_w_flat(b, 0);
+    double const rightw = j >= (b.n - 1) - nbin ? bin_w_flat(b, kNip*b.n - 1)
+                                                : bin_w_flat(b, kNip*(j + nbin + 1) - 1);
+    unsigned long long left = 0;
+    unsigned long long right = 0;
+    bool left_set = false;
+    bool right_set = false;
+    if (leftw <= v[n-1] && rightw >= v[0])
+    {
+        unsigned long long tmp;
+        bracket_dev(n, v, leftw, &left, &tmp);
+        bracket_dev(n - left, v + left, rightw, &tmp, &right);
+        right += left;
+        R.loc_lo = left;
+        R.loc_hi = right + 1;
+        left_set = right_set = true;
+    }
+    else if (leftw > v[n-1])
+    {
+        left = n;
+        left_set = true;
+    }
+    else
+    {
+        right = none;
+        right_set = true;
+    }
+    nbin = 25;
+    double const leftw_r = j > nbin ? bin_w_flat(b, kNip*(j - nbin)) : bin_w_flat(b, 0);
+    if (leftw >= v[0] && leftw_r <= v[n-1] && left_set && left >= 1)
+    {
+        unsigned long long left_r, tmp;
+        bracket_dev(left, v, leftw_r, &left_r, &tmp);
+        R.rl_lo = left_r;
+        R.rl_hi = left;
+    }
+    double const rightw_r = j >= (b.n - 1) - nbin ? bin_w_flat(b, kNip*b.n - 1)
+                                                  : bin_w_flat(b, kNip*(j + nbin + 1) - 1);
+    if (rightw <= v[n-1] && rightw_r >= v[0] && right_set)
+    {
+        unsigned long long const start = right == none ? 0 : right;    // right + f
+        if (start < n)
+        {
+            unsigned long long right_r, tmp;
+            bracket_dev(n - start, v + start, rightw_r, &tmp, &right_r);
+            right_r += start;
+            R.rr_lo = right == none ? 0 : right + 1;
+            R.rr_hi = right_r + 1;
+        }
+    }
+    *out = R;
+}
+
+// calc_optical_depth_line_sweep (kernels.c:322-400) turned around: the lines whose own
+// local / remote bin ranges contain bin k.  Every bound is a monotone function of the
+// line centre, so each set is a contiguous range of the sorted lines.
+__device__ __forceinline__ long long sweep_bin_of(double const w, double const w0, double const bw)
+{
+    return (long long)floor(__ddiv_rn(__dsub_rn(w, w0), bw));
+}
+
+template <typename Pred>
+__device__ unsigned long long first_true(unsigned long long const n, Pred pred)
+{
+    unsigned long long lo = 0, hi = n;      // pred is false ... false true ... true
+    while (lo < hi)
+    {
+        unsigned long long const mid = lo + (hi - lo)/2;
+        if (pred(mid)) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+__device__ void ranges_line_sweep(BinGeometry const &b, unsigned long long const k,
+                                  unsigned long long const n, double const *v, BinRanges *out)
+{
+    double const bw = __dmul_rn(b.wres, (double)b.ppb);
+    double const maxw = __dadd_rn(b.w0, __dmul_rn((double)b.num_wpoints, b.wres));
+    long long const kk = (long long)k;
+    auto lower = [&](double const c, double const cut) -> long long
+    {
+        double w = __dsub_rn(c, cut);
+        if (w < b.w0) w = b.w0;
+        return sweep_bin_of(w, b.w0, bw);
+    };
+    auto upper = [&](double const c, double const cut) -> long long
+    {
+        double w = __dadd_rn(c, cut);
+        if (w > maxw) w = maxw;
+        return sweep_bin_of(w, b.w0, bw);
+    };
+    // local: left(v) <= k <= right(v)
+    unsigned long long const i_lo = first_true(n, [&](unsigned long long i) { return upper(v[i], 1.5) >= kk; });
+    unsigned long long const i_hi = first_true(n, [&](unsigned long long i) { return lower(v[i], 1.5) > kk; });
+    // remote below the line's local bins: left_r(v) <= k < left(v)
+    unsigned long long const j_hi = first_true(n, [&](unsigned long long i) { return lower(v[i], 25.) > kk; });
+    // remote above: right(v) < k <= right_r(v)
+    unsigned long long const j_lo = first_true(n, [&](unsigned long long i) { return upper(v[i], 25.) >= kk; });
+    BinRanges R;
+    R.loc_lo = i_lo;
+    R.loc_hi = i_hi > i_lo ? i_hi : i_lo;
+    R.rl_lo = i_hi;                      // lines with left(v) > k ...
+    R.rl_hi = j_hi > i_hi ? j_hi : i_hi; // ... and left_r(v) <= k
+    R.rr_lo = j_lo;                      // lines with right_r(v) >= k ...
+    R.rr_hi = i_lo > j_lo ? i_lo : j_lo; // ... and right(v) < k
+    *out = R;
+}
+
+// S*N_s*K at one point of one line: rfm_voigt_line_shape for a single abscissa
+// (RFM_voigt.c:97-106 pure Lorentz, :109-278 Voigt) with the scale of kernels.c:459 in c.
+__device__ __forceinline__ double line_point(LineRec const &r, double const inw, double const i_d,
+                                             double const inwres)
+{
+    float const xi = abscissa(inw, i_d, inwres, r.v, (double)r.repwid);
+    if (r.hw0 == kHwLorentz)
+    {
+        return r.c/(double)(xi*xi + r.yq);
+    }
+    return r.c*voigt_core(xi, r.y, r.xlim0, r.xlim1);
+}
+
+// bin_quad_interp (kernel_utils.c:81-103) at grid point j.
+__device__ __forceinline__ double quad_interp(double const *x, double const *y, double const w)
+{
+    double t = (w - x[1])*(w - x[2])*y[0]/((x[0] - x[1])*(x[0] - x[2])) +
+               (w - x[0])*(w - x[2])*y[1]/((x[1] - x[0])*(x[1] - x[2])) +
+               (w - x[0])*(w - x[1])*y[2]/((x[2] - x[0])*(x[2] - x[1]));
+    if (t < 0.) t = 0.;
+    return t;
+}
+
+__global__ void __launch_bounds__(kBinThreads)
+bin_gather_kernel(BinParams const p)
+{
+    extern __shared__ double sh_acc[];          // [points of the bin]
+    __shared__ BinRanges sh_ranges;
+    __shared__ double sh_rem[kNip];
+    __shared__ double sh_warp[kBinThreads/32][kNip];
+    unsigned long long const k = blockIdx.x;
+    int const layer = blockIdx.y;
+    BinGeometry const &b = p.bins;
+    int const npts = bin_points(b, k);
+    unsigned long long const left = bin_left(b, k);
+    int const tid = threadIdx.x;
+    for (int q=tid; q<npts; q+=kBinThreads) sh_acc[q] = 0.;
+    if (tid < kNip) sh_rem[tid] = 0.;
+    double const x[kNip] = {bin_w(b, k, 0), bin_w(b, k, 1), bin_w(b, k, 2)};
+    double const loc_w = __dadd_rn(b.w0, __dmul_rn((double)left, b.wres));
+    double const rem_w = x[0];
+    double const rem_res = __dsub_rn(x[1], x[0]);
+    double rem[kNip] = {0., 0., 0.};
+    unsigned long long evals = 0;
+    // points handled by this thread in the local sweeps: the block is cut into `slots`
+    // groups of `span` threads; group q takes local lines q, q + slots, ...
+    int const span = npts < kBinThreads ? npts : kBinThreads;
+    int const slots = kBinThreads/span;
+    int const my_slot = tid/span;
+    int const my_pt = tid % span;
+    bool const worker = my_slot < slots;
+    __syncthreads();
+
+    for (int s=0; s<p.num_slots; ++s)
+    {
+        unsigned long long const off = p.slot_off[s];
+        unsigned long long const n = p.slot_off[s+1] - off;
+        if (n == 0) continue;
+        double const *v = p.vs + (size_t)layer*p.num_lines + off;
+        unsigned const *perm = p.perm + (size_t)layer*p.num_lines + off;
+        LineRec const *recs = p.recs + (size_t)layer*p.num_lines;
+        if (tid == 0)
+        {
+            if (p.method == 0) ranges_bin_sweep(b, k, n, v, &sh_ranges);
+            else ranges_line_sweep(b, k, n, v, &sh_ranges);
+        }
+        __syncthreads();
+        BinRanges const R = sh_ranges;
+        // local lines on every grid point of the bin
+        if (worker)
+        {
+            for (int pbase=0; pbase<npts; pbase+=span)
+            {
+                int const pt = pbase + my_pt;
+                if (pt >= npts) continue;
+                double a = 0.;
+                for (unsigned long long i=R.loc_lo + my_slot; i<R.loc_hi; i+=slots)
+                {
+                    LineRec const r = recs[perm[i]];
+                    a += line_point(r, loc_w, (double)pt, b.wres);
+                    ++evals;
+                }
+                if (a != 0.) atomicAdd(&sh_acc[pt], a);
+            }
+        }
+        // remote lines on the three interpolation points
+        for (int part=0; part<2; ++part)
+        {
+            unsigned long long const lo = part ? R.rr_lo : R.rl_lo;
+            unsigned long long const hi = part ? R.rr_hi : R.rl_hi;
+            for (unsigned long long i=lo + tid; i<hi; i+=kBinThreads)
+            {
+                LineRec const r = recs[perm[i]];
+#pragma unroll
+                for (int l=0; l<kNip; ++l) rem[l] += line_point(r, rem_w, (double)l, rem_res);
+                evals += kNip;
+            }
+        }
+        __syncthreads();
+    }
+
+    // block sum of the remote contributions
+#pragma unroll
+    for (int l=0; l<kNip; ++l)
+    {
+        double vsum = rem[l];
+        for (int o=16; o>0; o>>=1) vsum += __shfl_down_sync(0xffffffffu, vsum, o);
+        if ((tid & 31) == 0) sh_warp[tid >> 5][l] = vsum;
+    }
+    for (int o=16; o>0; o>>=1) evals += __shfl_down_sync(0xffffffffu, evals, o);
+    if ((tid & 31) == 0 && evals) atomicAdd(p.evals, evals);
+    __syncthreads();
+    if (tid < kNip)
+    {
+        double t = 0.;
+        for (int w=0; w<kBinThreads/32; ++w) t += sh_warp[w][tid];
+        sh_rem[tid] = t;
+    }
+    __syncthreads();
+    double const y[kNip] = {sh_rem[0], sh_rem[1], sh_rem[2]};
+    bool const interp = (k < b.n - 1) ? (b.do_interp != 0) : (b.do_last_interp != 0);
+
+    // interpolate (kernels.c:514-581) + continua, CFCs, CIA (kernels.c:469-510, 585-630)
+    int const L = p.num_layers;
+    for (int q=tid; q<npts; q+=kBinThreads)
+    {
+        unsigned long long const f = left + (unsigned long long)q;
+        double t = sh_acc[q];
+        if (p.tab.h2o_slot >= 0)
+        {
+            double const tref = 296.;
+            double const T = p.lay.tavg[layer];
+            double const Ps = p.lay.ps[p.tab.h2o_slot*L + layer];
+            double const N = p.lay.ns[p.tab.h2o_slot*L + layer];
+            double const P = p.lay.pavg[layer];
+            double const CS = p.tab.h2o[0][f];
+            double const T0 = p.tab.h2o[1][f];
+            double const CF = p.tab.h2o[2][f];
+            double const T0F = p.tab.h2o[3][f];
+            t += N*(tref/T)*((CS*Ps*exp(T0*(tref - T))) + (CF*(P - Ps)*exp(T0F*(tref - T))));
+        }
+        if (p.tab.o3_slot >= 0)
+        {
+            t += p.lay.ns[p.tab.o3_slot*L + layer]*p.tab.o3[f];
+        }
+        for (int c=0; c<p.tab.num_cfcs; ++c)
+        {
+            t += p.lay.cfc[c*L + layer]*p.tab.cfc[c][f];
+        }
+        for (int c=0; c<p.tab.num_cias; ++c)
+        {
+            t += p.lay.cia[c*L + layer]*p.tab.cia[c][f];
+        }
+        if (interp)
+        {
+            double const w = __dadd_rn(b.w0, __dmul_rn((double)f, b.wres));
+            t += quad_interp(x, y, w);
+        }
+        else
+        {
+            t += y[q];       // bin_no_interp (kernel_utils.c:106-118): at most three points
+        }
+        p.tau[(size_t)layer*b.num_wpoints + f] = t;
+    }
+}
+
+}  // namespace grt

@@ -165,6 +165,8 @@ __global__ void column_prep_kernel(int const num_layers, ColumnInputs const in,
 }  // namespace grt
 
 #include "sweep.cuh"
+#include "binned.cuh"
+#include <cub/device/device_segmented_radix_sort.cuh>
 
 namespace grt {
 
@@ -185,7 +187,8 @@ struct PrepStats
 __global__ void __launch_bounds__(256)
 line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay,
                  PrepMeta const meta, double const w0, double const wres, uint64_t const nw,
-                 int const fsteps, LineRec *recs, PrepStats *stats)
+                 int const fsteps, LineRec *recs, PrepStats *stats, double *vkey,
+                 unsigned *vidx)
 {
     uint64_t const j = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     int const i = blockIdx.y;
@@ -282,6 +285,12 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
             r.fc = kSkip;
         }
         recs[(size_t)i*lines.num_lines + j] = r;
+        if (vkey != nullptr)
+        {
+            // sort keys of the binned methods (sort_lines, kernels.c:135-172)
+            vkey[(size_t)i*lines.num_lines + j] = v;
+            vidx[(size_t)i*lines.num_lines + j] = (unsigned)j;
+        }
     }
     // Block-level statistics (bench bookkeeping only).
     __shared__ unsigned long long sh[4];
@@ -356,6 +365,18 @@ struct grt_gas
     unsigned *d_tile_last = nullptr;
     int tiles_pts = 0;                   // PTS the work list was built for
     double tiles_margin = 0.;            // margin [cm-1] it was built with
+    int order_method = -1;               // line order the device list was built for
+    std::vector<unsigned> slot_off;      // molecule segments of the molecule-major order
+    double *d_vkey = nullptr;            // binned methods: centres, sorted centres, permutation
+    double *d_vsorted = nullptr;
+    unsigned *d_vidx = nullptr;
+    unsigned *d_perm = nullptr;
+    int *d_seg_begin = nullptr;
+    int *d_seg_end = nullptr;
+    void *d_sort_temp = nullptr;
+    size_t sort_temp_bytes = 0;
+    size_t binned_capacity = 0;
+    unsigned long long *d_evals = nullptr;
     std::vector<double *> owned_tables;
     uint64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -385,14 +406,29 @@ static int find_slot(grt_gas const *g, int mol_id)
 
 
 // Sort the merged list by base centre and (re)upload it with the TIPS tables.
-static int finalize_lines(grt_gas *g)
+static int finalize_lines(grt_gas *g, int const method)
 {
     GRT_CUDA(cudaSetDevice(g->device));
     uint64_t const n = g->h_v0.size();
     std::vector<uint64_t> order(n);
     std::iota(order.begin(), order.end(), (uint64_t)0);
-    std::stable_sort(order.begin(), order.end(),
-                     [&](uint64_t a, uint64_t b) { return g->h_v0[a] < g->h_v0[b]; });
+    if (method == 2)
+    {
+        // line_sample: one list over all molecules, sorted by centre (tile ranges)
+        std::stable_sort(order.begin(), order.end(),
+                         [&](uint64_t a, uint64_t b) { return g->h_v0[a] < g->h_v0[b]; });
+    }
+    else
+    {
+        // binned methods: molecule-major, file order inside a molecule (the order
+        // sort_lines starts from, kernels.c:135)
+        std::stable_sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b)
+                         { return (g->h_slotiso[a] >> 8) < (g->h_slotiso[b] >> 8); });
+    }
+    g->slot_off.assign((size_t)g->meta.num_slots + 1, 0u);
+    for (uint64_t k=0; k<n; ++k) g->slot_off[(size_t)(g->h_slotiso[k] >> 8) + 1]++;
+    for (int sl=0; sl<g->meta.num_slots; ++sl) g->slot_off[sl+1] += g->slot_off[sl];
+    g->order_method = method;
     std::vector<double> packed(7*n);
     std::vector<uint16_t> si(n);
     double maxd = 0.;
@@ -521,6 +557,101 @@ static int launch_wing(SweepParams const &sp, int const sms, cudaStream_t const 
                  : launch_wing_impl<PTS, NL, false>(sp, sms, st);
 }
 
+// wavenumber_sweep / line_sweep after K0 + K1: per-(molecule, layer) sort of the shifted
+// centres (sort_lines, kernels.c:135-172: stable, ascending), then the gather kernel of
+// binned.cuh.  The radix sort is CUB's (stable); keys are the centres K1 wrote.
+static int binned_optical_depth(grt_gas *g, int const method, LayerView const &lay,
+                                double *tau_dev, int launches)
+{
+    cudaStream_t const st = g->stream;
+    int const L = g->num_layers;
+    uint64_t const N = g->num_lines;
+    GRT_CUDA(cudaEventRecord(g->ev[1], st));
+    if (g->d_evals == nullptr) GRT_CUDA(cudaMalloc(&g->d_evals, sizeof(unsigned long long)));
+    GRT_CUDA(cudaMemsetAsync(g->d_evals, 0, sizeof(unsigned long long), st));
+    int const slots = g->meta.num_slots;
+    if (N > 0)
+    {
+        if ((size_t)N*L > (size_t)INT32_MAX) return fail("too many (line, layer) pairs for the sort");
+        int const segs = slots*L;
+        std::vector<int> begin((size_t)segs), end((size_t)segs);
+        for (int i=0; i<L; ++i)
+        {
+            for (int sl=0; sl<slots; ++sl)
+            {
+                begin[(size_t)i*slots + sl] = (int)((size_t)i*N + g->slot_off[sl]);
+                end[(size_t)i*slots + sl] = (int)((size_t)i*N + g->slot_off[sl+1]);
+            }
+        }
+        cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end);
+        g->d_seg_begin = g->d_seg_end = nullptr;
+        GRT_CUDA(cudaMalloc(&g->d_seg_begin, sizeof(int)*segs));
+        GRT_CUDA(cudaMalloc(&g->d_seg_end, sizeof(int)*segs));
+        GRT_CUDA(cudaMemcpyAsync(g->d_seg_begin, begin.data(), sizeof(int)*segs,
+                                 cudaMemcpyHostToDevice, st));
+        GRT_CUDA(cudaMemcpyAsync(g->d_seg_end, end.data(), sizeof(int)*segs,
+                                 cudaMemcpyHostToDevice, st));
+        GRT_CUDA(cudaStreamSynchronize(st));   // the host vectors go out of scope below
+        size_t bytes = 0;
+        GRT_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(
+            nullptr, bytes, g->d_vkey, g->d_vsorted, g->d_vidx, g->d_perm, (int)(N*L), segs,
+            g->d_seg_begin, g->d_seg_end, 0, 64, st));
+        if (bytes > g->sort_temp_bytes)
+        {
+            cudaFree(g->d_sort_temp);
+            g->d_sort_temp = nullptr;
+            GRT_CUDA(cudaMalloc(&g->d_sort_temp, bytes));
+            g->sort_temp_bytes = bytes;
+        }
+        GRT_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(
+            g->d_sort_temp, bytes, g->d_vkey, g->d_vsorted, g->d_vidx, g->d_perm, (int)(N*L), segs,
+            g->d_seg_begin, g->d_seg_end, 0, 64, st));
+        ++launches;
+    }
+    GRT_CUDA(cudaEventRecord(g->ev[2], st));
+    BinParams bp;
+    bp.recs = g->d_recs;
+    bp.vs = g->d_vsorted;
+    bp.perm = g->d_perm;
+    bp.num_lines = N;
+    bp.num_slots = N > 0 ? slots : 0;
+    for (int sl=0; sl<=GRT_MAX_MOLS; ++sl)
+    {
+        bp.slot_off[sl] = sl < (int)g->slot_off.size() ? g->slot_off[sl] : (unsigned)N;
+    }
+    bp.num_layers = L;
+    bp.method = method;
+    bp.bins = make_bins(g->w0, g->nw, g->dw, 1.);      // bin width of gas_optics.c:73
+    bp.lay = lay;
+    bp.tab = g->tab;
+    bp.tau = tau_dev;
+    bp.evals = g->d_evals;
+    if (bp.bins.n > 0x7fffffffull) return fail("too many spectral bins");
+    dim3 grid((unsigned)bp.bins.n, (unsigned)L);
+    size_t const smem = sizeof(double)*(size_t)bp.bins.ppb;
+    if (smem > 48*1024) return fail("spectral resolution too fine for the binned methods");
+    bin_gather_kernel<<<grid, kBinThreads, smem, st>>>(bp);
+    GRT_CUDA(cudaGetLastError());
+    ++launches;
+    GRT_CUDA(cudaEventRecord(g->ev[3], st));
+    PrepStats hs;
+    unsigned long long evals = 0;
+    GRT_CUDA(cudaMemcpyAsync(&hs, g->d_stats, sizeof(PrepStats), cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaMemcpyAsync(&evals, g->d_evals, sizeof(evals), cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    float ms[3] = {0.f, 0.f, 0.f};
+    for (int k=0; k<3; ++k) GRT_CUDA(cudaEventElapsedTime(&ms[k], g->ev[k], g->ev[k+1]));
+    g->stats[0] = (uint64_t)N*(uint64_t)L;
+    g->stats[1] = evals;
+    g->stats[2] = (uint64_t)launches;
+    g->stats[3] = hs.lorentz;
+    g->stats[4] = (uint64_t)(ms[0]*1e6f);   // K0 + K1 [ns]
+    g->stats[5] = (uint64_t)(ms[2]*1e6f);   // bin gather [ns]
+    g->stats[6] = (uint64_t)(ms[1]*1e6f);   // sort [ns]
+    g->stats[7] = 0;
+    return 0;
+}
+
 extern "C" {
 
 int grt_gas_create(grt_gas **gas, int device, int num_levels, double w0, double dw,
@@ -577,6 +708,8 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_stats);
     cudaFree(g->d_tile_order);
     cudaFree(g->d_work_counter);
+    cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
+    cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_sort_temp); cudaFree(g->d_evals);
     for (double *t : g->owned_tables) cudaFree(t);
     for (int k=0; k<5; ++k) if (g->ev[k]) cudaEventDestroy(g->ev[k]);
     delete g;
@@ -685,13 +818,9 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
                           int method, double *tau_dev)
 {
     if (g == nullptr) return fail("null gas handle");
-    if (method != 2)
-    {
-        return fail("optical depth method %d is not implemented on sm_100a (only line_sample = 2)",
-                    method);
-    }
+    if (method < 0 || method > 2) return fail("unknown optical depth method %d", method);
     GRT_CUDA(cudaSetDevice(g->device));
-    if (g->dirty) GRT_TRY(finalize_lines(g));
+    if (g->dirty || g->order_method != method) GRT_TRY(finalize_lines(g, method));
     int const L = g->num_layers;
     int const levels = g->num_levels;
     cudaStream_t const st = g->stream;
@@ -760,9 +889,26 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
         lv.slotiso = g->d_slotiso;
         lv.num_lines = N;
         dim3 grid((unsigned)((N + 255)/256), (unsigned)L);
+        if (method != 2 && need > g->binned_capacity)
+        {
+            cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
+            g->d_vkey = g->d_vsorted = nullptr;
+            g->d_vidx = g->d_perm = nullptr;
+            GRT_CUDA(cudaMalloc(&g->d_vkey, sizeof(double)*need));
+            GRT_CUDA(cudaMalloc(&g->d_vsorted, sizeof(double)*need));
+            GRT_CUDA(cudaMalloc(&g->d_vidx, sizeof(unsigned)*need));
+            GRT_CUDA(cudaMalloc(&g->d_perm, sizeof(unsigned)*need));
+            g->binned_capacity = need;
+        }
         line_prep_kernel<<<grid, 256, 0, st>>>(lv, L, lay, g->meta, g->w0, g->dw, g->nw, fsteps,
-                                               g->d_recs, g->d_stats);
+                                               g->d_recs, g->d_stats,
+                                               method != 2 ? g->d_vkey : nullptr,
+                                               method != 2 ? g->d_vidx : nullptr);
         ++launches;
+    }
+    if (method != 2)
+    {
+        return binned_optical_depth(g, method, lay, tau_dev, launches);
     }
 
     GRT_CUDA(cudaEventRecord(g->ev[1], st));

@@ -344,12 +344,6 @@ int calculate_optical_depth(GasOptics_t * const gas_optics, fp_t * const pressur
     int same_grids;
     TRY(compare_spectral_grids(&gas_optics->grid, &optics->grid, &same_grids));
     REQUIRE_EQUAL(same_grids, 1);
-    if (gas_optics->optical_depth_method != line_sample)
-    {
-        FAIL(GRTCODE_VALUE_ERR, "optical_depth_method %d is not available on the GPU yet; create"
-             " the gas optics with line_sample (%d), the method every reference driver uses"
-             " (framework/src/driver.c:618).", gas_optics->optical_depth_method, line_sample);
-    }
     fp_t const mbtoatm = 0.000986923f;
     fp_t p[MAX_NUM_LEVELS];
     int i;

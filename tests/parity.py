@@ -30,13 +30,13 @@ def build_dataset(root, w0, wn, lines, seed, cfcs=(), cias=()):
 
 
 def oracle_column(ds, w0, wn, dw, col, molecules, use_ctm=True, threads=None, solvers=True,
-                  line_window=(None, None)):
+                  line_window=(None, None), method=R.LINE_SAMPLE):
     """Reference pipeline on the host: tau_gas, then (optionally) LW + SW fluxes."""
     r = R.Ref(threads=threads)
     g = r.grid(w0, wn, dw)
     levels = len(col.p)
     go = R.RefGasOptics(r, levels, g, ds.hitran, ds.h2o_ctm_dir if use_ctm else None,
-                        ds.o3_ctm if use_ctm else None)
+                        ds.o3_ctm if use_ctm else None, method=method)
     for m in molecules:
         go.add_molecule(m, *line_window)
     for c, path in ds.cfc.items():
@@ -76,12 +76,12 @@ def oracle_column(ds, w0, wn, dw, col, molecules, use_ctm=True, threads=None, so
 
 
 def gpu_column(ds, w0, wn, dw, col, molecules, use_ctm=True, solvers=True, device=0,
-               line_window=(None, None)):
+               line_window=(None, None), method=api.LINE_SAMPLE):
     """Same pipeline through libgrtcode.so (the reference's C API on the GPU)."""
     g = api.spectral_grid(w0, wn, dw)
     levels = len(col.p)
     go = api.GasOptics(levels, g, ds.hitran, ds.h2o_ctm_dir if use_ctm else None,
-                       ds.o3_ctm if use_ctm else None, device=device)
+                       ds.o3_ctm if use_ctm else None, device=device, method=method)
     for m in molecules:
         go.add_molecule(m, *line_window)
     for c, path in ds.cfc.items():

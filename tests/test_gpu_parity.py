@@ -121,3 +121,30 @@ def test_spectral_split_reproduces_the_unsplit_column(built, tmp_path):
     assert np.abs(total["lw"][1] - bb(want["lw_dn"])).max() <= FLUX_ATOL
     assert np.abs(total["sw"][0] - bb(want["sw_up"])).max() <= FLUX_ATOL
     assert np.abs(total["sw"][1] - bb(want["sw_dn"])).max() <= FLUX_ATOL
+
+
+@pytest.mark.parametrize("method", [0, 1, None], ids=["wavenumber_sweep", "line_sweep", "default"])
+@pytest.mark.parametrize("case", ["dense", "sparse"])
+def test_binned_methods(built, tmp_path, method, case):
+    """wavenumber_sweep (the library default, optical_depth_method = NULL) and line_sweep
+    (kernels.c:177-406 + interpolate, :514-581) against the reference on the same inputs;
+    "sparse" has molecules with a handful of lines, which exercises bracket()'s
+    out-of-range returns (kernel_utils.c:36-41)."""
+    if case == "dense":
+        lines = {synth.H2O: 1500, synth.CO2: 2500, synth.O3: 1500}
+        w0, wn, dw, levels = 400., 900., 0.1, 18
+    else:
+        lines = {synth.H2O: 40, synth.CO: 5, synth.O2: 12}
+        w0, wn, dw, levels = 1000., 1400., 0.05, 10
+    ds = parity.build_dataset(str(tmp_path), w0, wn, lines, 31)
+    rng = np.random.default_rng(31)
+    mols = tuple(lines)
+    col = synth.make_column(levels, rng, molecules=mols)
+    want = parity.oracle_column(ds, w0, wn, dw, col, mols, solvers=False, method=method)
+    got = parity.gpu_column(ds, w0, wn, dw, col, mols, solvers=False, method=method)
+    rel = parity.relative_error(got["tau"], want["tau"])
+    bad = int((rel > TAU_RTOL).sum())
+    where = np.unravel_index(int(rel.argmax()), rel.shape)
+    print(f"method {method} {case}: tau max rel {rel.max():.3e} at {where}; {bad} points > 1e-9; "
+          f"stats {got['stats']}")
+    assert rel.max() <= TAU_RTOL
