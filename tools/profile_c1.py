@@ -10,7 +10,8 @@ lines = {1: int(100000*scale), 2: int(300000*scale), 3: int(250000*scale)}
 ds = synth.make_dataset("/tmp/c1_%g" % scale, 1., 3000., lines, seed=1)
 g = api.spectral_grid(1., 3000., 0.1)
 col = synth.make_column(60, np.random.default_rng(1))
-go = api.GasOptics(60, g, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm)
+method = int(os.environ.get("GRT_METHOD", "2"))
+go = api.GasOptics(60, g, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm, method=method)
 for m in (1, 2, 3):
     go.add_molecule(m)
     go.set_ppmv("mol", m, col.ppmv[m])
