@@ -223,6 +223,52 @@ def workload_config(args, lw, sw, layers):
             "l2": "inputs larger than L2 (line records + tau > 2 GB per band)"}
 
 
+def rfmip_probe(args, bands2, device, rank, world, barrier, stream, torch, dist, ncols: int = 4):
+    """Secondary figure, BASELINE config 3 shape: RFMIP-IRF-like columns (61 levels, LW 1-3250
+    + SW 1-50000 cm-1 at 0.1 cm-1, the same synthetic line lists as config 2), `ncols` columns
+    per rank, end to end through the C API (host arrays in, broadband fluxes out).  Columns
+    are sharded over the ranks with no collective; columns/s is the whole-job figure."""
+    from grtcode_b200 import synth
+    from grtcode_b200 import workloads as W
+    from grtcode_b200.column_engine import ColumnEngine
+    if os.environ.get("GRT_BENCH_RFMIP", "1") == "0":
+        return None
+    lw3, sw3 = W.circ1_bands(0.1, args.scale)
+    lw3.dataset, sw3.dataset = bands2[0].dataset, bands2[1].dataset
+    cfcs = tuple(bands2[0].dataset.cfc.keys())
+
+    def column(site: int, expt: int):
+        rng = np.random.default_rng(7000 + site)
+        scale = (1., 4., 0.5, 2., 3., 8.)[expt % 6]
+        return synth.make_column(61, rng, molecules=W.MOLECULES, cfcs=cfcs, co2_scale=scale,
+                                 dt=4.*(expt % 3 - 1))
+
+    eng = ColumnEngine((lw3, sw3), column(0, 0), device, W.MOLECULES)
+    eng.step(column(rank, 0), upload_surface=True)
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    samples = 0
+    for k in range(ncols):
+        out = eng.step(column(100*rank + k, k), upload_surface=True)
+        samples += sum(out[n][2]["samples"] for n in ("lw", "sw"))
+    e1.record(stream)
+    barrier()
+    secs = e0.elapsed_time(e1)*1e-3
+    if world > 1:
+        t = torch.tensor([secs], device=f"cuda:{device}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        secs = float(t.item())
+    eng.close()
+    return {"columns_per_s": world*ncols/secs, "ms_per_column_per_gpu": 1e3*secs/ncols,
+            "columns_timed_per_gpu": ncols, "voigt_samples_per_column": samples//ncols,
+            "config": "BASELINE config 3 shape: 61 levels, LW 1-3250 (n=32491) + SW 1-50000 "
+                      "(n=499991) at 0.1 cm-1, 7 molecules + continua + 3 CIA + 3 CFCs, "
+                      "columns sharded over the GPUs, no collective",
+            "seconds_for_1800_columns": 1800.*secs/(world*ncols)}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -311,6 +357,8 @@ def run_ours(args):
     secs_e2e, _, _, _, out_e2e = timed(True, 200)
     h2d, d2h = eng.h2d, eng.d2h
 
+    rfmip = rfmip_probe(args, (lw, sw), device, rank, world, barrier, stream, torch, dist)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -348,6 +396,7 @@ def run_ours(args):
             "roofline": roofline,
             "voigt_samples_per_step": samples_step,
             "setup_s": t_setup,
+            "rfmip": rfmip,
             "fluxes_W_m2": {"lw_up_toa": float(out["lw"][0][0]), "lw_dn_sfc": float(out["lw"][1][-1]),
                             "sw_up_toa": float(out["sw"][0][0]), "sw_dn_sfc": float(out["sw"][1][-1])}}
     if world == 1 and not args.no_cpu_baseline:

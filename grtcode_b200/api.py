@@ -147,6 +147,8 @@ def load():
     _cuda.grt_synchronize.argtypes = [C.c_int]
     _cuda.grt_selftest_arithmetic.argtypes = [C.c_int, C.c_ulonglong, C.c_ulonglong,
                                               C.POINTER(C.c_ulonglong)]
+    _cuda.grt_selftest_voigt.argtypes = [C.c_int, C.c_ulonglong, C.c_ulonglong,
+                                         C.POINTER(C.c_ulonglong)]
     _cuda.grt_stream_handle.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     _cuda.grt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
     _cuda.grt_host_free.argtypes = [C.c_void_p]
@@ -204,6 +206,13 @@ def selftest_arithmetic(n: int, seed: int = 1, device: int = 0) -> int:
     bad = C.c_ulonglong(0)
     if cuda_layer().grt_selftest_arithmetic(device, n, seed, C.byref(bad)) != 0:
         raise RuntimeError("grt_selftest_arithmetic failed")
+    return int(bad.value)
+
+
+def selftest_voigt(n: int, seed: int = 1, device: int = 0) -> int:
+    bad = C.c_ulonglong(0)
+    if cuda_layer().grt_selftest_voigt(device, n, seed, C.byref(bad)) != 0:
+        raise RuntimeError("grt_selftest_voigt failed")
     return int(bad.value)
 
 

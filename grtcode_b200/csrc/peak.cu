@@ -128,3 +128,54 @@ extern "C" int grt_selftest_arithmetic(int device, unsigned long long n, unsigne
     GRT_CUDA(cudaFree(d));
     return 0;
 }
+
+
+// ---- self-test: the per-line Voigt evaluation (hoisted constants, packed CPF12, exact
+// division without the slow path) against the straight restatement voigt_core -----------
+namespace grt {
+
+__global__ void selftest_voigt_kernel(unsigned long long n, unsigned long long seed,
+                                      unsigned long long *bad)
+{
+    unsigned long long i = (unsigned long long)blockIdx.x*blockDim.x + threadIdx.x;
+    unsigned long long local = 0;
+    for (; i<n; i+=(unsigned long long)gridDim.x*blockDim.x)
+    {
+        unsigned long long z = seed + i*0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30))*0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27))*0x94D049BB133111EBull;
+        z ^= z >> 31;
+        // Y log-uniform over [1e-7, 70], x uniform over [-1.2 XLIM0, 1.2 XLIM0]
+        float const u = (float)(z & 0xffffffu)*(1.f/16777216.f);
+        float const w = (float)((z >> 24) & 0xffffffu)*(1.f/16777216.f);
+        float const y = exp2f(-23.f + 29.1f*u);
+        float xlim0, xlim1;
+        voigt_limits(y, &xlim0, &xlim1);
+        float x = (2.f*w - 1.f)*1.2f*xlim0;
+        if ((z >> 48) & 1) x *= 0.1f;                 // half of the samples near the centre
+        VoigtLine line;
+        voigt_line_init(line, y, xlim0, xlim1);
+        double const a = voigt_line_eval(line, x);
+        double const b = voigt_core(x, y, xlim0, xlim1);
+        if (__double_as_longlong(a) != __double_as_longlong(b)) ++local;
+    }
+    if (local) atomicAdd(bad, local);
+}
+
+}  // namespace grt
+
+extern "C" int grt_selftest_voigt(int device, unsigned long long n, unsigned long long seed,
+                                  unsigned long long *mismatches)
+{
+    cudaStream_t st;
+    GRT_TRY(grt::stream_of(device, &st));
+    unsigned long long *d;
+    GRT_CUDA(cudaMalloc(&d, sizeof(*d)));
+    GRT_CUDA(cudaMemsetAsync(d, 0, sizeof(*d), st));
+    grt::selftest_voigt_kernel<<<grt::sm_count(device)*8, 256, 0, st>>>(n, seed, d);
+    GRT_CUDA(cudaGetLastError());
+    GRT_CUDA(cudaMemcpyAsync(mismatches, d, sizeof(*d), cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    GRT_CUDA(cudaFree(d));
+    return 0;
+}

@@ -783,6 +783,8 @@ core_sweep_kernel(SweepParams const p)
     int const h = hd < (double)(2*F + 2) ? (int)hd : 2*F + 2;
     double const dwno = __dadd_rn(__dmul_rn((double)s, p.wres), p.w0);
     double *tau = p.tau + (size_t)layer*p.nw;
+    VoigtLine line;
+    voigt_line_init(line, y, xlim0, xlim1);
     for (int d=0; d<=h; ++d)
     {
 #pragma unroll
@@ -793,7 +795,7 @@ core_sweep_kernel(SweepParams const p)
             float const xi = abscissa(dwno, (double)(f - s), p.wres, vc.x, repwid);
             if (flagged || fabsf(xi) < xlim1)
             {
-                double const k = voigt_core(xi, y, xlim0, xlim1);
+                double const k = voigt_line_eval(line, xi);
                 atomicAdd(&tau[f], vc.y*k);
             }
         }

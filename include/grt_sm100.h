@@ -146,6 +146,11 @@ int grt_measure_fma_peak(int device, double *fp64_tflops, double *fp32_tflops);
  * operations on n pseudo-random operands; *mismatches must come back 0. */
 int grt_selftest_arithmetic(int device, unsigned long long n, unsigned long long seed,
                             unsigned long long *mismatches);
+/* The per-line Voigt evaluation of the line-core kernel (hoisted per-line polynomials,
+ * packed CPF12 sums) against the sample-by-sample restatement of RFM_voigt.c:109-277 on n
+ * pseudo-random (x, Y) pairs over all regions; *mismatches (bit-level) must come back 0. */
+int grt_selftest_voigt(int device, unsigned long long n, unsigned long long seed,
+                       unsigned long long *mismatches);
 
 #ifdef __cplusplus
 }
