@@ -99,16 +99,24 @@ class ColumnEngine:
             h2d += 8*self.levels*(2 + 53 + 21 + 2)
             name = part["band"].name[:2]
             if name == "lw":
-                emis = part["emis"] if upload_surface else None
+                send = upload_surface
+                if part["emis"][0] != col.emissivity:      # grey surface of this column
+                    part["emis"][:] = col.emissivity
+                    send = True
                 up, dn = part["solver"].column(part["gas"], col.p, col.t_surf, col.t_layer,
-                                               col.t, emis, window=part["window"])
-                h2d += 8*part["n"] if upload_surface else 0
-            else:
-                alb = part["alb"] if upload_surface else None
-                up, dn = part["solver"].column(part["gas"], col.p, col.mu0, 0.5, alb, alb,
-                                               col.tsi, part["solar"] if upload_surface else None,
+                                               col.t, part["emis"] if send else None,
                                                window=part["window"])
-                h2d += 2*8*part["n"] if upload_surface else 0
+                h2d += 8*part["n"] if send else 0
+            else:
+                send = upload_surface
+                if part["alb"][0] != col.albedo:
+                    part["alb"][:] = col.albedo
+                    send = True
+                alb = part["alb"] if send else None
+                up, dn = part["solver"].column(part["gas"], col.p, col.mu0, 0.5, alb, alb,
+                                               col.tsi, part["solar"] if send else None,
+                                               window=part["window"])
+                h2d += 2*8*part["n"] if send else 0
             launches += 1
             out[name] = (up, dn, st)
         self.launches = launches

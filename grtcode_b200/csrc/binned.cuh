@@ -280,6 +280,12 @@ __device__ __forceinline__ double line_point(LineRec const &r, double const inw,
     {
         return r.c/(double)(xi*xi + r.yq);
     }
+    float const ax = fabsf(xi);
+    if (ax >= r.xlim0 && r.hw0 != kHwCoreOnly)
+    {
+        // far wing (RFM_voigt.c:168-171): almost every remote sample
+        return r.c*(double)div_exact(r.yrrtpi, ax*ax + r.yq);
+    }
     return r.c*voigt_core(xi, r.y, r.xlim0, r.xlim1);
 }
 
