@@ -155,6 +155,13 @@ struct BinRanges
     unsigned long long rr_lo, rr_hi;       // remote lines above
 };
 
+struct BinRanges32
+{
+    unsigned loc_lo, loc_hi, rl_lo, rl_hi, rr_lo, rr_hi;
+};
+
+constexpr int kBinGroup = 8;            // bins per gather block
+
 // calc_optical_depth_bin_sweep's bookkeeping for bin j (kernels.c:195-300).
 __device__ void ranges_bin_sweep(BinGeometry const &b, unsigned long long const j,
                                  unsigned long long const n, double const *v, BinRanges *out)
@@ -299,111 +306,166 @@ __device__ __forceinline__ double quad_interp(double const *x, double const *y, 
     return t;
 }
 
-__global__ void __launch_bounds__(kBinThreads)
-bin_gather_kernel(BinParams const p)
+// Ranges of every (layer, bin, molecule), one thread each: the binary searches are serial
+// chains of dependent loads, so they are spread over as many threads as there are triples
+// instead of being walked by one thread of the gather block.
+__global__ void __launch_bounds__(128)
+bin_ranges_kernel(BinParams const p, BinRanges32 *out)
 {
-    extern __shared__ double sh_acc[];          // [points of the bin]
-    __shared__ BinRanges sh_ranges;
-    __shared__ double sh_rem[kNip];
-    __shared__ double sh_warp[kBinThreads/32][kNip];
-    unsigned long long const k = blockIdx.x;
-    int const layer = blockIdx.y;
+    unsigned long long const idx = (unsigned long long)blockIdx.x*blockDim.x + threadIdx.x;
+    int const S = p.num_slots;
+    unsigned long long const total = (unsigned long long)p.num_layers*p.bins.n*(unsigned long long)S;
+    if (idx >= total) return;
+    int const s = (int)(idx % (unsigned long long)S);
+    unsigned long long const k = (idx/(unsigned long long)S) % p.bins.n;
+    int const layer = (int)(idx/((unsigned long long)S*p.bins.n));
+    unsigned long long const off = p.slot_off[s];
+    unsigned long long const n = p.slot_off[s+1] - off;
+    BinRanges R = {0, 0, 0, 0, 0, 0};
+    if (n > 0)
+    {
+        double const *v = p.vs + (size_t)layer*p.num_lines + off;
+        if (p.method == 0) ranges_bin_sweep(p.bins, k, n, v, &R);
+        else ranges_line_sweep(p.bins, k, n, v, &R);
+    }
+    BinRanges32 r;
+    r.loc_lo = (unsigned)R.loc_lo; r.loc_hi = (unsigned)R.loc_hi;
+    r.rl_lo = (unsigned)R.rl_lo; r.rl_hi = (unsigned)R.rl_hi;
+    r.rr_lo = (unsigned)R.rr_lo; r.rr_hi = (unsigned)R.rr_hi;
+    out[idx] = r;
+}
+
+// A block owns kBinGroup consecutive bins of one layer.  Remote lines of neighbouring bins
+// are almost the same set (25 bins either side), so each record is loaded once per group
+// and evaluated on the three interpolation points of every bin of the group it is remote
+// to; local lines are swept bin by bin over the bin's grid points.
+__global__ void __launch_bounds__(kBinThreads)
+bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
+{
+    extern __shared__ double sh_acc[];          // [kBinGroup][points per bin]
+    __shared__ BinRanges32 sh_ranges[kBinGroup];
+    __shared__ double sh_rem[kBinGroup][kNip];
+    __shared__ double sh_warp[kBinThreads/32][kBinGroup*kNip];
     BinGeometry const &b = p.bins;
-    int const npts = bin_points(b, k);
-    unsigned long long const left = bin_left(b, k);
+    unsigned long long const k0 = (unsigned long long)blockIdx.x*kBinGroup;
+    int const ng = (int)((b.n - k0) < (unsigned long long)kBinGroup ? (b.n - k0) : kBinGroup);
+    int const layer = blockIdx.y;
     int const tid = threadIdx.x;
-    for (int q=tid; q<npts; q+=kBinThreads) sh_acc[q] = 0.;
-    if (tid < kNip) sh_rem[tid] = 0.;
-    double const x[kNip] = {bin_w(b, k, 0), bin_w(b, k, 1), bin_w(b, k, 2)};
-    double const loc_w = __dadd_rn(b.w0, __dmul_rn((double)left, b.wres));
-    double const rem_w = x[0];
-    double const rem_res = __dsub_rn(x[1], x[0]);
-    double rem[kNip] = {0., 0., 0.};
+    int const ppb = b.ppb;
+    for (int q=tid; q<kBinGroup*ppb; q+=kBinThreads) sh_acc[q] = 0.;
+    double rem[kBinGroup][kNip];
+    double rem_w[kBinGroup], rem_res[kBinGroup];
+#pragma unroll
+    for (int g=0; g<kBinGroup; ++g)
+    {
+        unsigned long long const k = g < ng ? k0 + g : k0;
+        rem_w[g] = bin_w(b, k, 0);
+        rem_res[g] = __dsub_rn(bin_w(b, k, 1), rem_w[g]);
+#pragma unroll
+        for (int l=0; l<kNip; ++l) rem[g][l] = 0.;
+    }
     unsigned long long evals = 0;
-    // points handled by this thread in the local sweeps: the block is cut into `slots`
-    // groups of `span` threads; group q takes local lines q, q + slots, ...
-    int const span = npts < kBinThreads ? npts : kBinThreads;
-    int const slots = kBinThreads/span;
-    int const my_slot = tid/span;
-    int const my_pt = tid % span;
-    bool const worker = my_slot < slots;
-    __syncthreads();
+    LineRec const *recs = p.recs + (size_t)layer*p.num_lines;
 
     for (int s=0; s<p.num_slots; ++s)
     {
         unsigned long long const off = p.slot_off[s];
-        unsigned long long const n = p.slot_off[s+1] - off;
-        if (n == 0) continue;
-        double const *v = p.vs + (size_t)layer*p.num_lines + off;
+        if (p.slot_off[s+1] == off) continue;
         unsigned const *perm = p.perm + (size_t)layer*p.num_lines + off;
-        LineRec const *recs = p.recs + (size_t)layer*p.num_lines;
-        if (tid == 0)
+        __syncthreads();
+        if (tid < ng)
         {
-            if (p.method == 0) ranges_bin_sweep(b, k, n, v, &sh_ranges);
-            else ranges_line_sweep(b, k, n, v, &sh_ranges);
+            sh_ranges[tid] = ranges[((size_t)layer*b.n + (k0 + tid))*p.num_slots + s];
         }
         __syncthreads();
-        BinRanges const R = sh_ranges;
-        // local lines on every grid point of the bin
-        if (worker)
+        // remote lines: union of the group's ranges, one record load per line
+        unsigned ulo = 0xffffffffu, uhi = 0;
+        for (int g=0; g<ng; ++g)
         {
+            BinRanges32 const &R = sh_ranges[g];
+            if (R.rl_hi > R.rl_lo) { ulo = min(ulo, R.rl_lo); uhi = max(uhi, R.rl_hi); }
+            if (R.rr_hi > R.rr_lo) { ulo = min(ulo, R.rr_lo); uhi = max(uhi, R.rr_hi); }
+        }
+        for (unsigned i=ulo + tid; i<uhi; i+=kBinThreads)
+        {
+            LineRec const r = recs[perm[i]];
+#pragma unroll
+            for (int g=0; g<kBinGroup; ++g)
+            {
+                if (g >= ng) break;
+                BinRanges32 const &R = sh_ranges[g];
+                if ((i >= R.rl_lo && i < R.rl_hi) || (i >= R.rr_lo && i < R.rr_hi))
+                {
+#pragma unroll
+                    for (int l=0; l<kNip; ++l)
+                    {
+                        rem[g][l] += line_point(r, rem_w[g], (double)l, rem_res[g]);
+                    }
+                    evals += kNip;
+                }
+            }
+        }
+        // local lines of every bin of the group on the bin's grid points
+        for (int g=0; g<ng; ++g)
+        {
+            BinRanges32 const R = sh_ranges[g];
+            unsigned long long const k = k0 + g;
+            int const npts = bin_points(b, k);
+            double const loc_w = __dadd_rn(b.w0, __dmul_rn((double)bin_left(b, k), b.wres));
+            int const span = npts < kBinThreads ? npts : kBinThreads;
+            int const slots = kBinThreads/span;
+            int const my_slot = tid/span;
+            int const my_pt = tid % span;
+            if (my_slot >= slots) continue;
             for (int pbase=0; pbase<npts; pbase+=span)
             {
                 int const pt = pbase + my_pt;
                 if (pt >= npts) continue;
                 double a = 0.;
-                for (unsigned long long i=R.loc_lo + my_slot; i<R.loc_hi; i+=slots)
+                for (unsigned i=R.loc_lo + my_slot; i<R.loc_hi; i+=slots)
                 {
                     LineRec const r = recs[perm[i]];
                     a += line_point(r, loc_w, (double)pt, b.wres);
                     ++evals;
                 }
-                if (a != 0.) atomicAdd(&sh_acc[pt], a);
+                if (a != 0.) atomicAdd(&sh_acc[g*ppb + pt], a);
             }
         }
-        // remote lines on the three interpolation points
-        for (int part=0; part<2; ++part)
-        {
-            unsigned long long const lo = part ? R.rr_lo : R.rl_lo;
-            unsigned long long const hi = part ? R.rr_hi : R.rl_hi;
-            for (unsigned long long i=lo + tid; i<hi; i+=kBinThreads)
-            {
-                LineRec const r = recs[perm[i]];
-#pragma unroll
-                for (int l=0; l<kNip; ++l) rem[l] += line_point(r, rem_w, (double)l, rem_res);
-                evals += kNip;
-            }
-        }
-        __syncthreads();
     }
 
-    // block sum of the remote contributions
+    // block sums of the remote contributions
 #pragma unroll
-    for (int l=0; l<kNip; ++l)
+    for (int g=0; g<kBinGroup; ++g)
     {
-        double vsum = rem[l];
-        for (int o=16; o>0; o>>=1) vsum += __shfl_down_sync(0xffffffffu, vsum, o);
-        if ((tid & 31) == 0) sh_warp[tid >> 5][l] = vsum;
+#pragma unroll
+        for (int l=0; l<kNip; ++l)
+        {
+            double vsum = rem[g][l];
+            for (int o=16; o>0; o>>=1) vsum += __shfl_down_sync(0xffffffffu, vsum, o);
+            if ((tid & 31) == 0) sh_warp[tid >> 5][g*kNip + l] = vsum;
+        }
     }
     for (int o=16; o>0; o>>=1) evals += __shfl_down_sync(0xffffffffu, evals, o);
     if ((tid & 31) == 0 && evals) atomicAdd(p.evals, evals);
     __syncthreads();
-    if (tid < kNip)
+    if (tid < kBinGroup*kNip)
     {
         double t = 0.;
         for (int w=0; w<kBinThreads/32; ++w) t += sh_warp[w][tid];
-        sh_rem[tid] = t;
+        sh_rem[tid/kNip][tid % kNip] = t;
     }
     __syncthreads();
-    double const y[kNip] = {sh_rem[0], sh_rem[1], sh_rem[2]};
-    bool const interp = (k < b.n - 1) ? (b.do_interp != 0) : (b.do_last_interp != 0);
 
     // interpolate (kernels.c:514-581) + continua, CFCs, CIA (kernels.c:469-510, 585-630)
     int const L = p.num_layers;
-    for (int q=tid; q<npts; q+=kBinThreads)
+    for (int q=tid; q<ng*ppb; q+=kBinThreads)
     {
-        unsigned long long const f = left + (unsigned long long)q;
-        double t = sh_acc[q];
+        int const g = q/ppb;
+        int const pt = q % ppb;
+        unsigned long long const k = k0 + g;
+        if (pt >= bin_points(b, k)) continue;
+        unsigned long long const f = bin_left(b, k) + (unsigned long long)pt;
+        double t = sh_acc[g*ppb + pt];
         if (p.tab.h2o_slot >= 0)
         {
             double const tref = 296.;
@@ -429,14 +491,17 @@ bin_gather_kernel(BinParams const p)
         {
             t += p.lay.cia[c*L + layer]*p.tab.cia[c][f];
         }
+        bool const interp = (k < b.n - 1) ? (b.do_interp != 0) : (b.do_last_interp != 0);
+        double const y[kNip] = {sh_rem[g][0], sh_rem[g][1], sh_rem[g][2]};
         if (interp)
         {
+            double const x[kNip] = {bin_w(b, k, 0), bin_w(b, k, 1), bin_w(b, k, 2)};
             double const w = __dadd_rn(b.w0, __dmul_rn((double)f, b.wres));
             t += quad_interp(x, y, w);
         }
         else
         {
-            t += y[q];       // bin_no_interp (kernel_utils.c:106-118): at most three points
+            t += y[pt];      // bin_no_interp (kernel_utils.c:106-118): at most three points
         }
         p.tau[(size_t)layer*b.num_wpoints + f] = t;
     }

@@ -377,6 +377,8 @@ struct grt_gas
     size_t sort_temp_bytes = 0;
     size_t binned_capacity = 0;
     unsigned long long *d_evals = nullptr;
+    void *d_ranges = nullptr;            // BinRanges32[layers][bins][slots]
+    size_t ranges_capacity = 0;
     std::vector<double *> owned_tables;
     uint64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -627,10 +629,24 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
     bp.tau = tau_dev;
     bp.evals = g->d_evals;
     if (bp.bins.n > 0x7fffffffull) return fail("too many spectral bins");
-    dim3 grid((unsigned)bp.bins.n, (unsigned)L);
-    size_t const smem = sizeof(double)*(size_t)bp.bins.ppb;
-    if (smem > 48*1024) return fail("spectral resolution too fine for the binned methods");
-    bin_gather_kernel<<<grid, kBinThreads, smem, st>>>(bp);
+    size_t const smem = sizeof(double)*(size_t)bp.bins.ppb*kBinGroup;
+    if (smem > 40*1024) return fail("spectral resolution too fine for the binned methods");
+    size_t const nranges = (size_t)L*bp.bins.n*(size_t)std::max(bp.num_slots, 1);
+    if (nranges > g->ranges_capacity)
+    {
+        cudaFree(g->d_ranges);
+        g->d_ranges = nullptr;
+        GRT_CUDA(cudaMalloc(&g->d_ranges, sizeof(BinRanges32)*nranges));
+        g->ranges_capacity = nranges;
+    }
+    if (bp.num_slots > 0)
+    {
+        bin_ranges_kernel<<<(unsigned)((nranges + 127)/128), 128, 0, st>>>(
+            bp, (BinRanges32 *)g->d_ranges);
+        ++launches;
+    }
+    dim3 grid((unsigned)((bp.bins.n + kBinGroup - 1)/kBinGroup), (unsigned)L);
+    bin_gather_kernel<<<grid, kBinThreads, smem, st>>>(bp, (BinRanges32 const *)g->d_ranges);
     GRT_CUDA(cudaGetLastError());
     ++launches;
     GRT_CUDA(cudaEventRecord(g->ev[3], st));
@@ -709,7 +725,7 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_tile_order);
     cudaFree(g->d_work_counter);
     cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
-    cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_sort_temp); cudaFree(g->d_evals);
+    cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_sort_temp); cudaFree(g->d_evals); cudaFree(g->d_ranges);
     for (double *t : g->owned_tables) cudaFree(t);
     for (int k=0; k<5; ++k) if (g->ev[k]) cudaEventDestroy(g->ev[k]);
     delete g;

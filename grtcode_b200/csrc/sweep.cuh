@@ -372,6 +372,9 @@ __device__ __forceinline__ void line_far_edge(LineRec const *rec, TileCtx const 
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
+        // a pair of chunks wholly beyond the window end: nothing to do (warp-uniform)
+        int const cb = t.warp_base + 32*j;
+        if (cb + 63 < s || cb > e) continue;
         f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
         f32x2 const k = far_wing2(mul2_unfused(xi, xi), yq2, yr2);
         float k0, k1;
@@ -415,6 +418,7 @@ __device__ __forceinline__ void line_near(LineRec const *rec, TileCtx const &t,
     for (int j=0; j<PTS; j+=2)
     {
         int const cb = t.warp_base + 32*j;            // the pair covers [cb, cb + 63]
+        if (cb + 63 < s || cb > e) continue;          // wholly outside the window
         int const dlo = max(max(cb - fc, fc - (cb + 63)), 0);
         int const dhi = max(fc - cb, cb + 63 - fc);
         int const fa = f0 + 32*j;
