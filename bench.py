@@ -250,9 +250,14 @@ def rfmip_probe(args, bands2, device, rank, world, barrier, stream, torch, dist,
     barrier()
     e0.record(stream)
     samples = 0
+    kern = {}
     for k in range(ncols):
         out = eng.step(column(100*rank + k, k), upload_surface=True)
         samples += sum(out[n][2]["samples"] for n in ("lw", "sw"))
+        for n in ("lw", "sw"):
+            for key in ("prep_ns", "wing_ns", "core_ns"):
+                name = f"{n}_{key[:-3]}"
+                kern[name] = kern.get(name, 0.) + out[n][2][key]*1e-6/ncols
     e1.record(stream)
     barrier()
     secs = e0.elapsed_time(e1)*1e-3
@@ -263,6 +268,7 @@ def rfmip_probe(args, bands2, device, rank, world, barrier, stream, torch, dist,
     eng.close()
     return {"columns_per_s": world*ncols/secs, "ms_per_column_per_gpu": 1e3*secs/ncols,
             "columns_timed_per_gpu": ncols, "voigt_samples_per_column": samples//ncols,
+            "kernel_ms_per_column": {k: round(v, 3) for k, v in kern.items()},
             "config": "BASELINE config 3 shape: 61 levels, LW 1-3250 (n=32491) + SW 1-50000 "
                       "(n=499991) at 0.1 cm-1, 7 molecules + continua + 3 CIA + 3 CFCs, "
                       "columns sharded over the GPUs, no collective",

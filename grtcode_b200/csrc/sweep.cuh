@@ -106,8 +106,8 @@ __device__ __forceinline__ double fast_rcp_of_float(float const d_f)
 
 
 // Per-warp cache of the sample abscissae for kernels without the shared-memory table:
-// t2[j] = fl(dwno(s) + fl(i*wres)) for the lane's PTS points and the window start s it
-// was computed for.  (Empty for TBL kernels, which rebuild t2 from the table per line:
+// t2[j] = fl(dwno(s) + fl(i*wres)) for the lane's PTS points, keyed by the centre index fc
+// of the line it was computed for (s = max(fc - fsteps, 0), kernels.c:435).  (Empty for TBL kernels, which rebuild t2 from the table per line:
 // fewer than one line in three shares its window start with its predecessor.)
 template <int PTS, bool TBL>
 struct GridCache
@@ -180,6 +180,21 @@ __device__ __forceinline__ double lds_f64(uint32_t const addr)
     return v;
 }
 
+__device__ __forceinline__ double2 lds_f64x2(uint32_t const addr)
+{
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ float4 lds_f32x4(uint32_t const addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
 // The grid wavenumbers of the lane's points as one line sees them (they depend on the
 // line through its window start s only).  TBL: fl(i*wres) comes from the block's
 // shared-memory table iw[] (i = f - s is a small integer: 0 <= i <= 2*fsteps inside a
@@ -193,12 +208,13 @@ template <int PTS>
 struct LineGrid<PTS, true>
 {
     GridCache<PTS, true> &gc;
-    __device__ __forceinline__ LineGrid(GridCache<PTS, true> &c, TileCtx const &t, int const s)
+    __device__ __forceinline__ LineGrid(GridCache<PTS, true> &c, TileCtx const &t, int const fc)
         : gc(c)
     {
-        if (s != gc.s)
+        if (fc != gc.s)
         {
-            gc.s = s;
+            gc.s = fc;
+            int const s = max(fc - t.fsteps, 0);
             double const dwno = __dadd_rn(__dmul_rn(int_to_double(s), t.wres), t.w0);
             uint32_t const a = t.iw_lane - 8u*(uint32_t)s;
 #pragma unroll
@@ -216,8 +232,9 @@ struct LineGrid<PTS, true>
 {
     double dwno;
     uint32_t a;
-    __device__ __forceinline__ LineGrid(GridCache<PTS, true> &, TileCtx const &t, int const s)
+    __device__ __forceinline__ LineGrid(GridCache<PTS, true> &, TileCtx const &t, int const fc)
     {
+        int const s = max(fc - t.fsteps, 0);
         dwno = __dadd_rn(__dmul_rn(int_to_double(s), t.wres), t.w0);
         a = t.iw_lane - 8u*(uint32_t)s;
     }
@@ -232,12 +249,13 @@ template <int PTS>
 struct LineGrid<PTS, false>
 {
     GridCache<PTS, false> &gc;
-    __device__ __forceinline__ LineGrid(GridCache<PTS, false> &c, TileCtx const &t, int const s)
+    __device__ __forceinline__ LineGrid(GridCache<PTS, false> &c, TileCtx const &t, int const fc)
         : gc(c)
     {
-        if (s != gc.s)
+        if (fc != gc.s)
         {
-            gc.s = s;
+            gc.s = fc;
+            int const s = max(fc - t.fsteps, 0);
             double const sd = int_to_double(s);
             double const dwno = __dadd_rn(__dmul_rn(sd, t.wres), t.w0);
             double const i0 = __dsub_rn(t.lane_pt, sd);     // exact
@@ -294,7 +312,7 @@ template <int PTS, bool TBL>
 __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
-    LineGrid<PTS, TBL> const grid(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
+    LineGrid<PTS, TBL> const grid(gc, t, __float_as_int(B.w));
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
@@ -316,7 +334,7 @@ __device__ __forceinline__ void line_r1(LineRec const *rec, TileCtx const &t,
     float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
     float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
     float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, -
-    LineGrid<PTS, TBL> const grid(gc, t, max(__float_as_int(B.w) - t.fsteps, 0));
+    LineGrid<PTS, TBL> const grid(gc, t, __float_as_int(B.w));
     double const repwid = widen_positive(B.x);
     f32x2 const y2 = pack2(C.y, C.y);
     f32x2 const a0 = pack2(D.x, D.x);
@@ -339,7 +357,7 @@ __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    LineGrid<PTS, TBL> const grid(gc, t, s);
+    LineGrid<PTS, TBL> const grid(gc, t, fc);
     double const repwid = widen_positive(B.x);
     int const f0 = t.warp_base + t.lane;
 #pragma unroll
@@ -364,7 +382,7 @@ __device__ __forceinline__ void line_far_edge(LineRec const *rec, TileCtx const 
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    LineGrid<PTS, TBL> const grid(gc, t, s);
+    LineGrid<PTS, TBL> const grid(gc, t, fc);
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
@@ -405,7 +423,7 @@ __device__ __forceinline__ void line_near(LineRec const *rec, TileCtx const &t,
     int const hw0in = (int)(__float_as_uint(D.w) >> 16);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    LineGrid<PTS, TBL> const grid(gc, t, s);
+    LineGrid<PTS, TBL> const grid(gc, t, fc);
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
@@ -467,6 +485,32 @@ __device__ __forceinline__ void line_near(LineRec const *rec, TileCtx const &t,
 }
 
 
+// Development build only (-DGRT_DBG_TIMERS=1): SM cycles and line visits per line class,
+// summed over warps, read back by grt_debug_timers() (tools/class_timers.py).
+#ifndef GRT_DBG_TIMERS
+#define GRT_DBG_TIMERS 0
+#endif
+#if GRT_DBG_TIMERS
+enum { kTmClassify = 0, kTmFast, kTmR1, kTmFarEdge, kTmNear, kTmLorFull, kTmLorEdge, kTmWait,
+       kTmEpilogue, kTmItem, kTmCount };
+__device__ unsigned long long g_dbg_cycles[kTmCount];
+__device__ unsigned long long g_dbg_visits[kTmCount];
+#define GRT_TM_BEGIN() long long tm_t0 = clock64()
+#define GRT_TM_END(slot, visits)                                                          \
+    do {                                                                                  \
+        long long const tm_t1 = clock64();                                                \
+        if ((threadIdx.x & 31) == 0)                                                      \
+        {                                                                                 \
+            atomicAdd(&g_dbg_cycles[slot], (unsigned long long)(tm_t1 - tm_t0));          \
+            atomicAdd(&g_dbg_visits[slot], (unsigned long long)(visits));                 \
+        }                                                                                 \
+        tm_t0 = clock64();                                                                \
+    } while (0)
+#else
+#define GRT_TM_BEGIN() do {} while (0)
+#define GRT_TM_END(slot, visits) do {} while (0)
+#endif
+
 // One staged batch (cnt <= 32 records of one layer) against the warp's tile.  Lane b
 // classifies record b; the classes are then walked as bit masks, the dominant one
 // (kClsFast) with the next record's vectors prefetched while the current one computes.
@@ -475,6 +519,7 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
                                               TileCtx const &t, GridCache<PTS, TBL> &gc,
                                               double (&acc)[PTS])
 {
+    GRT_TM_BEGIN();
     int cls = kClsNone;
     if (t.lane < cnt)
     {
@@ -510,48 +555,76 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
         }
     }
     unsigned m = __ballot_sync(0xffffffffu, cls == kClsFast);
+    GRT_TM_END(kTmClassify, 1);
+#if GRT_DBG_TIMERS
+    int tm_n = __popc(m);
+#endif
     if (m)
     {
         int b = __ffs(m) - 1;
         m &= m - 1;
-        double2 A = *reinterpret_cast<double2 const *>(&stage[b].v);
-        float4 B = *reinterpret_cast<float4 const *>(&stage[b].repwid);
+        // two records in flight, in alternating register sets (no copies between them);
+        // the stage address is kept opaque so that it stays in a register
+        uint32_t sa = smem_u32(stage);
+        asm volatile("" : "+r"(sa));
+        double2 A0 = lds_f64x2(sa + 64u*(uint32_t)b);
+        float4 B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
         for (;;)
         {
-            bool const more = m != 0;
-            int const bn = more ? __ffs(m) - 1 : b;
+            bool more = m != 0;
+            b = more ? __ffs(m) - 1 : b;
             m &= m - 1;
-            double2 const An = *reinterpret_cast<double2 const *>(&stage[bn].v);
-            float4 const Bn = *reinterpret_cast<float4 const *>(&stage[bn].repwid);
-            line_fast<PTS, TBL>(A, B, t, gc, acc);
+            double2 const A1 = lds_f64x2(sa + 64u*(uint32_t)b);
+            float4 const B1 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
+            line_fast<PTS, TBL>(A0, B0, t, gc, acc);
             if (!more) break;
-            A = An;
-            B = Bn;
-            b = bn;
+            more = m != 0;
+            b = more ? __ffs(m) - 1 : b;
+            m &= m - 1;
+            A0 = lds_f64x2(sa + 64u*(uint32_t)b);
+            B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
+            line_fast<PTS, TBL>(A1, B1, t, gc, acc);
+            if (!more) break;
         }
     }
+    GRT_TM_END(kTmFast, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsR1);
+#if GRT_DBG_TIMERS
+    tm_n = __popc(m);
+#endif
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
         line_r1<PTS, TBL>(stage + b, t, gc, acc);
     }
+    GRT_TM_END(kTmR1, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsFarEdge);
+#if GRT_DBG_TIMERS
+    tm_n = __popc(m);
+#endif
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
         line_far_edge<PTS, TBL>(stage + b, t, gc, acc);
     }
+    GRT_TM_END(kTmFarEdge, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsNear);
+#if GRT_DBG_TIMERS
+    tm_n = __popc(m);
+#endif
     while (m)
     {
         int const b = __ffs(m) - 1;
         m &= m - 1;
         line_near<PTS, TBL>(stage + b, t, gc, acc);
     }
+    GRT_TM_END(kTmNear, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull);
+#if GRT_DBG_TIMERS
+    tm_n = __popc(m);
+#endif
     while (m)
     {
         int const b = __ffs(m) - 1;
@@ -560,7 +633,11 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
                                      *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc,
                                      acc);
     }
+    GRT_TM_END(kTmLorFull, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge);
+#if GRT_DBG_TIMERS
+    tm_n = __popc(m);
+#endif
     while (m)
     {
         int const b = __ffs(m) - 1;
@@ -569,6 +646,7 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
                                       *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc,
                                       acc);
     }
+    GRT_TM_END(kTmLorEdge, tm_n);
 }
 
 
@@ -650,6 +728,9 @@ wing_sweep_kernel(SweepParams const p)
         int const layer0 = group*NL;
         int const nl = min(NL, L - layer0);
         int const nb = (int)((last - first + 31u)/32u);
+#if GRT_DBG_TIMERS
+        long long const ti0 = clock64();
+#endif
 
         double acc[NL][PTS];
 #pragma unroll
@@ -691,7 +772,17 @@ wing_sweep_kernel(SweepParams const p)
         for (int k=0; k<nb; ++k)
         {
             int const st = k & 1;
+#if GRT_DBG_TIMERS
+            long long const tw0 = clock64();
+#endif
             mbar_wait(st ? mb1 : mb0, (phase >> st) & 1u);
+#if GRT_DBG_TIMERS
+            if (lane == 0)
+            {
+                atomicAdd(&g_dbg_cycles[kTmWait], (unsigned long long)(clock64() - tw0));
+                atomicAdd(&g_dbg_visits[kTmWait], 1ull);
+            }
+#endif
             phase ^= 1u << st;
             int const cnt = (int)min(32u, last - (first + 32u*(unsigned)k));
             LineRec const *stage = reinterpret_cast<LineRec const *>(ring + st*Cfg::kStageBytes);
@@ -710,6 +801,9 @@ wing_sweep_kernel(SweepParams const p)
         }
 
         // Epilogue: continua, CFCs, CIA (kernels.c:469-510, 585-630), one store.
+#if GRT_DBG_TIMERS
+        long long const te0 = clock64();
+#endif
 #pragma unroll
         for (int l=0; l<NL; ++l)
         {
@@ -749,6 +843,16 @@ wing_sweep_kernel(SweepParams const p)
                 p.tau[(size_t)layer*p.nw + f] = t;
             }
         }
+#if GRT_DBG_TIMERS
+        if (lane == 0)
+        {
+            long long const te1 = clock64();
+            atomicAdd(&g_dbg_cycles[kTmEpilogue], (unsigned long long)(te1 - te0));
+            atomicAdd(&g_dbg_visits[kTmEpilogue], 1ull);
+            atomicAdd(&g_dbg_cycles[kTmItem], (unsigned long long)(te1 - ti0));
+            atomicAdd(&g_dbg_visits[kTmItem], 1ull);
+        }
+#endif
     }
 }
 
