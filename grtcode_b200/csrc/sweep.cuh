@@ -327,13 +327,11 @@ __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileC
 // kClsR1: the tile lies wholly inside the window and every point has
 // XLIM1 <= |x| < XLIM0 (wide Doppler cores of the shortwave): region 1 only.
 template <int PTS, bool TBL>
-__device__ __forceinline__ void line_r1(LineRec const *rec, TileCtx const &t,
+__device__ __forceinline__ void line_r1(double2 const A, float4 const B, float4 const C,
+                                        float4 const D, TileCtx const &t,
                                         GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
-    double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
-    float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
-    float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
-    float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, -
+    // C = hw0, y, xlim0, xlim1;  D = a0, d0, d2, -
     LineGrid<PTS, TBL> const grid(gc, t, __float_as_int(B.w));
     double const repwid = widen_positive(B.x);
     f32x2 const y2 = pack2(C.y, C.y);
@@ -374,11 +372,9 @@ __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
 // kClsFarEdge: far wing only, but a window end falls inside the tile (kernels.c:435-437):
 // the far-wing arithmetic with a per-point window predicate.
 template <int PTS, bool TBL>
-__device__ __forceinline__ void line_far_edge(LineRec const *rec, TileCtx const &t,
+__device__ __forceinline__ void line_far_edge(double2 const A, float4 const B, TileCtx const &t,
                                               GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
-    double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
-    float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
@@ -406,18 +402,76 @@ __device__ __forceinline__ void line_far_edge(LineRec const *rec, TileCtx const 
 
 // kClsNear: the tile overlaps the line's |x| < XLIM0 neighbourhood, so its points may be
 // far-wing, Humlicek region-1 (RFM_voigt.c:172-183) or line-core samples (the latter are
-// skipped here and left to core_sweep_kernel).  Every pair of 32-point chunks is
-// dispatched warp-uniformly from the record's conservative half-widths: all far wing,
-// all inside XLIM0 (region 1 where |x| >= XLIM1), or mixed (both formulas, per-lane
-// select with the reference's own float comparisons, RFM_voigt.c:166,172).
+// skipped here and left to core_sweep_kernel); the per-lane choice uses the reference's
+// own float comparisons (RFM_voigt.c:166,172).
+// Single-pair tiles (PTS = 2): far wing for both points, region 1 on top if the pair
+// reaches inside XLIM0 (warp-uniform test on the record's conservative half-width).
 template <int PTS, bool TBL>
-__device__ __forceinline__ void line_near(LineRec const *rec, TileCtx const &t,
+__device__ __forceinline__ void line_near_single(double2 const A, float4 const B, float4 const C,
+                                          float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
-    double2 const A = *reinterpret_cast<double2 const *>(&rec->v);
-    float4 const B = *reinterpret_cast<float4 const *>(&rec->repwid);
-    float4 const C = *reinterpret_cast<float4 const *>(&rec->hw0);   // hw0, y, xlim0, xlim1
-    float4 const D = *reinterpret_cast<float4 const *>(&rec->a0);    // a0, d0, d2, hw1_hw0in
+    // C = hw0, y, xlim0, xlim1;  D = a0, d0, d2, hw1_hw0in
+    int const fc = __float_as_int(B.w);
+    int const hw0 = __float_as_int(C.x);
+    int const s = max(fc - t.fsteps, 0);
+    int const e = min(fc + t.fsteps, t.nw - 1);
+    LineGrid<PTS, TBL> const grid(gc, t, fc);
+    double const repwid = widen_positive(B.x);
+    f32x2 const yq2 = pack2(B.y, B.y);
+    f32x2 const yr2 = pack2(B.z, B.z);
+    int const f0 = t.warp_base + t.lane;
+    f32x2 xi[PTS/2], xq[PTS/2], k[PTS/2];
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        xi[j/2] = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        xq[j/2] = mul2_unfused(xi[j/2], xi[j/2]);
+        k[j/2] = far_wing2(xq[j/2], yq2, yr2);
+    }
+    f32x2 const y2 = pack2(C.y, C.y);
+    f32x2 const a0 = pack2(D.x, D.x);
+    f32x2 const d0 = pack2(D.y, D.y);
+    f32x2 const d2 = pack2(D.z, D.z);
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        int const cb = t.warp_base + 32*j;            // the pair covers [cb, cb + 63]
+        int const dlo = max(max(cb - fc, fc - (cb + 63)), 0);
+        int const fa = f0 + 32*j;
+        int const fb = fa + 32;
+        bool ina = (fa >= s) && (fa <= e);
+        bool inb = (fb >= s) && (fb <= e);
+        float k0, k1;
+        unpack2(k[j/2], k0, k1);
+        if (dlo <= hw0)
+        {
+            float x0, x1, r0, r1;
+            unpack2(xi[j/2], x0, x1);
+            unpack2(region1_2(xq[j/2], y2, a0, d0, d2), r0, r1);
+            float const ax0 = fabsf(x0);
+            float const ax1 = fabsf(x1);
+            bool const far0 = ax0 >= C.z;
+            bool const far1 = ax1 >= C.z;
+            k0 = far0 ? k0 : r0;
+            k1 = far1 ? k1 : r1;
+            ina = ina && (far0 || (ax0 >= C.w));
+            inb = inb && (far1 || (ax1 >= C.w));
+        }
+        if (ina) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
+        if (inb) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+    }
+}
+
+// Wider tiles: the abscissae of all PTS points are formed first, as one straight-line block
+// with every dependency chain in flight; each pair of 32-point chunks is then dispatched
+// warp-uniformly to far wing / region 1 / both (measured: -2.4 % on the config-2 step
+// against forming them inside the branches).
+template <int PTS, bool TBL>
+__device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B, float4 const C,
+                                          float4 const D, TileCtx const &t,
+                                          GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+{
     int const fc = __float_as_int(B.w);
     int const hw0 = __float_as_int(C.x);
     int const hw0in = (int)(__float_as_uint(D.w) >> 16);
@@ -432,40 +486,44 @@ __device__ __forceinline__ void line_near(LineRec const *rec, TileCtx const &t,
     f32x2 const d0 = pack2(D.y, D.y);
     f32x2 const d2 = pack2(D.z, D.z);
     int const f0 = t.warp_base + t.lane;
+    f32x2 xi[PTS/2], xq[PTS/2];
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        xi[j/2] = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        xq[j/2] = mul2_unfused(xi[j/2], xi[j/2]);
+    }
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
         int const cb = t.warp_base + 32*j;            // the pair covers [cb, cb + 63]
-        if (cb + 63 < s || cb > e) continue;          // wholly outside the window
         int const dlo = max(max(cb - fc, fc - (cb + 63)), 0);
         int const dhi = max(fc - cb, cb + 63 - fc);
         int const fa = f0 + 32*j;
         int const fb = fa + 32;
         bool const ina = (fa >= s) && (fa <= e);
         bool const inb = (fb >= s) && (fb <= e);
-        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
-        f32x2 const xq = mul2_unfused(xi, xi);
         float x0, x1;
-        unpack2(xi, x0, x1);
+        unpack2(xi[j/2], x0, x1);
         if (dlo > hw0)
         {
             float k0, k1;
-            unpack2(far_wing2(xq, yq2, yr2), k0, k1);
+            unpack2(far_wing2(xq[j/2], yq2, yr2), k0, k1);
             if (ina) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
             if (inb) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
         }
         else if (dhi < hw0in)
         {
             float k0, k1;
-            unpack2(region1_2(xq, y2, a0, d0, d2), k0, k1);
+            unpack2(region1_2(xq[j/2], y2, a0, d0, d2), k0, k1);
             if (ina && (fabsf(x0) >= C.w)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
             if (inb && (fabsf(x1) >= C.w)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
         }
         else
         {
             float kf0, kf1, kr0, kr1;
-            unpack2(far_wing2(xq, yq2, yr2), kf0, kf1);
-            unpack2(region1_2(xq, y2, a0, d0, d2), kr0, kr1);
+            unpack2(far_wing2(xq[j/2], yq2, yr2), kf0, kf1);
+            unpack2(region1_2(xq[j/2], y2, a0, d0, d2), kr0, kr1);
             {
                 float const ax = fabsf(x0);
                 bool const isfar = ax >= C.z;
@@ -484,6 +542,51 @@ __device__ __forceinline__ void line_near(LineRec const *rec, TileCtx const &t,
     }
 }
 
+template <int PTS, bool TBL>
+__device__ __forceinline__ void line_near(double2 const A, float4 const B, float4 const C,
+                                          float4 const D, TileCtx const &t,
+                                          GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+{
+    if (PTS <= 2) line_near_single<PTS, TBL>(A, B, C, D, t, gc, acc);
+    else line_near_pairs<PTS, TBL>(A, B, C, D, t, gc, acc);
+}
+
+
+// The four 16-byte vectors of a staged record.
+template <int NV>
+struct RecVec
+{
+    double2 A;         // v, c
+    float4 B;          // repwid, yq, yrrtpi, fc
+    float4 C;          // hw0, y, xlim0, xlim1
+    float4 D;          // a0, d0, d2, hw1_hw0in
+    __device__ __forceinline__ void load(uint32_t const addr)
+    {
+        A = lds_f64x2(addr);
+        B = lds_f32x4(addr + 16u);
+        if (NV > 2)
+        {
+            C = lds_f32x4(addr + 32u);
+            D = lds_f32x4(addr + 48u);
+        }
+    }
+};
+
+// Walk the records of one class (bit mask m over the staged batch at shared address sa).
+// (Loading the next record while the current one computes, as the fast class does, was
+// measured slower here: the extra live registers cost more than the load latency.)
+template <int NV, class Body>
+__device__ __forceinline__ void walk_class(unsigned m, uint32_t const sa, Body &&body)
+{
+    while (m)
+    {
+        int const b = __ffs(m) - 1;
+        m &= m - 1;
+        RecVec<NV> r;
+        r.load(sa + 64u*(uint32_t)b);
+        body(r);
+    }
+}
 
 // Development build only (-DGRT_DBG_TIMERS=1): SM cycles and line visits per line class,
 // summed over warps, read back by grt_debug_timers() (tools/class_timers.py).
@@ -559,14 +662,14 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
 #if GRT_DBG_TIMERS
     int tm_n = __popc(m);
 #endif
+    // the stage address is kept opaque so that it stays in a register
+    uint32_t sa = smem_u32(stage);
+    asm volatile("" : "+r"(sa));
     if (m)
     {
         int b = __ffs(m) - 1;
         m &= m - 1;
-        // two records in flight, in alternating register sets (no copies between them);
-        // the stage address is kept opaque so that it stays in a register
-        uint32_t sa = smem_u32(stage);
-        asm volatile("" : "+r"(sa));
+        // two records in flight, in alternating register sets (no copies between them)
         double2 A0 = lds_f64x2(sa + 64u*(uint32_t)b);
         float4 B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
         for (;;)
@@ -592,60 +695,31 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    while (m)
-    {
-        int const b = __ffs(m) - 1;
-        m &= m - 1;
-        line_r1<PTS, TBL>(stage + b, t, gc, acc);
-    }
+    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_r1<PTS, TBL>(r.A, r.B, r.C, r.D, t, gc, acc); });
     GRT_TM_END(kTmR1, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsFarEdge);
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    while (m)
-    {
-        int const b = __ffs(m) - 1;
-        m &= m - 1;
-        line_far_edge<PTS, TBL>(stage + b, t, gc, acc);
-    }
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_far_edge<PTS, TBL>(r.A, r.B, t, gc, acc); });
     GRT_TM_END(kTmFarEdge, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsNear);
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    while (m)
-    {
-        int const b = __ffs(m) - 1;
-        m &= m - 1;
-        line_near<PTS, TBL>(stage + b, t, gc, acc);
-    }
+    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_near<PTS, TBL>(r.A, r.B, r.C, r.D, t, gc, acc); });
     GRT_TM_END(kTmNear, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull);
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    while (m)
-    {
-        int const b = __ffs(m) - 1;
-        m &= m - 1;
-        line_lorentz<PTS, TBL, true>(*reinterpret_cast<double2 const *>(&stage[b].v),
-                                     *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc,
-                                     acc);
-    }
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, true>(r.A, r.B, t, gc, acc); });
     GRT_TM_END(kTmLorFull, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge);
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    while (m)
-    {
-        int const b = __ffs(m) - 1;
-        m &= m - 1;
-        line_lorentz<PTS, TBL, false>(*reinterpret_cast<double2 const *>(&stage[b].v),
-                                      *reinterpret_cast<float4 const *>(&stage[b].repwid), t, gc,
-                                      acc);
-    }
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, false>(r.A, r.B, t, gc, acc); });
     GRT_TM_END(kTmLorEdge, tm_n);
 }
 

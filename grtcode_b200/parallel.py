@@ -77,11 +77,14 @@ class SpectralChunk:
         return self.w_hi - 0.25*self.dw
 
 
-def split_spectral_range(w0: float, wn: float, dw: float, world: int) -> list[SpectralChunk]:
-    """Cut the grid [w0, wn] @ dw into `world` chunks of (almost) equal numbers of
-    trapezoid intervals.  Neighbouring chunks share one grid point; every chunk keeps the
-    global spacing and starts on a global grid point, w(i) = w0 + i*dw
-    (spectral_grid.c:94)."""
+def split_spectral_range(w0: float, wn: float, dw: float, world: int,
+                         cost: np.ndarray | None = None) -> list[SpectralChunk]:
+    """Cut the grid [w0, wn] @ dw into `world` chunks.  Neighbouring chunks share one grid
+    point; every chunk keeps the global spacing and starts on a global grid point,
+    w(i) = w0 + i*dw (spectral_grid.c:94).  Without `cost` the chunks hold (almost) equal
+    numbers of trapezoid intervals; with `cost` (float[n-1], the estimated work of each
+    interval, e.g. ``interval_cost``) the cuts equalise the summed cost instead -- lines
+    cluster in bands, so equal point counts are not equal work."""
     n = grid_size(w0, wn, dw)
     intervals = n - 1
     if world < 1 or intervals < world:
@@ -90,14 +93,68 @@ def split_spectral_range(w0: float, wn: float, dw: float, world: int) -> list[Sp
     # dropped by the parser (parse_HITRAN_file.c:349), so their reach must end short of
     # the owned points
     halo = int(math.ceil(float(np.float32(LINE_CUTOFF))/dw)) + 1
+    if cost is None:
+        cuts = [(r*intervals)//world for r in range(world + 1)]
+    else:
+        c = np.asarray(cost, dtype=np.float64)
+        if c.shape != (intervals,) or not np.all(np.isfinite(c)) or np.any(c < 0.):
+            raise ValueError("cost must be a finite, non-negative float[n-1]")
+        cum = np.concatenate([[0.], np.cumsum(c)])
+        if cum[-1] <= 0.:
+            cuts = [(r*intervals)//world for r in range(world + 1)]
+        else:
+            cuts = [0]
+            for r in range(1, world):
+                k = int(np.searchsorted(cum, cum[-1]*r/world, side="left"))
+                # every chunk keeps at least one interval
+                k = min(max(k, cuts[-1] + 1), intervals - (world - r))
+                cuts.append(k)
+            cuts.append(intervals)
     chunks = []
     for r in range(world):
-        a = (r*intervals)//world
-        b = ((r + 1)*intervals)//world
+        a, b = cuts[r], cuts[r + 1]
         lo = max(a - halo, 0)
         hi = min(b + halo, n - 1)
         chunks.append(SpectralChunk(r, a, b, lo, hi, w0 + lo*dw, w0 + hi*dw, dw))
     return chunks
+
+
+def line_centres(hitran_path: str, molecules=None) -> np.ndarray:
+    """Transition wavenumbers of a HITRAN .par file (160-character records, field 2 =
+    columns 4-15, parse_HITRAN_file.c:79-100), optionally of the given molecule ids only."""
+    raw = np.fromfile(hitran_path, dtype=np.uint8)
+    if raw.size == 0:
+        return np.zeros(0)
+    nl = int(np.argmax(raw == 10))
+    rec = nl + 1
+    if raw[nl] != 10 or nl < 160 or raw.size % rec:
+        raise ValueError(f"{hitran_path}: not fixed-length HITRAN records")
+    tab = raw.reshape(-1, rec)
+    v = np.ascontiguousarray(tab[:, 3:15]).view("S12").ravel().astype(np.float64)
+    if molecules is not None:
+        mol = np.ascontiguousarray(tab[:, 0:2]).view("S2").ravel().astype(np.int64)
+        v = v[np.isin(mol, np.asarray(list(molecules), dtype=np.int64))]
+    return v
+
+
+def interval_cost(w0: float, wn: float, dw: float, centres: np.ndarray,
+                  point_cost: float | None = None) -> np.ndarray:
+    """Estimated work of each trapezoid interval of the grid, in units of one line:
+    a line spreads its cost evenly over the 2*ceil(25/dw)+1 points of its window
+    (kernels.c:417,435-437), and every grid point costs `point_cost` lines for the
+    continua, the solvers and the integration (default 2*dw: about 4 ns per point against
+    layers*window/1e12 s per line, measured on B200).  Used to balance
+    ``split_spectral_range``; only the relative sizes matter."""
+    n = grid_size(w0, wn, dw)
+    F = int(math.ceil(float(np.float32(LINE_CUTOFF))/dw))
+    fc = np.floor((np.asarray(centres, dtype=np.float64) - w0)/dw + 0.5).astype(np.int64)
+    fc = fc[(fc >= 0) & (fc < n)]
+    hist = np.bincount(fc, minlength=n).astype(np.float64)
+    cum = np.concatenate([[0.], np.cumsum(hist)])
+    idx = np.arange(n)
+    dens = (cum[np.minimum(idx + F, n - 1) + 1] - cum[np.maximum(idx - F, 0)])/(2*F + 1)
+    dens += (2.*dw if point_cost is None else point_cost)
+    return 0.5*(dens[:-1] + dens[1:])
 
 
 def trapezoid(flux: np.ndarray, dw: float) -> np.ndarray:
@@ -156,9 +213,11 @@ class SpectralSplitColumn:
     (config 4).  Every rank builds the engine for its own chunk (+ halo) of every band;
     ``run`` returns the all-reduced broadband fluxes
     {"lw"/"sw": (up[levels], down[levels])}.  The solar spectrum is normalised on the
-    GLOBAL grid (solar_flux.c:73-84) and sliced."""
+    GLOBAL grid (solar_flux.c:73-84) and sliced.  balance=True places the cuts by estimated
+    work (``interval_cost`` of the band's line list) instead of by point count."""
 
-    def __init__(self, bands, column, device: int, molecules, world: int, rank: int):
+    def __init__(self, bands, column, device: int, molecules, world: int, rank: int,
+                 balance: bool = True):
         from . import api
         from . import workloads as W
         from .column_engine import ColumnEngine
@@ -167,7 +226,12 @@ class SpectralSplitColumn:
         windows = {}
         solar = {}
         for band in bands:
-            ch = split_spectral_range(band.w0, band.wn, band.dw, world)[rank]
+            cost = None
+            if balance and world > 1:
+                # every rank derives the same cuts from the same line list
+                cost = interval_cost(band.w0, band.wn, band.dw,
+                                     line_centres(band.dataset.hitran, molecules))
+            ch = split_spectral_range(band.w0, band.wn, band.dw, world, cost)[rank]
             self.chunks[band.name] = ch
             sub.append(W.Band(band.name, ch.w_lo, ch.wn_arg, band.dw, band.lines, band.dataset))
             windows[band.name] = ch.window

@@ -53,6 +53,48 @@ def test_spectral_chunks_tile_the_grid(w0, wn, dw, world):
         P.split_spectral_range(1., 1.5, 0.1, 8)
 
 
+def test_cost_balanced_chunks(tmp_path):
+    """With a per-interval cost the cuts equalise the summed cost; the chunks still tile the
+    grid, share their seam points and carry the same halo.  A uniform cost reproduces the
+    equal-interval split (to the rounding of a cut)."""
+    from grtcode_b200 import synth
+    w0, wn, dw, world = 1., 3250., 0.1, 4
+    n = P.grid_size(w0, wn, dw)
+    same = P.split_spectral_range(w0, wn, dw, world, np.ones(n - 1))
+    plain = P.split_spectral_range(w0, wn, dw, world)
+    assert all(abs(a.first - b.first) <= 1 and abs(a.last - b.last) <= 1
+               for a, b in zip(same, plain))
+    # a line list crowded into 600-800 cm-1, written and read back as HITRAN records
+    rng = np.random.default_rng(3)
+    sets = [synth.make_lines(synth.CO2, 4000, 600., 800., rng),
+            synth.make_lines(synth.H2O, 500, w0, wn, rng)]
+    path = str(tmp_path/"lines.par")
+    synth.write_hitran(path, sets)
+    v = P.line_centres(path)
+    assert v.size == 4500 and v.min() >= w0 and v.max() <= wn
+    only = P.line_centres(path, molecules=(synth.H2O,))
+    assert only.size == 500
+    cost = P.interval_cost(w0, wn, dw, v)
+    assert cost.shape == (n - 1,) and np.all(cost > 0.)
+    # total line cost is conserved by the box filter away from the grid ends
+    assert abs((cost - 2.*dw).sum() - v.size) < 0.02*v.size
+    chunks = P.split_spectral_range(w0, wn, dw, world, cost)
+    assert chunks[0].first == 0 and chunks[-1].last == n - 1
+    for a, b in zip(chunks[:-1], chunks[1:]):
+        assert a.last == b.first and a.first < a.last
+    shares = np.array([cost[c.first:c.last].sum() for c in chunks])/cost.sum()
+    assert np.all(np.abs(shares - 1./world) < 0.02), shares
+    plain_shares = np.array([cost[c.first:c.last].sum() for c in plain])/cost.sum()
+    assert plain_shares.max() > 0.5                   # what equal point counts would give
+    with pytest.raises(ValueError):
+        P.split_spectral_range(w0, wn, dw, world, np.ones(n))
+    # degenerate: all the cost in one interval still leaves every rank an interval
+    spike = np.zeros(n - 1)
+    spike[10] = 1.
+    for c in P.split_spectral_range(w0, wn, dw, world, spike):
+        assert c.last > c.first
+
+
 def test_chunk_grids_have_the_expected_size_in_the_host_library(built):
     """create_spectral_grid (spectral_grid.c:61) on (w_lo, wn_arg, dw) gives hi - lo + 1
     points for every chunk of the config-4 split, and w(i) lands on the global grid."""
