@@ -23,6 +23,7 @@ The process group is torch.distributed: ``nccl`` with CUDA tensors on the GPU bo
 from __future__ import annotations
 
 import math
+import time
 from dataclasses import dataclass
 
 import numpy as np
@@ -138,18 +139,23 @@ def line_centres(hitran_path: str, molecules=None) -> np.ndarray:
 
 
 def interval_cost(w0: float, wn: float, dw: float, centres: np.ndarray,
-                  point_cost: float | None = None) -> np.ndarray:
-    """Estimated work of each trapezoid interval of the grid, in units of one line:
+                  point_cost: float | None = None, doppler_slope: float = 7.3e-8) -> np.ndarray:
+    """Estimated work of each trapezoid interval of the grid, in units of one far-wing line:
     a line spreads its cost evenly over the 2*ceil(25/dw)+1 points of its window
-    (kernels.c:417,435-437), and every grid point costs `point_cost` lines for the
-    continua, the solvers and the integration (default 2*dw: about 4 ns per point against
-    layers*window/1e12 s per line, measured on B200).  Used to balance
-    ``split_spectral_range``; only the relative sizes matter."""
+    (kernels.c:417,435-437); a line at wavenumber v costs 1 + doppler_slope*v/dw (its
+    Doppler core, and with it the number of samples outside the cheap far-wing branch,
+    widens with v: +17 % measured between the two halves of config 4 at 0.01 cm-1); and
+    every grid point costs `point_cost` lines for the continua, the solvers and the
+    integration (default 2*dw: about 4 ns per point against layers*window/1e12 s per line,
+    measured on B200).  Used to balance ``split_spectral_range``; only the relative sizes
+    matter."""
     n = grid_size(w0, wn, dw)
     F = int(math.ceil(float(np.float32(LINE_CUTOFF))/dw))
-    fc = np.floor((np.asarray(centres, dtype=np.float64) - w0)/dw + 0.5).astype(np.int64)
-    fc = fc[(fc >= 0) & (fc < n)]
-    hist = np.bincount(fc, minlength=n).astype(np.float64)
+    v = np.asarray(centres, dtype=np.float64)
+    fc = np.floor((v - w0)/dw + 0.5).astype(np.int64)
+    keep = (fc >= 0) & (fc < n)
+    weight = 1. + doppler_slope*np.abs(v[keep])/dw
+    hist = np.bincount(fc[keep], weights=weight, minlength=n).astype(np.float64)
     cum = np.concatenate([[0.], np.cumsum(hist)])
     idx = np.arange(n)
     dens = (cum[np.minimum(idx + F, n - 1) + 1] - cum[np.maximum(idx - F, 0)])/(2*F + 1)
@@ -247,7 +253,10 @@ class SpectralSplitColumn:
                 raise RuntimeError(f"chunk grid has {part['n']} points, expected {ch.n}")
 
     def run(self, col, group=None):
+        t0 = time.perf_counter()
         out = self.engine.step(col, upload_surface=True)
+        # this rank's own compute before the exchange (host clock; the calls are synchronous)
+        self.compute_seconds = time.perf_counter() - t0
         names = sorted(out)
         up = np.stack([out[k][0] for k in names])
         dn = np.stack([out[k][1] for k in names])

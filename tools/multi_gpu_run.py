@@ -63,6 +63,8 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    per_rank = []
+
     def timed(fn, reps):
         e0 = torch.cuda.Event(enable_timing=True)
         e1 = torch.cuda.Event(enable_timing=True)
@@ -71,8 +73,18 @@ def main():
         for _ in range(reps):
             out = fn()
         e1.record(stream)
+        torch.cuda.synchronize()
+        mine = e0.elapsed_time(e1)*1e-3/reps       # this rank's own time (no barrier inside)
         barrier()
-        return out, max_over_ranks(e0.elapsed_time(e1)*1e-3/reps)
+        per_rank.clear()
+        if world > 1:
+            t = torch.tensor([mine], device=f"cuda:{local}", dtype=torch.float64)
+            got = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(got, t)
+            per_rank.extend(float(g.item()) for g in got)
+        else:
+            per_rank.append(mine)
+        return out, max(per_rank)
 
     lw2, sw2 = W.circ1_bands(0.01, args.scale)
     if local == 0:
@@ -91,6 +103,13 @@ def main():
     part = P.SpectralSplitColumn(full, col, local, W.MOLECULES, world, rank)
     part.run(col)                                     # warm-up
     split, secs_split = timed(lambda: part.run(col), args.reps)
+    split_ranks = list(per_rank)
+    compute = [part.compute_seconds]
+    if world > 1:
+        t = torch.tensor(compute, device=f"cuda:{local}", dtype=torch.float64)
+        got = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(got, t)
+        compute = [float(g.item()) for g in got]
     chunk = part.chunks["sw_full"]
     part.close()
     two = P.split_spectral_range(sw2.w0, sw2.wn, sw2.dw, 2)[0]
@@ -98,7 +117,8 @@ def main():
     a = {"config": "BASELINE config 4: CIRC-1 column, 1-50000 cm-1 at 0.01 cm-1 (n=4999901), LW + SW, "
                    "7 molecules + continua + 3 CIA + 3 CFCs, spectral range split over the GPUs, "
                    "one NCCL all-reduce of the partial broadband integrals per column",
-         "seconds_per_column": secs_split,
+         "seconds_per_column": secs_split, "seconds_per_rank": split_ranks,
+         "compute_seconds_per_rank_before_allreduce": compute,
          "pts_layers_per_s": 2*full[0].n*(len(col.p) - 1)/secs_split,
          "rank0_chunk_points": chunk.n, "halo_points": halo,
          "allreduce_bytes": 2*2*8*len(col.p)}
