@@ -43,6 +43,10 @@ def parse_args():
     ap.add_argument("--dw", type=float, default=float(os.environ.get("GRT_BENCH_DW", "0.01")))
     ap.add_argument("--data", default=os.environ.get("GRT_BENCH_DATA", "/tmp/grt_bench"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--method", default="line_sample",
+                    choices=["line_sample", "wavenumber_sweep", "line_sweep"],
+                    help="optical_depth_method; the reference drivers (and the headline number) "
+                         "use line_sample (driver.c:618-624)")
     return ap.parse_args()
 
 
@@ -219,7 +223,7 @@ def workload_config(args, lw, sw, layers):
                         "H2O/O3 continua + 3 CIA pairs + 3 CFCs, one column per step per GPU",
             "layers": layers, "dw_cm-1": args.dw, "lw_points": lw.n, "sw_points": sw.n,
             "lw_lines": lw.num_lines, "sw_lines": sw.num_lines, "line_scale": args.scale,
-            "method": "line_sample", "columns_per_step_per_gpu": 1,
+            "method": args.method, "columns_per_step_per_gpu": 1,
             "l2": "inputs larger than L2 (line records + tau > 2 GB per band)"}
 
 
@@ -307,7 +311,8 @@ def run_ours(args):
         W.materialise(sw, args.data, seed=2)
     t_setup = time.perf_counter()
     from grtcode_b200.column_engine import ColumnEngine
-    eng = ColumnEngine((lw, sw), col0, device, W.MOLECULES)
+    method = {"wavenumber_sweep": 0, "line_sweep": 1, "line_sample": 2}[args.method]
+    eng = ColumnEngine((lw, sw), col0, device, W.MOLECULES, method=method)
     t_setup = time.perf_counter() - t_setup
     layers = eng.levels - 1
     pts_layers = (lw.n + sw.n)*layers
@@ -377,7 +382,7 @@ def run_ours(args):
     samples_step = sum(out[n][2]["samples"] for n in ("lw", "sw"))
     roofline = {
         "bound": "fp64",
-        "kernel": "wing_sweep_kernel",
+        "kernel": "wing_sweep_kernel" if args.method == "line_sample" else "bin_gather_kernel",
         "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": achieved/fp64_peak if achieved else None,
         "traffic": None,
@@ -390,6 +395,16 @@ def run_ours(args):
         "kernel_share_of_step": {k: v*1e-9/secs for k, v in kern.items() if k != "band_ms"},
         "kernel_ms_per_step": {k: round(v, 3) for k, v in kern["band_ms"].items()},
     }
+    # The unit that actually binds the exact-rounding far-wing chain is the XU pipe (one
+    # F2F.F32.F64 + one MUFU.RCP per sample at 16 lanes/clk/SM, profiles/*ubench_pipes.txt);
+    # reported beside the FP64 figure SURVEY.md 8(d) asks for.  A lower bound: region-1 and
+    # line-centre samples issue more XU instructions than two.
+    sm_mhz = clk.get("sm_mhz") or clk.get("sm_max_mhz")
+    if roofline["samples_per_s"] and sm_mhz:
+        xu_peak = torch.cuda.get_device_properties(device).multi_processor_count*16.*sm_mhz*1e6
+        roofline["xu_pipe"] = {"ops_per_sample": 2, "achieved_lane_ops_per_s": 2.*roofline["samples_per_s"],
+                               "peak_lane_ops_per_s": xu_peak,
+                               "frac": 2.*roofline["samples_per_s"]/xu_peak}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3*secs/args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64",

@@ -35,10 +35,12 @@ class ColumnEngine:
     own way of restricting the lines a GasOptics_t loads (gas_optics.h:117-119).
     windows: optional {band name: (first, last)} integration windows (spectral split).
     solar_override: optional {band name: float64[n]} incident solar spectrum to use
-    instead of create_solar_flux on the band's own grid."""
+    instead of create_solar_flux on the band's own grid.
+    method: optical_depth_method of create_gas_optics (gas_optics.h:45-50); the reference's
+    drivers pass line_sample (driver.c:618-624), None is the library default."""
 
     def __init__(self, bands, column, device: int, molecules, line_window=None, windows=None,
-                 solar_override=None):
+                 solar_override=None, method: int | None = _api.LINE_SAMPLE):
         api = _api
         api.load()
         self.device = device
@@ -48,7 +50,7 @@ class ColumnEngine:
             ds = band.dataset
             grid = api.spectral_grid(band.w0, band.wn, band.dw)
             go = api.GasOptics(self.levels, grid, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm,
-                               device=device)
+                               method=method, device=device)
             win = (line_window or {}).get(band.name, (None, None))
             for m in molecules:
                 go.add_molecule(m, *win)

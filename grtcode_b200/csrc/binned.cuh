@@ -25,7 +25,7 @@
 
 namespace grt {
 
-constexpr int kBinThreads = 128;
+constexpr int kBinThreads = 256;          // one warp per bin of a gather group
 constexpr int kNip = 3;                 // spectral_bin-internal.h:30
 
 struct BinGeometry
@@ -45,6 +45,7 @@ struct BinParams
     LineRec const *recs;                // [layers][num_lines], molecule-major line order
     double const *vs;                   // [layers][num_lines] centres sorted per (molecule, layer)
     unsigned const *perm;               // [layers][num_lines] record index of each sorted entry
+    LineRec const *sorted_recs;         // [layers][num_lines] records in sorted order
     unsigned long long num_lines;
     int num_slots;
     unsigned slot_off[GRT_MAX_MOLS + 1];
@@ -160,7 +161,7 @@ struct BinRanges32
     unsigned loc_lo, loc_hi, rl_lo, rl_hi, rr_lo, rr_hi;
 };
 
-constexpr int kBinGroup = 8;            // bins per gather block
+constexpr int kBinGroup = kBinThreads/32;   // bins per gather block
 
 // calc_optical_depth_bin_sweep's bookkeeping for bin j (kernels.c:195-300).
 __device__ void ranges_bin_sweep(BinGeometry const &b, unsigned long long const j,
@@ -306,6 +307,21 @@ __device__ __forceinline__ double quad_interp(double const *x, double const *y, 
     return t;
 }
 
+// Records in sorted order, so that the gather reads them with unit stride and no
+// dependent index load: out[layer][pos] = in[layer][perm[layer][pos]] (64 B each).
+__global__ void __launch_bounds__(256)
+permute_records_kernel(LineRec const *in, unsigned const *perm, LineRec *out,
+                       unsigned long long const num_lines)
+{
+    unsigned long long const pos = (unsigned long long)blockIdx.x*blockDim.x + threadIdx.x;
+    if (pos >= num_lines) return;
+    size_t const base = (size_t)blockIdx.y*num_lines;
+    uint4 const *src = reinterpret_cast<uint4 const *>(in + base + perm[base + pos]);
+    uint4 *dst = reinterpret_cast<uint4 *>(out + base + pos);
+    uint4 const a = src[0], b = src[1], c = src[2], d = src[3];
+    dst[0] = a; dst[1] = b; dst[2] = c; dst[3] = d;
+}
+
 // Ranges of every (layer, bin, molecule), one thread each: the binary searches are serial
 // chains of dependent loads, so they are spread over as many threads as there are triples
 // instead of being walked by one thread of the gather block.
@@ -335,137 +351,105 @@ bin_ranges_kernel(BinParams const p, BinRanges32 *out)
     out[idx] = r;
 }
 
-// A block owns kBinGroup consecutive bins of one layer.  Remote lines of neighbouring bins
-// are almost the same set (25 bins either side), so each record is loaded once per group
-// and evaluated on the three interpolation points of every bin of the group it is remote
-// to; local lines are swept bin by bin over the bin's grid points.
-__global__ void __launch_bounds__(kBinThreads)
+// A block owns kBinGroup consecutive bins of one layer, one warp per bin: neighbouring bins
+// see almost the same remote lines (25 bins either side), so the eight warps stream the same
+// records through L1 at the same time.  Remote lines: lanes take consecutive records and
+// evaluate the bin's three interpolation points (three register accumulators per thread for
+// the whole kernel).  Local lines: the warp's lanes form a (line, grid point) grid over the
+// bin's points.  No block barrier inside the molecule loop.
+#ifndef GRT_BIN_MINBLOCKS
+#define GRT_BIN_MINBLOCKS 4
+#endif
+__global__ void __launch_bounds__(kBinThreads, GRT_BIN_MINBLOCKS)
 bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
 {
     extern __shared__ double sh_acc[];          // [kBinGroup][points per bin]
-    __shared__ BinRanges32 sh_ranges[kBinGroup];
     __shared__ double sh_rem[kBinGroup][kNip];
-    __shared__ double sh_warp[kBinThreads/32][kBinGroup*kNip];
     BinGeometry const &b = p.bins;
     unsigned long long const k0 = (unsigned long long)blockIdx.x*kBinGroup;
     int const ng = (int)((b.n - k0) < (unsigned long long)kBinGroup ? (b.n - k0) : kBinGroup);
     int const layer = blockIdx.y;
     int const tid = threadIdx.x;
+    int const lane = tid & 31;
+    int const g = tid >> 5;                      // the warp's bin inside the group
     int const ppb = b.ppb;
     for (int q=tid; q<kBinGroup*ppb; q+=kBinThreads) sh_acc[q] = 0.;
-    double rem[kBinGroup][kNip];
-    double rem_w[kBinGroup], rem_res[kBinGroup];
-#pragma unroll
-    for (int g=0; g<kBinGroup; ++g)
-    {
-        unsigned long long const k = g < ng ? k0 + g : k0;
-        rem_w[g] = bin_w(b, k, 0);
-        rem_res[g] = __dsub_rn(bin_w(b, k, 1), rem_w[g]);
-#pragma unroll
-        for (int l=0; l<kNip; ++l) rem[g][l] = 0.;
-    }
+    __syncthreads();
     unsigned long long evals = 0;
-    LineRec const *recs = p.recs + (size_t)layer*p.num_lines;
-
-    for (int s=0; s<p.num_slots; ++s)
+    double rem[kNip] = {0., 0., 0.};
+    if (g < ng)
     {
-        unsigned long long const off = p.slot_off[s];
-        if (p.slot_off[s+1] == off) continue;
-        unsigned const *perm = p.perm + (size_t)layer*p.num_lines + off;
-        __syncthreads();
-        if (tid < ng)
+        unsigned long long const k = k0 + g;
+        double const rem_w = bin_w(b, k, 0);
+        double const rem_res = __dsub_rn(bin_w(b, k, 1), rem_w);
+        int const npts = bin_points(b, k);
+        double const loc_w = __dadd_rn(b.w0, __dmul_rn((double)bin_left(b, k), b.wres));
+        int const span = npts < 32 ? npts : 32;
+        int const lslots = 32/span;
+        int const my_slot = lane/span;
+        int const my_pt = lane % span;
+        for (int s=0; s<p.num_slots; ++s)
         {
-            sh_ranges[tid] = ranges[((size_t)layer*b.n + (k0 + tid))*p.num_slots + s];
-        }
-        __syncthreads();
-        // remote lines: union of the group's ranges, one record load per line
-        unsigned ulo = 0xffffffffu, uhi = 0;
-        for (int g=0; g<ng; ++g)
-        {
-            BinRanges32 const &R = sh_ranges[g];
-            if (R.rl_hi > R.rl_lo) { ulo = min(ulo, R.rl_lo); uhi = max(uhi, R.rl_hi); }
-            if (R.rr_hi > R.rr_lo) { ulo = min(ulo, R.rr_lo); uhi = max(uhi, R.rr_hi); }
-        }
-        for (unsigned i=ulo + tid; i<uhi; i+=kBinThreads)
-        {
-            LineRec const r = recs[perm[i]];
-#pragma unroll
-            for (int g=0; g<kBinGroup; ++g)
+            unsigned long long const off = p.slot_off[s];
+            if (p.slot_off[s+1] == off) continue;
+            LineRec const *recs = p.sorted_recs + (size_t)layer*p.num_lines + off;
+            BinRanges32 const R = ranges[((size_t)layer*b.n + k)*p.num_slots + s];
+            // remote lines on the three interpolation points
+#pragma unroll 1
+            for (int side=0; side<2; ++side)
             {
-                if (g >= ng) break;
-                BinRanges32 const &R = sh_ranges[g];
-                if ((i >= R.rl_lo && i < R.rl_hi) || (i >= R.rr_lo && i < R.rr_hi))
+                unsigned const lo = side ? R.rr_lo : R.rl_lo;
+                unsigned const hi = side ? R.rr_hi : R.rl_hi;
+#pragma unroll 2
+                for (unsigned i=lo + lane; i<hi; i+=32)
                 {
+                    LineRec const r = recs[i];
 #pragma unroll
-                    for (int l=0; l<kNip; ++l)
-                    {
-                        rem[g][l] += line_point(r, rem_w[g], (double)l, rem_res[g]);
-                    }
+                    for (int l=0; l<kNip; ++l) rem[l] += line_point(r, rem_w, (double)l, rem_res);
                     evals += kNip;
                 }
             }
-        }
-        // local lines of every bin of the group on the bin's grid points
-        for (int g=0; g<ng; ++g)
-        {
-            BinRanges32 const R = sh_ranges[g];
-            unsigned long long const k = k0 + g;
-            int const npts = bin_points(b, k);
-            double const loc_w = __dadd_rn(b.w0, __dmul_rn((double)bin_left(b, k), b.wres));
-            int const span = npts < kBinThreads ? npts : kBinThreads;
-            int const slots = kBinThreads/span;
-            int const my_slot = tid/span;
-            int const my_pt = tid % span;
-            if (my_slot >= slots) continue;
-            for (int pbase=0; pbase<npts; pbase+=span)
+            // local lines on the bin's grid points
+            if (my_slot < lslots)
             {
-                int const pt = pbase + my_pt;
-                if (pt >= npts) continue;
-                double a = 0.;
-                for (unsigned i=R.loc_lo + my_slot; i<R.loc_hi; i+=slots)
+                for (int pbase=0; pbase<npts; pbase+=span)
                 {
-                    LineRec const r = recs[perm[i]];
-                    a += line_point(r, loc_w, (double)pt, b.wres);
-                    ++evals;
+                    int const pt = pbase + my_pt;
+                    if (pt >= npts) continue;
+                    double a = 0.;
+#pragma unroll 2
+                    for (unsigned i=R.loc_lo + my_slot; i<R.loc_hi; i+=lslots)
+                    {
+                        LineRec const r = recs[i];
+                        a += line_point(r, loc_w, (double)pt, b.wres);
+                        ++evals;
+                    }
+                    if (a != 0.) atomicAdd(&sh_acc[g*ppb + pt], a);
                 }
-                if (a != 0.) atomicAdd(&sh_acc[g*ppb + pt], a);
             }
         }
     }
-
-    // block sums of the remote contributions
 #pragma unroll
-    for (int g=0; g<kBinGroup; ++g)
+    for (int l=0; l<kNip; ++l)
     {
-#pragma unroll
-        for (int l=0; l<kNip; ++l)
-        {
-            double vsum = rem[g][l];
-            for (int o=16; o>0; o>>=1) vsum += __shfl_down_sync(0xffffffffu, vsum, o);
-            if ((tid & 31) == 0) sh_warp[tid >> 5][g*kNip + l] = vsum;
-        }
+        double vsum = rem[l];
+        for (int o=16; o>0; o>>=1) vsum += __shfl_down_sync(0xffffffffu, vsum, o);
+        if (lane == 0) sh_rem[g][l] = vsum;
     }
     for (int o=16; o>0; o>>=1) evals += __shfl_down_sync(0xffffffffu, evals, o);
-    if ((tid & 31) == 0 && evals) atomicAdd(p.evals, evals);
-    __syncthreads();
-    if (tid < kBinGroup*kNip)
-    {
-        double t = 0.;
-        for (int w=0; w<kBinThreads/32; ++w) t += sh_warp[w][tid];
-        sh_rem[tid/kNip][tid % kNip] = t;
-    }
+    if (lane == 0 && evals) atomicAdd(p.evals, evals);
     __syncthreads();
 
     // interpolate (kernels.c:514-581) + continua, CFCs, CIA (kernels.c:469-510, 585-630)
     int const L = p.num_layers;
     for (int q=tid; q<ng*ppb; q+=kBinThreads)
     {
-        int const g = q/ppb;
+        int const gq = q/ppb;
         int const pt = q % ppb;
-        unsigned long long const k = k0 + g;
+        unsigned long long const k = k0 + gq;
         if (pt >= bin_points(b, k)) continue;
         unsigned long long const f = bin_left(b, k) + (unsigned long long)pt;
-        double t = sh_acc[g*ppb + pt];
+        double t = sh_acc[gq*ppb + pt];
         if (p.tab.h2o_slot >= 0)
         {
             double const tref = 296.;
@@ -492,7 +476,7 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
             t += p.lay.cia[c*L + layer]*p.tab.cia[c][f];
         }
         bool const interp = (k < b.n - 1) ? (b.do_interp != 0) : (b.do_last_interp != 0);
-        double const y[kNip] = {sh_rem[g][0], sh_rem[g][1], sh_rem[g][2]};
+        double const y[kNip] = {sh_rem[gq][0], sh_rem[gq][1], sh_rem[gq][2]};
         if (interp)
         {
             double const x[kNip] = {bin_w(b, k, 0), bin_w(b, k, 1), bin_w(b, k, 2)};

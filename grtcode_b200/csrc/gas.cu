@@ -371,6 +371,7 @@ struct grt_gas
     double *d_vsorted = nullptr;
     unsigned *d_vidx = nullptr;
     unsigned *d_perm = nullptr;
+    LineRec *d_sorted_recs = nullptr;    // binned methods: records in sorted order
     int *d_seg_begin = nullptr;
     int *d_seg_end = nullptr;
     void *d_sort_temp = nullptr;
@@ -609,12 +610,16 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
             g->d_sort_temp, bytes, g->d_vkey, g->d_vsorted, g->d_vidx, g->d_perm, (int)(N*L), segs,
             g->d_seg_begin, g->d_seg_end, 0, 64, st));
         ++launches;
+        dim3 pgrid((unsigned)((N + 255)/256), (unsigned)L);
+        permute_records_kernel<<<pgrid, 256, 0, st>>>(g->d_recs, g->d_perm, g->d_sorted_recs, N);
+        ++launches;
     }
     GRT_CUDA(cudaEventRecord(g->ev[2], st));
     BinParams bp;
     bp.recs = g->d_recs;
     bp.vs = g->d_vsorted;
     bp.perm = g->d_perm;
+    bp.sorted_recs = g->d_sorted_recs;
     bp.num_lines = N;
     bp.num_slots = N > 0 ? slots : 0;
     for (int sl=0; sl<=GRT_MAX_MOLS; ++sl)
@@ -725,6 +730,7 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_tile_order);
     cudaFree(g->d_work_counter);
     cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
+    cudaFree(g->d_sorted_recs);
     cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_sort_temp); cudaFree(g->d_evals); cudaFree(g->d_ranges);
     for (double *t : g->owned_tables) cudaFree(t);
     for (int k=0; k<5; ++k) if (g->ev[k]) cudaEventDestroy(g->ev[k]);
@@ -908,8 +914,11 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
         if (method != 2 && need > g->binned_capacity)
         {
             cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
+            cudaFree(g->d_sorted_recs);
             g->d_vkey = g->d_vsorted = nullptr;
             g->d_vidx = g->d_perm = nullptr;
+            g->d_sorted_recs = nullptr;
+            GRT_CUDA(cudaMalloc(&g->d_sorted_recs, sizeof(LineRec)*need));
             GRT_CUDA(cudaMalloc(&g->d_vkey, sizeof(double)*need));
             GRT_CUDA(cudaMalloc(&g->d_vsorted, sizeof(double)*need));
             GRT_CUDA(cudaMalloc(&g->d_vidx, sizeof(unsigned)*need));

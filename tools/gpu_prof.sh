@@ -8,5 +8,9 @@ ncu --set full --clock-control none --import-source on -k regex:wing_sweep -s 2 
     -f -o gpurun_out/prof_sweep_q $BENCH > gpurun_out/ncu_q.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:core_sweep -s 3 -c 1 \
     -f -o gpurun_out/prof_core_q $BENCH > gpurun_out/ncu_core_q.log 2>&1
-tail -2 gpurun_out/ncu_q.log; tail -2 gpurun_out/ncu_core_q.log
+# full-size longwave launch (the first wing launch of the run): DRAM traffic of a real launch
+FULL="python bench.py --steps 1 --warmup 1 --no-cpu-baseline"
+GRT_BENCH_RFMIP=0 ncu --set full --clock-control none --import-source on -k regex:wing_sweep -s 0 -c 1 \
+    -f -o gpurun_out/prof_wing_lw_full $FULL > gpurun_out/ncu_lw_full.log 2>&1
+tail -2 gpurun_out/ncu_q.log; tail -2 gpurun_out/ncu_core_q.log; tail -2 gpurun_out/ncu_lw_full.log
 grep '^{' gpurun_out/plain_q.log | cut -c1-400
