@@ -7,11 +7,16 @@
  *   - v and S stay double; gamma_air, gamma_self, E'', n_air and delta are rounded
  *     through float (:197-213, 331-345) -- this is part of the numerical contract;
  *   - finally S *= Q(296)/(exp(c2 E''/296)(1 - exp(c2 v/296))), c2 = -1.4387686f (:372-384).
- * The whole file is read in one pass into memory instead of twice line by line. */
+ * The file is read and converted once per process, see HitranTable_t below. */
 #include <float.h>
 #include <math.h>
+#include <pthread.h>
+#include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include "errors.h"
 #include "hitran.h"
 #include "tips.h"
@@ -79,6 +84,303 @@ static int field_float(char const *rec, int offset, int width, int column, fp_t 
     return GRTCODE_SUCCESS;
 }
 
+/* Isotopologue code (parse_HITRAN_file.c:177-194). */
+static int parse_iso(char const c, int *iso)
+{
+    if (c == '0')
+    {
+        *iso = 10;
+        return GRTCODE_SUCCESS;
+    }
+    if (c >= 'A' && c <= 'Z')
+    {
+        *iso = c - 'A' + 11;
+        return GRTCODE_SUCCESS;
+    }
+    char tmp[2];
+    tmp[0] = c;
+    tmp[1] = '\0';
+    return to_int(tmp, iso);
+}
+
+/* One record -> one row.  offsets: 3 v(12) | 15 S(10) | 25 A(10) | 35 g_air(5) |
+   40 g_self(5) | 45 E''(10) | 55 n(4) | 59 delta(8). */
+static int parse_record(char const *rec, int *iso, fp_t *vnn, fp_t *snn, fp_t *yair,
+                        fp_t *yself, fp_t *en, fp_t *n, fp_t *d)
+{
+    int rc = parse_iso(rec[2], iso);
+    if (rc == GRTCODE_SUCCESS) rc = field_double(rec, 3, 12, vnn);
+    if (rc == GRTCODE_SUCCESS) rc = field_double(rec, 15, 10, snn);
+    if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 35, 5, 5, yair);
+    if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 40, 5, 6, yself);
+    if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 45, 10, 7, en);
+    if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 55, 4, 8, n);
+    if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 59, 8, 9, d);
+    return rc;
+}
+
+/* The reference reads the whole file once per add_molecule (parse_HITRAN_file.c:224-413:
+ * 14 passes for seven molecules on two grids).  Here a file is read and converted ONCE, by
+ * all host cores, into a table of every record; parse_hitran_file() then filters that
+ * table by molecule and wavenumber range.  The table is keyed by (path, size, mtime); the
+ * two most recently used files are kept (one per spectral band). */
+enum { ROW_OK = 0, ROW_BAD_MOLECULE = 1, ROW_BAD_FIELD = 2 };
+
+typedef struct HitranTable
+{
+    char *path;
+    off_t size;
+    struct timespec mtime;
+    uint64_t num_records;
+    char *text;               /* the file, kept while rows may have to be re-read for errors */
+    uint64_t *start;          /* offset of every record in text */
+    signed char *status;
+    short *mol;
+    int *iso;
+    fp_t *vnn, *snn, *yair, *yself, *en, *n, *d;
+    uint64_t stamp;
+} HitranTable_t;
+
+#define TABLE_SLOTS 2
+static HitranTable_t tables[TABLE_SLOTS];
+static uint64_t table_clock = 0;
+
+static void free_table(HitranTable_t *t)
+{
+    free(t->path); free(t->text); free(t->start); free(t->status); free(t->mol); free(t->iso);
+    free(t->vnn); free(t->snn); free(t->yair); free(t->yself); free(t->en); free(t->n);
+    free(t->d);
+    memset(t, 0, sizeof(*t));
+}
+
+void grt_hitran_cache_clear(void)
+{
+    int i;
+    for (i=0; i<TABLE_SLOTS; ++i)
+    {
+        free_table(&tables[i]);
+    }
+}
+
+typedef struct ParseJob
+{
+    HitranTable_t *t;
+    uint64_t first, last;
+} ParseJob_t;
+
+/* Worker: converts rows [first, last).  No error text here (the error buffer is global):
+ * a failing row is only marked and re-read serially when a caller asks for it. */
+static void *parse_rows(void *arg)
+{
+    ParseJob_t const *job = (ParseJob_t const *)arg;
+    HitranTable_t *t = job->t;
+    uint64_t i;
+    for (i=job->first; i<job->last; ++i)
+    {
+        char const *rec = t->text + t->start[i];
+        char tmp[3];
+        tmp[0] = rec[0];
+        tmp[1] = rec[1];
+        tmp[2] = '\0';
+        char *end = NULL;
+        long const mol = strtol(tmp, &end, 10);
+        if (end == tmp || *end != '\0')
+        {
+            t->status[i] = ROW_BAD_MOLECULE;
+            t->mol[i] = -1;
+            continue;
+        }
+        t->mol[i] = (short)mol;
+        t->status[i] = ROW_OK;
+    }
+    return NULL;
+}
+
+static void *convert_rows(void *arg)
+{
+    ParseJob_t const *job = (ParseJob_t const *)arg;
+    HitranTable_t *t = job->t;
+    uint64_t i;
+    for (i=job->first; i<job->last; ++i)
+    {
+        if (t->status[i] != ROW_OK)
+        {
+            continue;
+        }
+        if (parse_record(t->text + t->start[i], &t->iso[i], &t->vnn[i], &t->snn[i], &t->yair[i],
+                         &t->yself[i], &t->en[i], &t->n[i], &t->d[i]) != GRTCODE_SUCCESS)
+        {
+            t->status[i] = ROW_BAD_FIELD;
+        }
+    }
+    return NULL;
+}
+
+static int worker_count(uint64_t const rows)
+{
+    long n = sysconf(_SC_NPROCESSORS_ONLN);
+    char const *env = getenv("GRT_PARSE_THREADS");
+    if (env != NULL && atoi(env) > 0)
+    {
+        n = atoi(env);
+    }
+    if (n > 64) n = 64;
+    if (n < 1) n = 1;
+    if ((uint64_t)n > rows/4096 + 1) n = (long)(rows/4096 + 1);
+    return (int)n;
+}
+
+static void run_parallel(HitranTable_t *t, void *(*fn)(void *))
+{
+    int const nthreads = worker_count(t->num_records);
+    pthread_t tid[64];
+    ParseJob_t job[64];
+    int started[64];
+    int k;
+    for (k=0; k<nthreads; ++k)
+    {
+        job[k].t = t;
+        job[k].first = t->num_records*(uint64_t)k/(uint64_t)nthreads;
+        job[k].last = t->num_records*(uint64_t)(k + 1)/(uint64_t)nthreads;
+        started[k] = (k > 0) && (pthread_create(&tid[k], NULL, fn, &job[k]) == 0);
+    }
+    for (k=0; k<nthreads; ++k)
+    {
+        if (!started[k])
+        {
+            fn(&job[k]);       /* the caller's share, and any share whose thread failed to start */
+        }
+    }
+    for (k=0; k<nthreads; ++k)
+    {
+        if (started[k])
+        {
+            pthread_join(tid[k], NULL);
+        }
+    }
+}
+
+/* Reads and converts a file; bad record lengths are reported exactly as the reference does. */
+static int load_table(HitranTable_t *t, char const *filepath, struct stat const *st)
+{
+    FILE *fp = NULL;
+    TRY(open_file(&fp, filepath, "r"));
+    size_t const size = (size_t)st->st_size;
+    t->text = (char *)malloc(size + 1);
+    if (t->text == NULL)
+    {
+        fclose(fp);
+        FAIL(GRTCODE_NULL_ERR, "out of memory reading %s.", filepath);
+    }
+    size_t const got = fread(t->text, 1, size, fp);
+    if (fclose(fp) != 0 || got != size)
+    {
+        FAIL(GRTCODE_IO_ERR, "error reading file %s.", filepath);
+    }
+    t->text[size] = '\0';
+    /* index the records */
+    uint64_t capacity = size/(RECORD_LEN + 1) + 2;
+    t->start = (uint64_t *)malloc(sizeof(uint64_t)*capacity);
+    if (t->start == NULL)
+    {
+        FAIL(GRTCODE_NULL_ERR, "out of memory indexing %s.", filepath);
+    }
+    uint64_t n = 0;
+    size_t pos = 0;
+    while (pos < size)
+    {
+        char const *nl = (char const *)memchr(t->text + pos, '\n', size - pos);
+        size_t const ll = nl != NULL ? (size_t)(nl - (t->text + pos)) + 1 : size - pos;
+        if (ll > RECORD_LEN + RECORD_PAD || ll < RECORD_LEN)
+        {
+            grt_error_reset();
+            char m[512];
+            snprintf(m, sizeof(m), "Error: Found bad record at line %llu (%zu characters, expected"
+                     " %d to %d) in file %s.\nBacktrace:", (unsigned long long)(n + 1), ll,
+                     RECORD_LEN, RECORD_LEN + RECORD_PAD, filepath);
+            grt_error_append(m);
+            grt_error_frame(__FILE__, __LINE__);
+            return GRTCODE_VALUE_ERR;
+        }
+        if (n == capacity)
+        {
+            capacity *= 2;
+            uint64_t *grown = (uint64_t *)realloc(t->start, sizeof(uint64_t)*capacity);
+            if (grown == NULL)
+            {
+                FAIL(GRTCODE_NULL_ERR, "out of memory indexing %s.", filepath);
+            }
+            t->start = grown;
+        }
+        t->start[n++] = pos;
+        pos += ll;
+    }
+    t->num_records = n;
+    size_t const c = n > 0 ? n : 1;
+    t->status = (signed char *)malloc(c);
+    t->mol = (short *)malloc(sizeof(short)*c);
+    t->iso = (int *)malloc(sizeof(int)*c);
+    t->vnn = (fp_t *)malloc(sizeof(fp_t)*c);
+    t->snn = (fp_t *)malloc(sizeof(fp_t)*c);
+    t->yair = (fp_t *)malloc(sizeof(fp_t)*c);
+    t->yself = (fp_t *)malloc(sizeof(fp_t)*c);
+    t->en = (fp_t *)malloc(sizeof(fp_t)*c);
+    t->n = (fp_t *)malloc(sizeof(fp_t)*c);
+    t->d = (fp_t *)malloc(sizeof(fp_t)*c);
+    if (!t->status || !t->mol || !t->iso || !t->vnn || !t->snn || !t->yair || !t->yself ||
+        !t->en || !t->n || !t->d)
+    {
+        FAIL(GRTCODE_NULL_ERR, "out of memory for %llu spectral lines.", (unsigned long long)n);
+    }
+    run_parallel(t, parse_rows);
+    run_parallel(t, convert_rows);
+    return GRTCODE_SUCCESS;
+}
+
+static int find_table(char const *filepath, HitranTable_t **found)
+{
+    struct stat st;
+    if (stat(filepath, &st) != 0)
+    {
+        /* let open_file produce the reference's message */
+        FILE *fp = NULL;
+        TRY(open_file(&fp, filepath, "r"));
+        fclose(fp);
+        FAIL(GRTCODE_IO_ERR, "cannot stat file %s.", filepath);
+    }
+    int i;
+    int victim = 0;
+    for (i=0; i<TABLE_SLOTS; ++i)
+    {
+        HitranTable_t *t = &tables[i];
+        if (t->path != NULL && strcmp(t->path, filepath) == 0 && t->size == st.st_size &&
+            t->mtime.tv_sec == st.st_mtim.tv_sec && t->mtime.tv_nsec == st.st_mtim.tv_nsec)
+        {
+            t->stamp = ++table_clock;
+            *found = t;
+            return GRTCODE_SUCCESS;
+        }
+        if (tables[i].stamp < tables[victim].stamp)
+        {
+            victim = i;
+        }
+    }
+    HitranTable_t *t = &tables[victim];
+    free_table(t);
+    int const rc = load_table(t, filepath, &st);
+    if (rc != GRTCODE_SUCCESS)
+    {
+        free_table(t);
+        return rc;
+    }
+    t->path = strdup(filepath);
+    t->size = st.st_size;
+    t->mtime = st.st_mtim;
+    t->stamp = ++table_clock;
+    *found = t;
+    return GRTCODE_SUCCESS;
+}
+
 int parse_hitran_file(LineParams_t * const out, char const * const filepath, int const mol_id,
                       double const w0, double const wn)
 {
@@ -86,105 +388,64 @@ int parse_hitran_file(LineParams_t * const out, char const * const filepath, int
     REQUIRE_PTR(filepath);
     memset(out, 0, sizeof(*out));
     LOG_INFO("Opening and reading HITRAN line parameters from file %s.", filepath);
-    FILE *fp = NULL;
-    TRY(open_file(&fp, filepath, "r"));
-    LineParams_t lp;
-    memset(&lp, 0, sizeof(lp));
-    uint64_t capacity = 1 << 16;
-    int rc = reserve(&lp, capacity);
-    char *buf = NULL;
-    size_t buf_len = 0;
-    ssize_t ll;
+    HitranTable_t *t = NULL;
+    TRY(find_table(filepath, &t));
+    /* first pass: count, and stop at the first row the reference would have failed on */
+    uint64_t i;
     uint64_t n = 0;
-    size_t line_count = 0;
-    while (rc == GRTCODE_SUCCESS && (ll = getline(&buf, &buf_len, fp)) != -1)
+    for (i=0; i<t->num_records; ++i)
     {
-        ++line_count;
-        if (ll > RECORD_LEN + RECORD_PAD || ll < RECORD_LEN)
+        if (t->status[i] == ROW_BAD_MOLECULE)
         {
-            grt_error_reset();
-            char m[512];
-            snprintf(m, sizeof(m), "Error: Found bad record at line %zu (%zd characters, expected"
-                     " %d to %d) in file %s.\nBacktrace:", line_count, ll, RECORD_LEN,
-                     RECORD_LEN + RECORD_PAD, filepath);
-            grt_error_append(m);
-            grt_error_frame(__FILE__, __LINE__);
-            rc = GRTCODE_VALUE_ERR;
-            break;
+            char tmp[3];
+            int mol;
+            tmp[0] = t->text[t->start[i]];
+            tmp[1] = t->text[t->start[i] + 1];
+            tmp[2] = '\0';
+            TRY(to_int(tmp, &mol));           /* produces the conversion error */
+            FAIL(GRTCODE_VALUE_ERR, "bad molecule id in record %llu.", (unsigned long long)(i + 1));
         }
-        char tmp[4];
-        tmp[0] = buf[0];
-        tmp[1] = buf[1];
-        tmp[2] = '\0';
-        int mol;
-        rc = to_int(tmp, &mol);
-        if (rc != GRTCODE_SUCCESS || mol != mol_id)
+        if (t->mol[i] != mol_id)
         {
             continue;
         }
-        if (n == capacity)
+        if (t->status[i] == ROW_BAD_FIELD)
         {
-            capacity *= 2;
-            rc = reserve(&lp, capacity);
-            if (rc != GRTCODE_SUCCESS)
-            {
-                break;
-            }
+            int iso;
+            fp_t f[7];
+            TRY(parse_record(t->text + t->start[i], &iso, &f[0], &f[1], &f[2], &f[3], &f[4], &f[5],
+                             &f[6]));
+            FAIL(GRTCODE_VALUE_ERR, "bad field in record %llu.", (unsigned long long)(i + 1));
         }
-        char const c = buf[2];
-        if (c == '0')
-        {
-            lp.iso[n] = 10;
-        }
-        else if (c >= 'A' && c <= 'Z')
-        {
-            lp.iso[n] = c - 'A' + 11;
-        }
-        else
-        {
-            tmp[0] = c;
-            tmp[1] = '\0';
-            rc = to_int(tmp, &lp.iso[n]);
-        }
-        /* offsets: 3 v(12) | 15 S(10) | 25 A(10) | 35 g_air(5) | 40 g_self(5) |
-           45 E''(10) | 55 n(4) | 59 delta(8) */
-        if (rc == GRTCODE_SUCCESS) rc = field_double(buf, 3, 12, &lp.vnn[n]);
-        if (rc == GRTCODE_SUCCESS) rc = field_double(buf, 15, 10, &lp.snn[n]);
-        if (rc == GRTCODE_SUCCESS) rc = field_float(buf, 35, 5, 5, &lp.yair[n]);
-        if (rc == GRTCODE_SUCCESS) rc = field_float(buf, 40, 5, 6, &lp.yself[n]);
-        if (rc == GRTCODE_SUCCESS) rc = field_float(buf, 45, 10, 7, &lp.en[n]);
-        if (rc == GRTCODE_SUCCESS) rc = field_float(buf, 55, 4, 8, &lp.n[n]);
-        if (rc == GRTCODE_SUCCESS) rc = field_float(buf, 59, 8, 9, &lp.d[n]);
-        if (rc != GRTCODE_SUCCESS)
-        {
-            grt_error_frame(__FILE__, __LINE__);
-            break;
-        }
-        if ((w0 < 0 && wn < 0) || (lp.vnn[n] >= w0 && lp.vnn[n] <= wn))
+        if ((w0 < 0 && wn < 0) || (t->vnn[i] >= w0 && t->vnn[i] <= wn))
         {
             ++n;
         }
     }
-    free(buf);
-    if (fclose(fp) != 0 && rc == GRTCODE_SUCCESS)
-    {
-        free_line_params(&lp);
-        FAIL(GRTCODE_IO_ERR, "error closing file %s.", filepath);
-    }
-    if (rc != GRTCODE_SUCCESS)
-    {
-        free_line_params(&lp);
-        return rc;
-    }
-
-    /* Scale the raw intensities (parse_HITRAN_file.c:372-384). */
+    LineParams_t lp;
+    memset(&lp, 0, sizeof(lp));
+    TRY(reserve(&lp, n));
+    uint64_t k = 0;
     fp_t const tref = 296.f;
     fp_t const c2 = -1.4387686f;
-    uint64_t i;
-    for (i=0; i<n; ++i)
+    for (i=0; i<t->num_records; ++i)
     {
-        lp.snn[i] *= grt_tips_q(mol_id, tref, lp.iso[i])/(exp(c2*lp.en[i]/tref)*
-                     (1.f - exp(c2*lp.vnn[i]/tref)));
+        if (t->mol[i] != mol_id ||
+            !((w0 < 0 && wn < 0) || (t->vnn[i] >= w0 && t->vnn[i] <= wn)))
+        {
+            continue;
+        }
+        lp.iso[k] = t->iso[i];
+        lp.vnn[k] = t->vnn[i];
+        lp.yair[k] = t->yair[i];
+        lp.yself[k] = t->yself[i];
+        lp.en[k] = t->en[i];
+        lp.n[k] = t->n[i];
+        lp.d[k] = t->d[i];
+        /* Scale the raw intensity (parse_HITRAN_file.c:372-384). */
+        lp.snn[k] = t->snn[i]*(grt_tips_q(mol_id, tref, lp.iso[k])/(exp(c2*lp.en[k]/tref)*
+                    (1.f - exp(c2*lp.vnn[k]/tref))));
+        ++k;
     }
     lp.num_lines = n;
     *out = lp;

@@ -22,4 +22,7 @@ typedef struct LineParams
 int parse_hitran_file(LineParams_t * const line_params, char const * const filepath,
                       int const mol_id, double const w0, double const wn);
 void free_line_params(LineParams_t * const line_params);
+/* Drops the parsed-file tables kept between parse_hitran_file() calls (hitran.c). */
+void grt_hitran_cache_clear(void);
+
 #endif

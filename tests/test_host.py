@@ -158,6 +158,62 @@ def test_hitran_parser_matches_oracle(built, tmp_path):
     assert L.parse_hitran_file(C.byref(lp), b"/nonexistent.par", 1, -1., -1.) == 11   # IO_ERR
 
 
+def test_hitran_table_cache_and_error_rows(built, tmp_path):
+    """The parser converts a file once (all host cores) and serves every molecule from the
+    table.  What a caller of the reference would see must not change: a field that cannot be
+    converted fails only the molecule it belongs to (parse_HITRAN_file.c:310 skips other
+    molecules before converting), a rewritten file is read again, thread count does not
+    change the result."""
+    import os
+    L = built.load()
+    L.parse_hitran_file.argtypes = [C.POINTER(_LineParams), C.c_char_p, C.c_int, C.c_double,
+                                    C.c_double]
+    ds = synth.make_dataset(str(tmp_path), 100., 900., {1: 6000, 2: 9000}, seed=4)
+    path = ds.hitran.encode()
+
+    def parse(mol):
+        lp = _LineParams()
+        rc = L.parse_hitran_file(C.byref(lp), path, mol, -1., -1.)
+        if rc != 0:
+            return rc, None
+        n = int(lp.num_lines)
+        out = {f: np.ctypeslib.as_array(getattr(lp, f), shape=(n,)).copy()
+               for f in ("vnn", "snn", "yair", "yself", "en", "n", "d")}
+        L.free_line_params(C.byref(lp))
+        return 0, out
+
+    os.environ["GRT_PARSE_THREADS"] = "1"
+    L.grt_hitran_cache_clear()
+    rc, one = parse(2)
+    assert rc == 0 and len(one["vnn"]) == 9000
+    os.environ["GRT_PARSE_THREADS"] = "7"
+    L.grt_hitran_cache_clear()
+    rc, many = parse(2)
+    del os.environ["GRT_PARSE_THREADS"]
+    assert rc == 0 and all(np.array_equal(one[f], many[f]) for f in one)
+    # corrupt the strength field of one H2O record: H2O fails, CO2 is untouched
+    rows = open(ds.hitran).read().split("\n")
+    k = next(i for i, r in enumerate(rows) if r.startswith(" 1"))
+    rows[k] = rows[k][:15] + "  garbage " + rows[k][25:]
+    assert len(rows[k]) == 160
+    st = os.stat(ds.hitran)
+    open(ds.hitran, "w").write("\n".join(rows))
+    os.utime(ds.hitran, ns=(st.st_atime_ns, st.st_mtime_ns + 1_000_000_000))
+    rc, _ = parse(1)
+    assert rc != 0
+    buf = C.create_string_buffer(4096)
+    L.grtcode_errstr(rc, buf, 4096)
+    msg = buf.value.decode(errors="replace")
+    assert "garbage" in msg or "convert" in msg.lower() or "record" in msg.lower(), msg
+    rc, again = parse(2)
+    assert rc == 0 and all(np.array_equal(one[f], again[f]) for f in one)
+    # a non-numeric molecule field fails every request, as the reference's loop does
+    rows[k] = "xx" + rows[k][2:]
+    open(ds.hitran, "w").write("\n".join(rows))
+    os.utime(ds.hitran, ns=(st.st_atime_ns, st.st_mtime_ns + 2_000_000_000))
+    assert parse(2)[0] != 0
+
+
 def test_tables_and_solar_match_oracle(built, tmp_path):
     ds = synth.make_dataset(str(tmp_path), 1., 3000., {1: 10}, seed=2, cfcs=("CFC11",),
                             cias=((0, 0),))
