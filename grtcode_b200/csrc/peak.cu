@@ -102,6 +102,9 @@ __global__ void selftest_kernel(unsigned long long n, unsigned long long seed,
         unpack2(div_exact2(pack2(a, a2), pack2(b, b2)), p1, p2);
         if (__float_as_uint(p1) != __float_as_uint(q2)) ++local;
         if (__float_as_uint(p2) != __float_as_uint(__fdiv_rn(a2, b2))) ++local;
+        unpack2(div_exact2_seeded(pack2(a, a2), pack2(b, b2)), p1, p2);
+        if (__float_as_uint(p1) != __float_as_uint(q2)) ++local;
+        if (__float_as_uint(p2) != __float_as_uint(__fdiv_rn(a2, b2))) ++local;
         // x*x + yq must round twice (RFM_voigt.c:166,170): the packed add of scalar products
         float s1, s2;
         unpack2(add2(mul2_unfused(pack2(a, a2), pack2(a, a2)), pack2(b, b2)), s1, s2);

@@ -306,6 +306,10 @@ __device__ __forceinline__ void accumulate2(double &a0, double &a1, double const
     a1 = fma(c, widen_positive(k1), a1);
 }
 
+#ifndef GRT_SEED_MIX
+#define GRT_SEED_MIX 0
+#endif
+
 // kClsFast: the tile lies wholly inside the line's window and wholly in its far wing:
 // no predicates, PTS independent dependency chains in flight, two samples per packed op.
 template <int PTS, bool TBL>
@@ -320,7 +324,11 @@ __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileC
     for (int j=0; j<PTS; j+=2)
     {
         f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
-        accumulate2(acc[j], acc[j+1], A.y, far_wing2(mul2_unfused(xi, xi), yq2, yr2));
+        f32x2 const xq = mul2_unfused(xi, xi);
+        // GRT_SEED_MIX of every four pairs take the XU-free division (voigt.cuh)
+        f32x2 const k = ((j/2) % 4 < GRT_SEED_MIX) ? div_exact2_seeded(yr2, add2(xq, yq2))
+                                                   : far_wing2(xq, yq2, yr2);
+        accumulate2(acc[j], acc[j+1], A.y, k);
     }
 }
 
