@@ -371,6 +371,7 @@ struct grt_gas
     double *d_vsorted = nullptr;
     unsigned *d_vidx = nullptr;
     unsigned *d_perm = nullptr;
+    bool tiles_spectral = false;         // tile order of the sweep: spectral + tile-major items
     LineRec *d_sorted_recs = nullptr;    // binned methods: records in sorted order
     int *d_seg_begin = nullptr;
     int *d_seg_end = nullptr;
@@ -500,6 +501,16 @@ static int prepare_tiles(grt_gas *g, int pts, double margin, double shift)
         last[t] = (unsigned)(b - v0.begin());
         cost[t] = {(uint64_t)(b - a), t};
     }
+    // Order of the work items.  Few items (less than 16 per warp in flight): layer groups one
+    // after the other, heaviest tiles first inside a group (LPT), which trims the tail (2 %
+    // on a config-1 column).  Otherwise: tiles in spectral order, all layers of a tile adjacent,
+    // so that the warps in flight work on neighbouring tiles (records shared through L2) and
+    // the continuum / CFC / CIA tables of a tile are read from DRAM once, not once per layer
+    // (11 tables x 40 MB x 54 layers = 24 GB per config-2 shortwave launch otherwise).
+    bool spectral = (size_t)num_tiles*(size_t)g->num_layers >= 16u*24u*(size_t)sm_count(g->device);
+    if (char const *env = getenv("GRT_TILE_ORDER")) spectral = (env[0] == 's');
+    g->tiles_spectral = spectral;
+    if (!spectral)
     std::stable_sort(cost.begin(), cost.end(),
                      [](auto const &x, auto const &y) { return x.first > y.first; });
     std::vector<int> order((size_t)num_tiles);
@@ -966,6 +977,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     GRT_TRY(prepare_tiles(g, pts, margin, g->max_abs_delta*pmax));
     sp.num_tiles = g->num_tiles;
     sp.tile_order = g->d_tile_order;
+    sp.tile_major = g->tiles_spectral ? 1 : 0;
     sp.tile_first = g->d_tile_first;
     sp.tile_last = g->d_tile_last;
     sp.work_counter = g->d_work_counter;

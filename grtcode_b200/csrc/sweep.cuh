@@ -40,7 +40,8 @@ struct SweepParams
     int fsteps;
     int num_layers;
     int num_tiles;             // warp tiles of 32*PTS grid points
-    int const *tile_order;     // tiles sorted by line count, heaviest first
+    int const *tile_order;     // tiles heaviest first (LPT), or in spectral order
+    int tile_major;            // items run tile by tile (all layers of a tile adjacent)
     unsigned const *tile_first;  // per tile: first record whose window may reach it
     unsigned const *tile_last;   // per tile: one past the last such record
     unsigned int *work_counter;
@@ -801,8 +802,10 @@ wing_sweep_kernel(SweepParams const p)
         if (lane == 0) item = atomicAdd(p.work_counter, 1u);
         item = __shfl_sync(0xffffffffu, item, 0);
         if (item >= total) break;
-        int const group = (int)(item/(unsigned)p.num_tiles);
-        int const slot = (int)(item%(unsigned)p.num_tiles);
+        // tile-major: the layers of a tile follow each other, so its continuum / CFC / CIA
+        // table values are read from DRAM once instead of once per layer
+        int const group = p.tile_major ? (int)(item%(unsigned)groups) : (int)(item/(unsigned)p.num_tiles);
+        int const slot = p.tile_major ? (int)(item/(unsigned)groups) : (int)(item%(unsigned)p.num_tiles);
         int const tile = p.tile_order[slot];
         unsigned const first = p.tile_first[tile];
         unsigned const last = p.tile_last[tile];
