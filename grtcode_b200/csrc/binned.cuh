@@ -355,8 +355,9 @@ bin_ranges_kernel(BinParams const p, BinRanges32 *out)
 // see almost the same remote lines (25 bins either side), so the eight warps stream the same
 // records through L1 at the same time.  Remote lines: lanes take consecutive records and
 // evaluate the bin's three interpolation points (three register accumulators per thread for
-// the whole kernel).  Local lines: the warp's lanes form a (line, grid point) grid over the
-// bin's points.  No block barrier inside the molecule loop.
+// the whole kernel).  Local lines: a lane per line with shuffle sums on coarse grids, a lane per
+// grid point on fine ones.  The warp owns its bin's accumulators: no atomics, no block
+// barrier inside the molecule loop.
 #ifndef GRT_BIN_MINBLOCKS
 #define GRT_BIN_MINBLOCKS 4
 #endif
@@ -384,10 +385,6 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
         double const rem_res = __dsub_rn(bin_w(b, k, 1), rem_w);
         int const npts = bin_points(b, k);
         double const loc_w = __dadd_rn(b.w0, __dmul_rn((double)bin_left(b, k), b.wres));
-        int const span = npts < 32 ? npts : 32;
-        int const lslots = 32/span;
-        int const my_slot = lane/span;
-        int const my_pt = lane % span;
         for (int s=0; s<p.num_slots; ++s)
         {
             unsigned long long const off = p.slot_off[s];
@@ -410,21 +407,41 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
                 }
             }
             // local lines on the bin's grid points
-            if (my_slot < lslots)
+            if (npts <= 16)
             {
-                for (int pbase=0; pbase<npts; pbase+=span)
+                // coarse grid: a lane per line (consecutive lines of the sorted list sit at
+                // nearly the same distance from a grid point, so the warp takes the same
+                // Voigt branch), each point's sum over the 32 lines by shuffles
+                for (unsigned i0=R.loc_lo; i0<R.loc_hi; i0+=32)
                 {
-                    int const pt = pbase + my_pt;
+                    unsigned const i = i0 + lane;
+                    bool const have = i < R.loc_hi;
+                    LineRec const r = recs[have ? i : R.loc_lo];
+                    if (have) evals += (unsigned long long)npts;
+                    for (int pt=0; pt<npts; ++pt)
+                    {
+                        double a = have ? line_point(r, loc_w, (double)pt, b.wres) : 0.;
+                        for (int o=16; o>0; o>>=1) a += __shfl_down_sync(0xffffffffu, a, o);
+                        if (lane == 0) sh_acc[g*ppb + pt] += a;
+                    }
+                }
+            }
+            else
+            {
+                // fine grid: a lane per grid point (32 at a time), every local line in turn
+                for (int pbase=0; pbase<npts; pbase+=32)
+                {
+                    int const pt = pbase + lane;
                     if (pt >= npts) continue;
                     double a = 0.;
 #pragma unroll 2
-                    for (unsigned i=R.loc_lo + my_slot; i<R.loc_hi; i+=lslots)
+                    for (unsigned i=R.loc_lo; i<R.loc_hi; ++i)
                     {
                         LineRec const r = recs[i];
                         a += line_point(r, loc_w, (double)pt, b.wres);
                         ++evals;
                     }
-                    if (a != 0.) atomicAdd(&sh_acc[g*ppb + pt], a);
+                    sh_acc[g*ppb + pt] += a;
                 }
             }
         }
