@@ -227,6 +227,21 @@ def workload_config(args, lw, sw, layers):
             "l2": "inputs larger than L2 (line records + tau > 2 GB per band)"}
 
 
+def recorded_wing_traffic(args):
+    """DRAM bytes (read + write) per wing_sweep_kernel launch, averaged over the LW and SW
+    launches of a step, from the latest ncu capture committed under profiles/ (ncu cannot run
+    inside a timed bench; the figure is only valid for the full-size line_sample workload it
+    was captured on, else None)."""
+    import glob
+    if args.scale != 1. or args.method != "line_sample":
+        return None
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_wing_dram.json")))
+    if not files:
+        return None
+    rec = json.load(open(files[-1]))["launches"]
+    return sum(r["dram_read_bytes"] + r["dram_write_bytes"] for r in rec)/len(rec)
+
+
 def rfmip_probe(args, bands2, device, rank, world, barrier, stream, torch, dist, ncols: int = 4):
     """Secondary figure, BASELINE config 3 shape: RFMIP-IRF-like columns (61 levels, LW 1-3250
     + SW 1-50000 cm-1 at 0.1 cm-1, the same synthetic line lists as config 2), `ncols` columns
@@ -385,7 +400,7 @@ def run_ours(args):
         "kernel": "wing_sweep_kernel" if args.method == "line_sample" else "bin_gather_kernel",
         "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": achieved/fp64_peak if achieved else None,
-        "traffic": None,
+        "traffic": recorded_wing_traffic(args),
         "peak_source": "measured here: dependent-free DFMA chains, all SMs (grt_measure_fma_peak); "
                        "MEASURED_PEAKS.json has no FP64 figure",
         "flop_per_sample": FLOP_PER_SAMPLE,
