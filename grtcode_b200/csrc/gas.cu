@@ -363,7 +363,7 @@ struct grt_gas
     int num_tiles = 0;
     unsigned *d_tile_first = nullptr;    // (inside the d_tile_order allocation)
     unsigned *d_tile_last = nullptr;
-    int tiles_pts = 0;                   // PTS the work list was built for
+    int tiles_pts = 0;                   // points per tile the work list was built for
     double tiles_margin = 0.;            // margin [cm-1] it was built with
     int order_method = -1;               // line order the device list was built for
     std::vector<unsigned> slot_off;      // molecule segments of the molecule-major order
@@ -482,11 +482,11 @@ static int finalize_lines(grt_gas *g, int const method)
 // of records whose window can reach it (binary searches in the sorted centres, with the
 // pressure-shift margin) and the tiles ordered by that count, heaviest first, so that
 // the dynamic scheduler ends with the cheap tiles (longest-processing-time-first).
-static int prepare_tiles(grt_gas *g, int pts, double margin, double shift)
+static int prepare_tiles(grt_gas *g, int tile_points, double margin, double shift)
 {
-    if (g->tiles_pts == pts && g->tiles_margin >= margin && g->d_tile_order != nullptr) return 0;
+    if (g->tiles_pts == tile_points && g->tiles_margin >= margin && g->d_tile_order != nullptr) return 0;
     margin += 0.25*shift;   // head-room so that a slightly larger surface pressure does not rebuild
-    int const tile = 32*pts;
+    int const tile = tile_points;
     int const num_tiles = (int)((g->nw + tile - 1)/tile);
     std::vector<double> const &v0 = g->h_sorted_v0;
     std::vector<std::pair<uint64_t, int>> cost((size_t)num_tiles);
@@ -528,7 +528,7 @@ static int prepare_tiles(grt_gas *g, int pts, double margin, double shift)
                              cudaMemcpyHostToDevice, g->stream));
     GRT_CUDA(cudaStreamSynchronize(g->stream));
     g->num_tiles = num_tiles;
-    g->tiles_pts = pts;
+    g->tiles_pts = tile_points;
     g->tiles_margin = margin;
     return 0;
 }
@@ -537,38 +537,38 @@ static int prepare_tiles(grt_gas *g, int pts, double margin, double shift)
 // TBL kernels carry the fl(i*wres) table behind the record rings in shared memory.
 constexpr int kMaxTableBytes = 64*1024;
 
-template <int PTS, int NL, bool TBL>
+template <int PTS, int NL, bool TBL, int LN>
 static int launch_wing_impl(SweepParams const &sp, int const sms, cudaStream_t const st)
 {
     using Cfg = SweepConfig<PTS, NL>;
     static bool configured = false;
     if (!configured)
     {
-        GRT_CUDA(cudaFuncSetAttribute(wing_sweep_kernel<PTS, NL, TBL>,
+        GRT_CUDA(cudaFuncSetAttribute(wing_sweep_kernel<PTS, NL, TBL, LN>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       Cfg::kRingBytes + (TBL ? kMaxTableBytes : 0)));
         configured = true;
     }
-    int const smem = Cfg::kRingBytes + (TBL ? 8*sweep_table_entries<PTS>(sp.fsteps) : 0);
+    int const smem = Cfg::kRingBytes + (TBL ? 8*sweep_table_entries<PTS, LN>(sp.fsteps) : 0);
     int per_sm = 0;
-    GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<PTS, NL, TBL>,
+    GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<PTS, NL, TBL, LN>,
                                                            kSweepThreads, smem));
     int const groups = (sp.num_layers + NL - 1)/NL;
     unsigned const total = (unsigned)sp.num_tiles*(unsigned)groups;
     unsigned const grid = std::min<unsigned>((total + kSweepWarps - 1)/kSweepWarps,
                                              (unsigned)(sms*std::max(per_sm, 1)));
-    wing_sweep_kernel<PTS, NL, TBL><<<std::max(grid, 1u), kSweepThreads, smem, st>>>(sp);
+    wing_sweep_kernel<PTS, NL, TBL, LN><<<std::max(grid, 1u), kSweepThreads, smem, st>>>(sp);
     GRT_CUDA(cudaGetLastError());
     return 0;
 }
 
-template <int PTS, int NL>
+template <int PTS, int NL, int LN = 32>
 static int launch_wing(SweepParams const &sp, int const sms, cudaStream_t const st)
 {
-    bool table = 8*sweep_table_entries<PTS>(sp.fsteps) <= kMaxTableBytes;
+    bool table = 8*sweep_table_entries<PTS, LN>(sp.fsteps) <= kMaxTableBytes;
     if (char const *env = getenv("GRT_SWEEP_TABLE")) table = table && atoi(env) != 0;
-    return table ? launch_wing_impl<PTS, NL, true>(sp, sms, st)
-                 : launch_wing_impl<PTS, NL, false>(sp, sms, st);
+    return table ? launch_wing_impl<PTS, NL, true, LN>(sp, sms, st)
+                 : launch_wing_impl<PTS, NL, false, LN>(sp, sms, st);
 }
 
 // wavenumber_sweep / line_sweep after K0 + K1: per-(molecule, layer) sort of the shifted
@@ -963,7 +963,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     sp.tab = g->tab;
     sp.tau = tau_dev;
 
-    // Points per thread (PTS): 32*PTS points per warp; NL layers per work item.  Wider
+    // Points per thread (PTS): LN*PTS points per warp tile; NL layers per work item.  Wider
     // tiles amortise the per-line work better; narrower ones waste fewer lanes at window
     // ends and balance better (a window is 5001 points at 0.01 cm-1 but only 501 at 0.1,
     // where a 64-point tile beats a 128-point one by 8 % and a 256-point one by 30 %).
@@ -974,7 +974,24 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     if (pts != 2 && pts != 4 && pts != 8 && pts != 16) pts = 4;
     if (nl != 1 && nl != 2) nl = 1;
     if (pts == 2 || pts == 16) nl = 1;
-    GRT_TRY(prepare_tiles(g, pts, margin, g->max_abs_delta*pmax));
+    // Lanes per line group (sweep.cuh): 32 = one line at a time per warp; 16 / 8 = two / four
+    // lines at a time on a tile of LN*PTS points.
+    int ln = 32;
+    if (g->dw >= 0.05)
+    {
+        // 501-point windows: two lines at a time on 64-point tiles, four samples per lane and
+        // visit (config-1 column 24.4 -> 20.2 ms, RFMIP-shaped column 101.5 -> 93.9 ms)
+        ln = 16;
+        pts = 4;
+    }
+    if (char const *env = getenv("GRT_SWEEP_PTS")) pts = atoi(env);
+    if (pts != 2 && pts != 4 && pts != 8 && pts != 16) pts = 4;
+    if (char const *env = getenv("GRT_SWEEP_LANES")) ln = atoi(env);
+    if (ln != 8 && ln != 16) ln = 32;
+    if (ln != 32) nl = 1;
+    if (ln == 16 && pts == 2) pts = 4;
+    if (ln == 8 && pts < 4) pts = 4;
+    GRT_TRY(prepare_tiles(g, ln*pts, margin, g->max_abs_delta*pmax));
     sp.num_tiles = g->num_tiles;
     sp.tile_order = g->d_tile_order;
     sp.tile_major = g->tiles_spectral ? 1 : 0;
@@ -985,8 +1002,14 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     {
         int const sms = sm_count(g->device);
         int rc = 0;
-        switch (pts*10 + nl)
+        switch ((ln != 32 ? ln*1000 : 0) + pts*10 + nl)
         {
+            case 16041: rc = launch_wing<4, 1, 16>(sp, sms, st); break;
+            case 16081: rc = launch_wing<8, 1, 16>(sp, sms, st); break;
+            case 16161: rc = launch_wing<16, 1, 16>(sp, sms, st); break;
+            case 8041: rc = launch_wing<4, 1, 8>(sp, sms, st); break;
+            case 8081: rc = launch_wing<8, 1, 8>(sp, sms, st); break;
+            case 8161: rc = launch_wing<16, 1, 8>(sp, sms, st); break;
             case 21: rc = launch_wing<2, 1>(sp, sms, st); break;
             case 41: rc = launch_wing<4, 1>(sp, sms, st); break;
             case 42: rc = launch_wing<4, 2>(sp, sms, st); break;

@@ -159,13 +159,15 @@ struct TileCtx
 {
     int warp_base;
     int warp_last;
-    int lane;
+    int lane;                  // lane in the warp (owner of record `lane` of a staged batch)
+    int sub;                   // lane in its line group: owns points warp_base + j*LN + sub
+    unsigned gmask;            // records of a staged batch that the lane's group walks
     int fsteps;
     int nw;
     double w0;
     double wres;
-    double lane_pt;            // (double)(warp_base + lane)
-    uint32_t iw_lane;          // shared-memory address of iw[warp_base + lane] (TBL kernels)
+    double lane_pt;            // (double)(warp_base + sub)
+    uint32_t iw_lane;          // shared-memory address of iw[warp_base + sub] (TBL kernels)
 };
 
 // (double)k for 0 <= k < 2^31 on the FP64 pipe instead of the conversion unit.
@@ -201,12 +203,12 @@ __device__ __forceinline__ float4 lds_f32x4(uint32_t const addr)
 // shared-memory table iw[] (i = f - s is a small integer: 0 <= i <= 2*fsteps inside a
 // window), one LDS + one DADD per point.  Otherwise three FP64 operations per point,
 // cached in registers across lines that share s.
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 struct LineGrid;
 
 #if GRT_TBL_CACHE
-template <int PTS>
-struct LineGrid<PTS, true>
+template <int PTS, int LN>
+struct LineGrid<PTS, true, LN>
 {
     GridCache<PTS, true> &gc;
     __device__ __forceinline__ LineGrid(GridCache<PTS, true> &c, TileCtx const &t, int const fc)
@@ -219,7 +221,7 @@ struct LineGrid<PTS, true>
             double const dwno = __dadd_rn(__dmul_rn(int_to_double(s), t.wres), t.w0);
             uint32_t const a = t.iw_lane - 8u*(uint32_t)s;
 #pragma unroll
-            for (int j=0; j<PTS; ++j) gc.t2[j] = __dadd_rn(dwno, lds_f64(a + 256u*(uint32_t)j));
+            for (int j=0; j<PTS; ++j) gc.t2[j] = __dadd_rn(dwno, lds_f64(a + (8u*LN)*(uint32_t)j));
         }
     }
     __device__ __forceinline__ double t2(int const j) const
@@ -228,8 +230,8 @@ struct LineGrid<PTS, true>
     }
 };
 #else
-template <int PTS>
-struct LineGrid<PTS, true>
+template <int PTS, int LN>
+struct LineGrid<PTS, true, LN>
 {
     double dwno;
     uint32_t a;
@@ -241,13 +243,13 @@ struct LineGrid<PTS, true>
     }
     __device__ __forceinline__ double t2(int const j) const
     {
-        return __dadd_rn(dwno, lds_f64(a + 256u*(uint32_t)j));
+        return __dadd_rn(dwno, lds_f64(a + (8u*LN)*(uint32_t)j));
     }
 };
 #endif
 
-template <int PTS>
-struct LineGrid<PTS, false>
+template <int PTS, int LN>
+struct LineGrid<PTS, false, LN>
 {
     GridCache<PTS, false> &gc;
     __device__ __forceinline__ LineGrid(GridCache<PTS, false> &c, TileCtx const &t, int const fc)
@@ -263,7 +265,7 @@ struct LineGrid<PTS, false>
 #pragma unroll
             for (int j=0; j<PTS; ++j)
             {
-                gc.t2[j] = __dadd_rn(dwno, __dmul_rn(i0 + (double)(32*j), t.wres));
+                gc.t2[j] = __dadd_rn(dwno, __dmul_rn(i0 + (double)(LN*j), t.wres));
             }
         }
     }
@@ -313,11 +315,11 @@ __device__ __forceinline__ void accumulate2(double &a0, double &a1, double const
 
 // kClsFast: the tile lies wholly inside the line's window and wholly in its far wing:
 // no predicates, PTS independent dependency chains in flight, two samples per packed op.
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
-    LineGrid<PTS, TBL> const grid(gc, t, __float_as_int(B.w));
+    LineGrid<PTS, TBL, LN> const grid(gc, t, __float_as_int(B.w));
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
@@ -335,13 +337,13 @@ __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileC
 
 // kClsR1: the tile lies wholly inside the window and every point has
 // XLIM1 <= |x| < XLIM0 (wide Doppler cores of the shortwave): region 1 only.
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_r1(double2 const A, float4 const B, float4 const C,
                                         float4 const D, TileCtx const &t,
                                         GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
     // C = hw0, y, xlim0, xlim1;  D = a0, d0, d2, -
-    LineGrid<PTS, TBL> const grid(gc, t, __float_as_int(B.w));
+    LineGrid<PTS, TBL, LN> const grid(gc, t, __float_as_int(B.w));
     double const repwid = widen_positive(B.x);
     f32x2 const y2 = pack2(C.y, C.y);
     f32x2 const a0 = pack2(D.x, D.x);
@@ -356,7 +358,7 @@ __device__ __forceinline__ void line_r1(double2 const A, float4 const B, float4 
 }
 
 // Pure-Lorentz lines (Y >= 70.55, RFM_voigt.c:97-106).  FULL: the window covers the tile.
-template <int PTS, bool TBL, bool FULL>
+template <int PTS, bool TBL, int LN, bool FULL>
 __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
                                              TileCtx const &t, GridCache<PTS, TBL> &gc,
                                              double (&acc)[PTS])
@@ -364,13 +366,13 @@ __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    LineGrid<PTS, TBL> const grid(gc, t, fc);
+    LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     double const repwid = widen_positive(B.x);
-    int const f0 = t.warp_base + t.lane;
+    int const f0 = t.warp_base + t.sub;
 #pragma unroll
     for (int j=0; j<PTS; ++j)
     {
-        int const f = f0 + 32*j;
+        int const f = f0 + LN*j;
         float const xi = abscissa_from(grid.t2(j), A.x, repwid);
         double const k = fast_rcp_of_float(xi*xi + B.y);
         if (FULL || ((f >= s) && (f <= e))) acc[j] = fma(A.y, k, acc[j]);
@@ -380,30 +382,30 @@ __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
 
 // kClsFarEdge: far wing only, but a window end falls inside the tile (kernels.c:435-437):
 // the far-wing arithmetic with a per-point window predicate.
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_far_edge(double2 const A, float4 const B, TileCtx const &t,
                                               GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    LineGrid<PTS, TBL> const grid(gc, t, fc);
+    LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
-    int const f0 = t.warp_base + t.lane;
+    int const f0 = t.warp_base + t.sub;
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
         // a pair of chunks wholly beyond the window end: nothing to do (warp-uniform)
-        int const cb = t.warp_base + 32*j;
-        if (cb + 63 < s || cb > e) continue;
+        int const cb = t.warp_base + LN*j;
+        if (cb + 2*LN - 1 < s || cb > e) continue;
         f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
         f32x2 const k = far_wing2(mul2_unfused(xi, xi), yq2, yr2);
         float k0, k1;
         unpack2(k, k0, k1);
-        int const fa = f0 + 32*j;
-        int const fb = fa + 32;
+        int const fa = f0 + LN*j;
+        int const fb = fa + LN;
         if ((fa >= s) && (fa <= e)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
         if ((fb >= s) && (fb <= e)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
     }
@@ -415,7 +417,7 @@ __device__ __forceinline__ void line_far_edge(double2 const A, float4 const B, T
 // own float comparisons (RFM_voigt.c:166,172).
 // Single-pair tiles (PTS = 2): far wing for both points, region 1 on top if the pair
 // reaches inside XLIM0 (warp-uniform test on the record's conservative half-width).
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_near_single(double2 const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
@@ -425,11 +427,11 @@ __device__ __forceinline__ void line_near_single(double2 const A, float4 const B
     int const hw0 = __float_as_int(C.x);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    LineGrid<PTS, TBL> const grid(gc, t, fc);
+    LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
-    int const f0 = t.warp_base + t.lane;
+    int const f0 = t.warp_base + t.sub;
     f32x2 xi[PTS/2], xq[PTS/2], k[PTS/2];
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
@@ -445,10 +447,10 @@ __device__ __forceinline__ void line_near_single(double2 const A, float4 const B
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        int const cb = t.warp_base + 32*j;            // the pair covers [cb, cb + 63]
-        int const dlo = max(max(cb - fc, fc - (cb + 63)), 0);
-        int const fa = f0 + 32*j;
-        int const fb = fa + 32;
+        int const cb = t.warp_base + LN*j;            // the pair covers [cb, cb + 2*LN - 1]
+        int const dlo = max(max(cb - fc, fc - (cb + 2*LN - 1)), 0);
+        int const fa = f0 + LN*j;
+        int const fb = fa + LN;
         bool ina = (fa >= s) && (fa <= e);
         bool inb = (fb >= s) && (fb <= e);
         float k0, k1;
@@ -476,7 +478,7 @@ __device__ __forceinline__ void line_near_single(double2 const A, float4 const B
 // with every dependency chain in flight; each pair of 32-point chunks is then dispatched
 // warp-uniformly to far wing / region 1 / both (measured: -2.4 % on the config-2 step
 // against forming them inside the branches).
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
@@ -486,7 +488,7 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
     int const hw0in = (int)(__float_as_uint(D.w) >> 16);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
-    LineGrid<PTS, TBL> const grid(gc, t, fc);
+    LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     double const repwid = widen_positive(B.x);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
@@ -494,7 +496,7 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
     f32x2 const a0 = pack2(D.x, D.x);
     f32x2 const d0 = pack2(D.y, D.y);
     f32x2 const d2 = pack2(D.z, D.z);
-    int const f0 = t.warp_base + t.lane;
+    int const f0 = t.warp_base + t.sub;
     f32x2 xi[PTS/2], xq[PTS/2];
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
@@ -505,11 +507,11 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        int const cb = t.warp_base + 32*j;            // the pair covers [cb, cb + 63]
-        int const dlo = max(max(cb - fc, fc - (cb + 63)), 0);
-        int const dhi = max(fc - cb, cb + 63 - fc);
-        int const fa = f0 + 32*j;
-        int const fb = fa + 32;
+        int const cb = t.warp_base + LN*j;            // the pair covers [cb, cb + 2*LN - 1]
+        int const dlo = max(max(cb - fc, fc - (cb + 2*LN - 1)), 0);
+        int const dhi = max(fc - cb, cb + 2*LN - 1 - fc);
+        int const fa = f0 + LN*j;
+        int const fb = fa + LN;
         bool const ina = (fa >= s) && (fa <= e);
         bool const inb = (fb >= s) && (fb <= e);
         float x0, x1;
@@ -551,13 +553,13 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
     }
 }
 
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_near(double2 const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
-    if (PTS <= 2) line_near_single<PTS, TBL>(A, B, C, D, t, gc, acc);
-    else line_near_pairs<PTS, TBL>(A, B, C, D, t, gc, acc);
+    if (PTS <= 2) line_near_single<PTS, TBL, LN>(A, B, C, D, t, gc, acc);
+    else line_near_pairs<PTS, TBL, LN>(A, B, C, D, t, gc, acc);
 }
 
 
@@ -626,7 +628,7 @@ __device__ unsigned long long g_dbg_visits[kTmCount];
 // One staged batch (cnt <= 32 records of one layer) against the warp's tile.  Lane b
 // classifies record b; the classes are then walked as bit masks, the dominant one
 // (kClsFast) with the next record's vectors prefetched while the current one computes.
-template <int PTS, bool TBL>
+template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void process_batch(LineRec const *stage, int const cnt,
                                               TileCtx const &t, GridCache<PTS, TBL> &gc,
                                               double (&acc)[PTS])
@@ -666,7 +668,7 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
             }
         }
     }
-    unsigned m = __ballot_sync(0xffffffffu, cls == kClsFast);
+    unsigned m = __ballot_sync(0xffffffffu, cls == kClsFast) & t.gmask;
     GRT_TM_END(kTmClassify, 1);
 #if GRT_DBG_TIMERS
     int tm_n = __popc(m);
@@ -688,47 +690,47 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
             m &= m - 1;
             double2 const A1 = lds_f64x2(sa + 64u*(uint32_t)b);
             float4 const B1 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
-            line_fast<PTS, TBL>(A0, B0, t, gc, acc);
+            line_fast<PTS, TBL, LN>(A0, B0, t, gc, acc);
             if (!more) break;
             more = m != 0;
             b = more ? __ffs(m) - 1 : b;
             m &= m - 1;
             A0 = lds_f64x2(sa + 64u*(uint32_t)b);
             B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
-            line_fast<PTS, TBL>(A1, B1, t, gc, acc);
+            line_fast<PTS, TBL, LN>(A1, B1, t, gc, acc);
             if (!more) break;
         }
     }
     GRT_TM_END(kTmFast, tm_n);
-    m = __ballot_sync(0xffffffffu, cls == kClsR1);
+    m = __ballot_sync(0xffffffffu, cls == kClsR1) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_r1<PTS, TBL>(r.A, r.B, r.C, r.D, t, gc, acc); });
+    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_r1<PTS, TBL, LN>(r.A, r.B, r.C, r.D, t, gc, acc); });
     GRT_TM_END(kTmR1, tm_n);
-    m = __ballot_sync(0xffffffffu, cls == kClsFarEdge);
+    m = __ballot_sync(0xffffffffu, cls == kClsFarEdge) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_far_edge<PTS, TBL>(r.A, r.B, t, gc, acc); });
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_far_edge<PTS, TBL, LN>(r.A, r.B, t, gc, acc); });
     GRT_TM_END(kTmFarEdge, tm_n);
-    m = __ballot_sync(0xffffffffu, cls == kClsNear);
+    m = __ballot_sync(0xffffffffu, cls == kClsNear) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_near<PTS, TBL>(r.A, r.B, r.C, r.D, t, gc, acc); });
+    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_near<PTS, TBL, LN>(r.A, r.B, r.C, r.D, t, gc, acc); });
     GRT_TM_END(kTmNear, tm_n);
-    m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull);
+    m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, true>(r.A, r.B, t, gc, acc); });
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, LN, true>(r.A, r.B, t, gc, acc); });
     GRT_TM_END(kTmLorFull, tm_n);
-    m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge);
+    m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, false>(r.A, r.B, t, gc, acc); });
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, LN, false>(r.A, r.B, t, gc, acc); });
     GRT_TM_END(kTmLorEdge, tm_n);
 }
 
@@ -742,14 +744,14 @@ struct SweepConfig
     static constexpr int kMinBlocks = (PTS*NL <= 8) ? 3 : ((PTS*NL <= 16) ? 2 : 1);
 };
 
-// Entries of the fl(i*wres) table for a kernel with tiles of 32*PTS points: i = f - s runs
+// Entries of the fl(i*wres) table for a kernel with tiles of LN*PTS points: i = f - s runs
 // over [0, 2*fsteps] inside a window; points of an edge tile beyond the window end read up
 // to one tile further (real entries), points before the window start read below the table,
 // into the record rings (any bit pattern: those samples are predicated off).
-template <int PTS>
+template <int PTS, int LN = 32>
 __host__ __device__ constexpr int sweep_table_entries(int const fsteps)
 {
-    return 2*fsteps + 32*PTS + 1;
+    return 2*fsteps + LN*PTS + 1;
 }
 
 
@@ -757,10 +759,22 @@ __host__ __device__ constexpr int sweep_table_entries(int const fsteps)
 // work item from the global counter and streams the records of its lines through a
 // warp-private shared-memory ring: no block-wide barrier after the prologue, so a warp
 // never waits for a neighbour whose lines are denser.
-template <int PTS, int NL, bool TBL>
+//
+// LN = lanes per line group.  LN = 32: the whole warp walks one line at a time over a tile
+// of 32*PTS points.  LN = 16 / 8: the warp walks 2 / 4 lines at a time -- group g of LN
+// lanes takes records [g*LN, (g+1)*LN) of each staged batch -- over a tile of LN*PTS points,
+// every group holding partial sums of ALL the tile's points (summed over the groups with
+// shuffles in the epilogue).  A line visit then covers PTS samples per lane on a tile 32/LN
+// times narrower, which is what the 501-point windows of a 0.1 cm-1 grid need: the per-visit
+// work (record loads, class walk, per-line constants) is amortised over 4-8 samples per lane
+// without widening the tile beyond 64 points (wider tiles lose more to window ends).
+template <int PTS, int NL, bool TBL, int LN>
 __global__ void __launch_bounds__(kSweepThreads, SweepConfig<PTS, NL>::kMinBlocks)
 wing_sweep_kernel(SweepParams const p)
 {
+    static_assert(LN == 32 || LN == 16 || LN == 8, "lanes per line group");
+    constexpr int kGroups = 32/LN;
+    static_assert(PTS % kGroups == 0, "the groups share the tile's chunks in the epilogue");
     using Cfg = SweepConfig<PTS, NL>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     int const lane = threadIdx.x & 31;
@@ -782,7 +796,7 @@ wing_sweep_kernel(SweepParams const p)
     if (TBL)
     {
         // iw[k] = fl(k*wres): the product of RFM_voigt.c:165 for every sample index.
-        int const entries = sweep_table_entries<PTS>(p.fsteps);
+        int const entries = sweep_table_entries<PTS, LN>(p.fsteps);
         for (int k=threadIdx.x; k<entries; k+=kSweepThreads)
         {
             iw[k] = __dmul_rn((double)k, p.wres);
@@ -809,7 +823,7 @@ wing_sweep_kernel(SweepParams const p)
         int const tile = p.tile_order[slot];
         unsigned const first = p.tile_first[tile];
         unsigned const last = p.tile_last[tile];
-        int const warp_base = tile*(32*PTS);
+        int const warp_base = tile*(LN*PTS);
         int const layer0 = group*NL;
         int const nl = min(NL, L - layer0);
         int const nb = (int)((last - first + 31u)/32u);
@@ -826,14 +840,16 @@ wing_sweep_kernel(SweepParams const p)
         }
         TileCtx tc;
         tc.warp_base = warp_base;
-        tc.warp_last = warp_base + 32*PTS - 1;
+        tc.warp_last = warp_base + LN*PTS - 1;
         tc.lane = lane;
+        tc.sub = lane & (LN - 1);
+        tc.gmask = (LN == 32) ? 0xffffffffu : (((1u << (LN & 31)) - 1u) << ((lane/LN)*LN));
         tc.fsteps = p.fsteps;
         tc.nw = p.nw;
         tc.w0 = p.w0;
         tc.wres = p.wres;
-        tc.lane_pt = (double)(warp_base + lane);
-        tc.iw_lane = smem_u32(iw) + 8u*(uint32_t)(warp_base + lane);
+        tc.lane_pt = (double)(warp_base + tc.sub);
+        tc.iw_lane = smem_u32(iw) + 8u*(uint32_t)(warp_base + tc.sub);
         GridCache<PTS, TBL> gc;
         reset_cache(gc);
 
@@ -874,7 +890,7 @@ wing_sweep_kernel(SweepParams const p)
 #pragma unroll
             for (int l=0; l<NL; ++l)
             {
-                if (l < nl) process_batch<PTS, TBL>(stage + l*32, cnt, tc, gc, acc[l]);
+                if (l < nl) process_batch<PTS, TBL, LN>(stage + l*32, cnt, tc, gc, acc[l]);
             }
             __syncwarp();
             if (lane == 0 && k + 2 < nb)
@@ -894,12 +910,32 @@ wing_sweep_kernel(SweepParams const p)
         {
             if (l >= nl) continue;
             int const layer = layer0 + l;
-#pragma unroll
-            for (int j=0; j<PTS; ++j)
+            if (kGroups > 1)
             {
+                // every group holds partial sums of all the tile's points: sum them
+                __syncwarp();
+#pragma unroll
+                for (int j=0; j<PTS; ++j)
+                {
+#pragma unroll
+                    for (int off=LN; off<32; off<<=1)
+                    {
+                        acc[l][j] += __shfl_xor_sync(0xffffffffu, acc[l][j], off);
+                    }
+                }
+            }
+#pragma unroll
+            for (int j=0; j<PTS/kGroups; ++j)
+            {
+                // chunk j*kGroups + g of LN points is stored by group g: 32 contiguous points
                 int const f = warp_base + j*32 + lane;
                 if (f >= p.nw) continue;
-                double t = acc[l][j];
+                double t = acc[l][j*kGroups];
+#pragma unroll
+                for (int gi=1; gi<kGroups; ++gi)
+                {
+                    if (lane/LN == gi) t = acc[l][j*kGroups + gi];
+                }
                 if (p.tab.h2o_slot >= 0)
                 {
                     double const tref = 296.;

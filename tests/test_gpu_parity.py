@@ -148,3 +148,77 @@ def test_binned_methods(built, tmp_path, method, case):
     print(f"method {method} {case}: tau max rel {rel.max():.3e} at {where}; {bad} points > 1e-9; "
           f"stats {got['stats']}")
     assert rel.max() <= TAU_RTOL
+
+
+# ---- BASELINE full sizes: size-independent properties (no oracle: it would take hours) ----
+
+def _full_size_tau(ds, w0, wn, dw, col, mols, method=2, use_ctm=False):
+    from grtcode_b200 import api
+    got = parity.gpu_column(ds, w0, wn, dw, col, mols, use_ctm=use_ctm, solvers=False,
+                            method=method)
+    return got["tau"], got["stats"]
+
+
+def test_full_size_config1_is_additive_over_molecules_and_line_order(built, tmp_path):
+    """BASELINE config 1 at its real size (60 levels, 1-3000 cm-1 at 0.1 cm-1, 6.5e5 lines,
+    1.9e10 Voigt samples).  Optical depth is a sum over lines (kernels.c:456-460), so
+    (1) tau(H2O + CO2 + O3) = tau(H2O) + tau(CO2) + tau(O3), and (2) the order of the records
+    in the HITRAN file does not matter -- both up to the rounding of a re-ordered double sum,
+    five orders of magnitude inside the 1e-9 parity tolerance."""
+    import os
+    mols = (synth.H2O, synth.CO2, synth.O3)
+    lines = {synth.H2O: 100_000, synth.CO2: 300_000, synth.O3: 250_000}
+    w0, wn, dw, levels = 1., 3000., 0.1, 60
+    ds = parity.build_dataset(str(tmp_path/"a"), w0, wn, lines, 31)
+    col = synth.make_column(levels, np.random.default_rng(31), molecules=mols)
+    whole, st = _full_size_tau(ds, w0, wn, dw, col, mols)
+    assert st["samples"] > 1.8e10
+    assert np.isfinite(whole).all() and (whole >= 0.).all()
+    parts = np.zeros_like(whole)
+    for m in mols:
+        t, _ = _full_size_tau(ds, w0, wn, dw, col, (m,))
+        parts += t
+    rel = parity.relative_error(parts, whole)
+    print(f"additivity: max rel {rel.max():.3e}")
+    assert rel.max() <= 1e-12
+    # same records, shuffled file order
+    rows = open(ds.hitran).read().splitlines(keepends=True)
+    np.random.default_rng(5).shuffle(rows)
+    os.makedirs(tmp_path/"b", exist_ok=True)
+    shuffled = str(tmp_path/"b"/"shuffled.par")
+    open(shuffled, "w").writelines(rows)
+    import dataclasses
+    ds2 = dataclasses.replace(ds, hitran=shuffled)
+    again, st2 = _full_size_tau(ds2, w0, wn, dw, col, mols)
+    assert st2["samples"] == st["samples"]
+    rel = parity.relative_error(again, whole)
+    print(f"line order: max rel {rel.max():.3e}")
+    assert rel.max() <= 1e-12
+
+
+def test_full_size_fine_grid_chunks_reproduce_the_whole(built, tmp_path):
+    """BASELINE config 2/4 resolution at a real line density (0.01 cm-1, 5001-point windows,
+    8.8e4 lines over 325 cm-1, 54 layers): tau on a sub-grid that starts on a grid point of
+    the whole grid, fed only the lines within 25 cm-1 of it (add_molecule min/max), equals
+    the whole-grid tau away from the cut-off seam (kernels.c:431-439: a line's window is
+    centred on its own nearest grid point, so interior points see the same samples)."""
+    mols = (synth.H2O, synth.CO2, synth.CH4)
+    lines = {synth.H2O: 20_000, synth.CO2: 40_000, synth.CH4: 28_000}
+    w0, wn, dw, levels = 600., 925., 0.01, 55
+    ds = parity.build_dataset(str(tmp_path), w0, wn, lines, 37)
+    col = synth.make_column(levels, np.random.default_rng(37), molecules=mols)
+    whole, st = _full_size_tau(ds, w0, wn, dw, col, mols)
+    assert st["samples"] > 2e10
+    a, b = 700., 760.
+    got = parity.gpu_column(ds, a, b, dw, col, mols, use_ctm=False, solvers=False,
+                            line_window=(a, b))
+    i0 = int(round((a - w0)/dw))
+    n = got["tau"].shape[1]
+    # points further than 25 cm-1 (+ one step) from both ends of the sub-grid only see lines
+    # that the sub-grid run also loaded
+    k = int(np.ceil(25./dw)) + 2
+    sub = got["tau"][:, k:n-k]
+    ref = whole[:, i0+k:i0+n-k]
+    rel = parity.relative_error(sub, ref)
+    print(f"chunk vs whole: max rel {rel.max():.3e} over {sub.size} points")
+    assert rel.max() <= 1e-9
