@@ -540,7 +540,7 @@ constexpr int kMaxTableBytes = 64*1024;
 template <int PTS, int NL, bool TBL, int LN>
 static int launch_wing_impl(SweepParams const &sp, int const sms, cudaStream_t const st)
 {
-    using Cfg = SweepConfig<PTS, NL>;
+    using Cfg = SweepConfig<PTS, NL, LN>;
     static bool configured = false;
     if (!configured)
     {

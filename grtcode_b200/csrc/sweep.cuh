@@ -735,11 +735,16 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
 }
 
 
-template <int PTS, int NL>
+template <int PTS, int NL, int LN = 32>
 struct SweepConfig
 {
     static constexpr int kStageBytes = NL*32*(int)sizeof(LineRec);
-    static constexpr int kRingBytes = kSweepWarps*2*kStageBytes + kSweepWarps*2*8;
+    // Stages of the warp's record ring.  Whole-warp lines on a fine grid spend thousands of
+    // cycles on a batch and two stages hide the copy; the grouped kernels of the coarse grids
+    // go through a batch in a fraction of that (narrow tiles, two or four lines at a time), so
+    // they keep four batches in flight.
+    static constexpr int kStages = (LN == 32) ? 2 : 4;
+    static constexpr int kRingBytes = kSweepWarps*kStages*kStageBytes + kSweepWarps*kStages*8;
     // registers: PTS*NL accumulators + PTS cached abscissae, all double
     static constexpr int kMinBlocks = (PTS*NL <= 8) ? 3 : ((PTS*NL <= 16) ? 2 : 1);
 };
@@ -769,27 +774,26 @@ __host__ __device__ constexpr int sweep_table_entries(int const fsteps)
 // work (record loads, class walk, per-line constants) is amortised over 4-8 samples per lane
 // without widening the tile beyond 64 points (wider tiles lose more to window ends).
 template <int PTS, int NL, bool TBL, int LN>
-__global__ void __launch_bounds__(kSweepThreads, SweepConfig<PTS, NL>::kMinBlocks)
+__global__ void __launch_bounds__(kSweepThreads, SweepConfig<PTS, NL, LN>::kMinBlocks)
 wing_sweep_kernel(SweepParams const p)
 {
     static_assert(LN == 32 || LN == 16 || LN == 8, "lanes per line group");
     constexpr int kGroups = 32/LN;
     static_assert(PTS % kGroups == 0, "the groups share the tile's chunks in the epilogue");
-    using Cfg = SweepConfig<PTS, NL>;
+    using Cfg = SweepConfig<PTS, NL, LN>;
+    constexpr int STG = Cfg::kStages;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     int const lane = threadIdx.x & 31;
     int const warp = threadIdx.x >> 5;
-    unsigned char *ring = smem_raw + (size_t)warp*(2*Cfg::kStageBytes);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)kSweepWarps*2*Cfg::kStageBytes) +
-                     warp*2;
-    uint32_t const mb0 = smem_u32(bars);
-    uint32_t const mb1 = smem_u32(bars + 1);
-    uint32_t const sb0 = smem_u32(ring);
-    uint32_t const sb1 = sb0 + Cfg::kStageBytes;
+    unsigned char *ring = smem_raw + (size_t)warp*(STG*Cfg::kStageBytes);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)kSweepWarps*STG*Cfg::kStageBytes) +
+                     warp*STG;
+    uint32_t const mb0 = smem_u32(bars);       // barrier of stage k: mb0 + 8k
+    uint32_t const sb0 = smem_u32(ring);       // records of stage k: sb0 + k*kStageBytes
     if (lane == 0)
     {
-        mbar_init(mb0, 1);
-        mbar_init(mb1, 1);
+#pragma unroll
+        for (int k=0; k<STG; ++k) mbar_init(mb0 + 8u*(uint32_t)k, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     double *iw = reinterpret_cast<double *>(smem_raw + Cfg::kRingBytes);
@@ -867,16 +871,20 @@ wing_sweep_kernel(SweepParams const p)
         };
         if (lane == 0)
         {
-            if (nb > 0) issue(0, sb0, mb0);
-            if (nb > 1) issue(1, sb1, mb1);
+#pragma unroll
+            for (int k=0; k<STG; ++k)
+            {
+                if (k < nb) issue(k, sb0 + (uint32_t)(k*Cfg::kStageBytes), mb0 + 8u*(uint32_t)k);
+            }
         }
         for (int k=0; k<nb; ++k)
         {
-            int const st = k & 1;
+            int const st = k & (STG - 1);
+            uint32_t const mb = mb0 + 8u*(uint32_t)st;
 #if GRT_DBG_TIMERS
             long long const tw0 = clock64();
 #endif
-            mbar_wait(st ? mb1 : mb0, (phase >> st) & 1u);
+            mbar_wait(mb, (phase >> st) & 1u);
 #if GRT_DBG_TIMERS
             if (lane == 0)
             {
@@ -893,11 +901,11 @@ wing_sweep_kernel(SweepParams const p)
                 if (l < nl) process_batch<PTS, TBL, LN>(stage + l*32, cnt, tc, gc, acc[l]);
             }
             __syncwarp();
-            if (lane == 0 && k + 2 < nb)
+            if (lane == 0 && k + STG < nb)
             {
                 // order the warp's generic-proxy reads before the async-proxy overwrite
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                issue(k + 2, st ? sb1 : sb0, st ? mb1 : mb0);
+                issue(k + STG, sb0 + (uint32_t)(st*Cfg::kStageBytes), mb);
             }
         }
 
