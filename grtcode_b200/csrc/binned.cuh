@@ -283,16 +283,18 @@ __device__ void ranges_line_sweep(BinGeometry const &b, unsigned long long const
 __device__ __forceinline__ double line_point(LineRec const &r, double const inw, double const i_d,
                                              double const inwres)
 {
-    float const xi = abscissa(inw, i_d, inwres, r.v, (double)r.repwid);
+    // float -> double by integer ops (exact for the positive normal values here): the
+    // conversion unit shares the XU pipe with the reciprocal of the division
+    float const xi = abscissa(inw, i_d, inwres, r.v, widen_positive(r.repwid));
     if (r.hw0 == kHwLorentz)
     {
-        return r.c/(double)(xi*xi + r.yq);
+        return r.c/widen_positive(xi*xi + r.yq);
     }
     float const ax = fabsf(xi);
     if (ax >= r.xlim0 && r.hw0 != kHwCoreOnly)
     {
         // far wing (RFM_voigt.c:168-171): almost every remote sample
-        return r.c*(double)div_exact(r.yrrtpi, ax*ax + r.yq);
+        return r.c*widen_positive(div_exact(r.yrrtpi, ax*ax + r.yq));
     }
     return r.c*voigt_core(xi, r.y, r.xlim0, r.xlim1);
 }

@@ -167,6 +167,7 @@ __global__ void column_prep_kernel(int const num_layers, ColumnInputs const in,
 #include "sweep.cuh"
 #include "binned.cuh"
 #include <cub/device/device_segmented_radix_sort.cuh>
+#include <cub/device/device_radix_sort.cuh>
 
 namespace grt {
 
@@ -289,7 +290,7 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         {
             // sort keys of the binned methods (sort_lines, kernels.c:135-172)
             vkey[(size_t)i*lines.num_lines + j] = v;
-            vidx[(size_t)i*lines.num_lines + j] = (unsigned)j;
+            vidx[(size_t)i*lines.num_lines + j] = (unsigned)((size_t)i*lines.num_lines + j);
         }
     }
     // Block-level statistics (bench bookkeeping only).
@@ -375,6 +376,7 @@ struct grt_gas
     LineRec *d_sorted_recs = nullptr;    // binned methods: records in sorted order
     int *d_seg_begin = nullptr;
     int *d_seg_end = nullptr;
+    unsigned short *d_segkey = nullptr;  // [2][layers*lines] segment ids of the second sort pass
     void *d_sort_temp = nullptr;
     size_t sort_temp_bytes = 0;
     size_t binned_capacity = 0;
@@ -571,6 +573,64 @@ static int launch_wing(SweepParams const &sp, int const sms, cudaStream_t const 
                  : launch_wing_impl<PTS, NL, false, LN>(sp, sms, st);
 }
 
+// Segment id (layer*slots + molecule slot) of every entry of a list of global record indices.
+struct SegmentMap
+{
+    int num_slots;
+    unsigned long long num_lines;
+    unsigned slot_off[GRT_MAX_MOLS + 1];
+};
+
+__global__ void __launch_bounds__(256)
+segment_keys_kernel(unsigned const *gidx, SegmentMap const map, unsigned long long const total,
+                    unsigned short *seg)
+{
+    unsigned long long const pos = (unsigned long long)blockIdx.x*blockDim.x + threadIdx.x;
+    if (pos >= total) return;
+    unsigned const gi = gidx[pos];
+    unsigned const layer = (unsigned)(gi/map.num_lines);
+    unsigned const j = (unsigned)(gi - (unsigned long long)layer*map.num_lines);
+    int lo = 0, hi = map.num_slots;          // slot_off[lo] <= j < slot_off[hi]
+    while (hi - lo > 1)
+    {
+        int const mid = (lo + hi)/2;
+        if (j >= map.slot_off[mid]) lo = mid; else hi = mid;
+    }
+    seg[pos] = (unsigned short)(layer*(unsigned)map.num_slots + (unsigned)lo);
+}
+
+// After the sort: gidx[p] = global index of the record at sorted position p.  Writes the
+// layer-relative permutation, the sorted centres and the records in sorted order (so that the
+// gather reads them with unit stride).  perm may alias gidx.
+__global__ void __launch_bounds__(256)
+sort_finish_kernel(unsigned const *gidx, double const *vkey, LineRec const *recs,
+                   unsigned long long const num_lines, unsigned long long const total,
+                   unsigned *perm, double *vsorted, LineRec *sorted_recs)
+{
+    unsigned long long const pos = (unsigned long long)blockIdx.x*blockDim.x + threadIdx.x;
+    if (pos >= total) return;
+    unsigned const gi = gidx[pos];
+    unsigned long long const layer = pos/num_lines;
+    perm[pos] = (unsigned)(gi - layer*num_lines);
+    vsorted[pos] = vkey[gi];
+    uint4 const *src = reinterpret_cast<uint4 const *>(recs + gi);
+    uint4 *dst = reinterpret_cast<uint4 *>(sorted_recs + pos);
+    uint4 const a = src[0], b = src[1], c = src[2], d = src[3];
+    dst[0] = a; dst[1] = b; dst[2] = c; dst[3] = d;
+}
+
+static int sort_temp(grt_gas *g, size_t const bytes)
+{
+    if (bytes > g->sort_temp_bytes)
+    {
+        cudaFree(g->d_sort_temp);
+        g->d_sort_temp = nullptr;
+        GRT_CUDA(cudaMalloc(&g->d_sort_temp, bytes));
+        g->sort_temp_bytes = bytes;
+    }
+    return 0;
+}
+
 // wavenumber_sweep / line_sweep after K0 + K1: per-(molecule, layer) sort of the shifted
 // centres (sort_lines, kernels.c:135-172: stable, ascending), then the gather kernel of
 // binned.cuh.  The radix sort is CUB's (stable); keys are the centres K1 wrote.
@@ -588,42 +648,81 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
     {
         if ((size_t)N*L > (size_t)INT32_MAX) return fail("too many (line, layer) pairs for the sort");
         int const segs = slots*L;
-        std::vector<int> begin((size_t)segs), end((size_t)segs);
-        for (int i=0; i<L; ++i)
+        bool segmented = segs > 65535;
+        if (char const *env = getenv("GRT_BIN_SORT")) segmented = segmented || env[0] == 's';
+        if (segmented)
         {
-            for (int sl=0; sl<slots; ++sl)
+            // One CUB segment per (layer, molecule): a thread block per segment, which leaves
+            // most of the GPU idle when there are a few hundred segments of 1e5 lines.
+            std::vector<int> begin((size_t)segs), end((size_t)segs);
+            for (int i=0; i<L; ++i)
             {
-                begin[(size_t)i*slots + sl] = (int)((size_t)i*N + g->slot_off[sl]);
-                end[(size_t)i*slots + sl] = (int)((size_t)i*N + g->slot_off[sl+1]);
+                for (int sl=0; sl<slots; ++sl)
+                {
+                    begin[(size_t)i*slots + sl] = (int)((size_t)i*N + g->slot_off[sl]);
+                    end[(size_t)i*slots + sl] = (int)((size_t)i*N + g->slot_off[sl+1]);
+                }
             }
+            cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end);
+            g->d_seg_begin = g->d_seg_end = nullptr;
+            GRT_CUDA(cudaMalloc(&g->d_seg_begin, sizeof(int)*segs));
+            GRT_CUDA(cudaMalloc(&g->d_seg_end, sizeof(int)*segs));
+            GRT_CUDA(cudaMemcpyAsync(g->d_seg_begin, begin.data(), sizeof(int)*segs,
+                                     cudaMemcpyHostToDevice, st));
+            GRT_CUDA(cudaMemcpyAsync(g->d_seg_end, end.data(), sizeof(int)*segs,
+                                     cudaMemcpyHostToDevice, st));
+            GRT_CUDA(cudaStreamSynchronize(st));   // the host vectors go out of scope below
+            size_t bytes = 0;
+            GRT_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(
+                nullptr, bytes, g->d_vkey, g->d_vsorted, g->d_vidx, g->d_perm, (int)(N*L), segs,
+                g->d_seg_begin, g->d_seg_end, 0, 64, st));
+            GRT_TRY(sort_temp(g, bytes));
+            GRT_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(
+                g->d_sort_temp, bytes, g->d_vkey, g->d_vsorted, g->d_vidx, g->d_perm, (int)(N*L), segs,
+                g->d_seg_begin, g->d_seg_end, 0, 64, st));
+            ++launches;
+            // d_perm holds global indices in segment order
+            sort_finish_kernel<<<(unsigned)((N*L + 255)/256), 256, 0, st>>>(
+                g->d_perm, g->d_vkey, g->d_recs, N, N*L, g->d_perm, g->d_vsorted, g->d_sorted_recs);
+            ++launches;
         }
-        cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end);
-        g->d_seg_begin = g->d_seg_end = nullptr;
-        GRT_CUDA(cudaMalloc(&g->d_seg_begin, sizeof(int)*segs));
-        GRT_CUDA(cudaMalloc(&g->d_seg_end, sizeof(int)*segs));
-        GRT_CUDA(cudaMemcpyAsync(g->d_seg_begin, begin.data(), sizeof(int)*segs,
-                                 cudaMemcpyHostToDevice, st));
-        GRT_CUDA(cudaMemcpyAsync(g->d_seg_end, end.data(), sizeof(int)*segs,
-                                 cudaMemcpyHostToDevice, st));
-        GRT_CUDA(cudaStreamSynchronize(st));   // the host vectors go out of scope below
-        size_t bytes = 0;
-        GRT_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(
-            nullptr, bytes, g->d_vkey, g->d_vsorted, g->d_vidx, g->d_perm, (int)(N*L), segs,
-            g->d_seg_begin, g->d_seg_end, 0, 64, st));
-        if (bytes > g->sort_temp_bytes)
+        else
         {
-            cudaFree(g->d_sort_temp);
-            g->d_sort_temp = nullptr;
-            GRT_CUDA(cudaMalloc(&g->d_sort_temp, bytes));
-            g->sort_temp_bytes = bytes;
+            // Two device-wide passes, every SM busy: (1) all (line, layer) pairs by centre,
+            // (2) stable sort by segment id = layer*slots + molecule slot (radix sorts are
+            // stable, so each segment keeps the centre order, ties in file order as the
+            // reference's insertion sort leaves them).  Segments are contiguous and in
+            // segment-id order in the record layout, so position p of the result belongs to
+            // layer p / N.
+            SegmentMap map;
+            map.num_slots = slots;
+            map.num_lines = N;
+            for (int sl=0; sl<=GRT_MAX_MOLS; ++sl)
+            {
+                map.slot_off[sl] = sl < (int)g->slot_off.size() ? g->slot_off[sl] : (unsigned)N;
+            }
+            int seg_bits = 1;
+            while ((1 << seg_bits) < segs) ++seg_bits;
+            unsigned short *seg_in = g->d_segkey;
+            unsigned short *seg_out = g->d_segkey + (size_t)N*L;
+            size_t bytes_a = 0, bytes_b = 0;
+            GRT_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes_a, g->d_vkey, g->d_vsorted,
+                                                     g->d_vidx, g->d_perm, (int)(N*L), 0, 64, st));
+            GRT_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes_b, seg_in, seg_out, g->d_perm,
+                                                     g->d_vidx, (int)(N*L), 0, seg_bits, st));
+            size_t bytes = std::max(bytes_a, bytes_b);
+            GRT_TRY(sort_temp(g, bytes));
+            GRT_CUDA(cub::DeviceRadixSort::SortPairs(g->d_sort_temp, bytes, g->d_vkey, g->d_vsorted,
+                                                     g->d_vidx, g->d_perm, (int)(N*L), 0, 64, st));
+            segment_keys_kernel<<<(unsigned)((N*L + 255)/256), 256, 0, st>>>(g->d_perm, map, N*L,
+                                                                             seg_in);
+            GRT_CUDA(cub::DeviceRadixSort::SortPairs(g->d_sort_temp, bytes, seg_in, seg_out,
+                                                     g->d_perm, g->d_vidx, (int)(N*L), 0, seg_bits,
+                                                     st));
+            sort_finish_kernel<<<(unsigned)((N*L + 255)/256), 256, 0, st>>>(
+                g->d_vidx, g->d_vkey, g->d_recs, N, N*L, g->d_perm, g->d_vsorted, g->d_sorted_recs);
+            launches += 4;
         }
-        GRT_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(
-            g->d_sort_temp, bytes, g->d_vkey, g->d_vsorted, g->d_vidx, g->d_perm, (int)(N*L), segs,
-            g->d_seg_begin, g->d_seg_end, 0, 64, st));
-        ++launches;
-        dim3 pgrid((unsigned)((N + 255)/256), (unsigned)L);
-        permute_records_kernel<<<pgrid, 256, 0, st>>>(g->d_recs, g->d_perm, g->d_sorted_recs, N);
-        ++launches;
     }
     GRT_CUDA(cudaEventRecord(g->ev[2], st));
     BinParams bp;
@@ -742,7 +841,7 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_work_counter);
     cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
     cudaFree(g->d_sorted_recs);
-    cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_sort_temp); cudaFree(g->d_evals); cudaFree(g->d_ranges);
+    cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_segkey); cudaFree(g->d_sort_temp); cudaFree(g->d_evals); cudaFree(g->d_ranges);
     for (double *t : g->owned_tables) cudaFree(t);
     for (int k=0; k<5; ++k) if (g->ev[k]) cudaEventDestroy(g->ev[k]);
     delete g;
@@ -925,7 +1024,8 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
         if (method != 2 && need > g->binned_capacity)
         {
             cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
-            cudaFree(g->d_sorted_recs);
+            cudaFree(g->d_sorted_recs); cudaFree(g->d_segkey);
+            g->d_segkey = nullptr;
             g->d_vkey = g->d_vsorted = nullptr;
             g->d_vidx = g->d_perm = nullptr;
             g->d_sorted_recs = nullptr;
@@ -934,6 +1034,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
             GRT_CUDA(cudaMalloc(&g->d_vsorted, sizeof(double)*need));
             GRT_CUDA(cudaMalloc(&g->d_vidx, sizeof(unsigned)*need));
             GRT_CUDA(cudaMalloc(&g->d_perm, sizeof(unsigned)*need));
+            GRT_CUDA(cudaMalloc(&g->d_segkey, sizeof(unsigned short)*2*need));
             g->binned_capacity = need;
         }
         line_prep_kernel<<<grid, 256, 0, st>>>(lv, L, lay, g->meta, g->w0, g->dw, g->nw, fsteps,
