@@ -46,6 +46,8 @@ struct BinParams
     double const *vs;                   // [layers][num_lines] centres sorted per (molecule, layer)
     unsigned const *perm;               // [layers][num_lines] record index of each sorted entry
     LineRec const *sorted_recs;         // [layers][num_lines] records in sorted order
+    double2 const *wing_a;              // [layers][num_lines] sorted order: v, c
+    float4 const *wing_b;               //   repwid, yq, yrrtpi, far-wing limit (see WingRec)
     unsigned long long num_lines;
     int num_slots;
     unsigned slot_off[GRT_MAX_MOLS + 1];
@@ -278,24 +280,42 @@ __device__ void ranges_line_sweep(BinGeometry const &b, unsigned long long const
     *out = R;
 }
 
+// The 32 bytes of a record that a far-wing or pure-Lorentz sample needs, as two arrays of
+// 16-byte vectors in sorted order: a warp whose lanes take consecutive lines then loads two
+// contiguous 512-byte rows instead of gathering 48 bytes out of 32 different 64-byte records
+// (which kept the L1 data pipe at 85 % of its wavefront peak and the issue rate at 57 %).
+// limit = XLIM0 for a Voigt record (|x| >= limit is the far wing, RFM_voigt.c:166-171),
+// +inf for a record flagged core-only (never the shortcut), NaN for a pure-Lorentz record.
+__device__ __forceinline__ void wing_record(LineRec const &r, double2 *a, float4 *b)
+{
+    float limit = r.xlim0;
+    if (r.hw0 == kHwCoreOnly) limit = __int_as_float(0x7f800000);
+    if (r.hw0 == kHwLorentz) limit = __int_as_float(0x7fc00000);
+    *a = make_double2(r.v, r.c);
+    *b = make_float4(r.repwid, r.yq, r.yrrtpi, limit);
+}
+
 // S*N_s*K at one point of one line: rfm_voigt_line_shape for a single abscissa
 // (RFM_voigt.c:97-106 pure Lorentz, :109-278 Voigt) with the scale of kernels.c:459 in c.
-__device__ __forceinline__ double line_point(LineRec const &r, double const inw, double const i_d,
+// `full` is only dereferenced for the samples inside |x| < XLIM0.
+__device__ __forceinline__ double line_point(double2 const A, float4 const B, LineRec const *full,
+                                             double const inw, double const i_d,
                                              double const inwres)
 {
     // float -> double by integer ops (exact for the positive normal values here): the
     // conversion unit shares the XU pipe with the reciprocal of the division
-    float const xi = abscissa(inw, i_d, inwres, r.v, widen_positive(r.repwid));
-    if (r.hw0 == kHwLorentz)
-    {
-        return r.c/widen_positive(xi*xi + r.yq);
-    }
+    float const xi = abscissa(inw, i_d, inwres, A.x, widen_positive(B.x));
     float const ax = fabsf(xi);
-    if (ax >= r.xlim0 && r.hw0 != kHwCoreOnly)
+    if (ax >= B.w)
     {
         // far wing (RFM_voigt.c:168-171): almost every remote sample
-        return r.c*widen_positive(div_exact(r.yrrtpi, ax*ax + r.yq));
+        return A.y*widen_positive(div_exact(B.z, ax*ax + B.y));
     }
+    if (B.w != B.w)
+    {
+        return A.y/widen_positive(xi*xi + B.y);
+    }
+    LineRec const r = *full;
     return r.c*voigt_core(xi, r.y, r.xlim0, r.xlim1);
 }
 
@@ -392,6 +412,8 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
             unsigned long long const off = p.slot_off[s];
             if (p.slot_off[s+1] == off) continue;
             LineRec const *recs = p.sorted_recs + (size_t)layer*p.num_lines + off;
+            double2 const *wa = p.wing_a + (size_t)layer*p.num_lines + off;
+            float4 const *wb = p.wing_b + (size_t)layer*p.num_lines + off;
             BinRanges32 const R = ranges[((size_t)layer*b.n + k)*p.num_slots + s];
             // remote lines on the three interpolation points
 #pragma unroll 1
@@ -402,9 +424,10 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
 #pragma unroll 2
                 for (unsigned i=lo + lane; i<hi; i+=32)
                 {
-                    LineRec const r = recs[i];
+                    double2 const A = wa[i];
+                    float4 const B = wb[i];
 #pragma unroll
-                    for (int l=0; l<kNip; ++l) rem[l] += line_point(r, rem_w, (double)l, rem_res);
+                    for (int l=0; l<kNip; ++l) rem[l] += line_point(A, B, recs + i, rem_w, (double)l, rem_res);
                     evals += kNip;
                 }
             }
@@ -418,11 +441,13 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
                 {
                     unsigned const i = i0 + lane;
                     bool const have = i < R.loc_hi;
-                    LineRec const r = recs[have ? i : R.loc_lo];
+                    unsigned const ii = have ? i : R.loc_lo;
+                    double2 const A = wa[ii];
+                    float4 const B = wb[ii];
                     if (have) evals += (unsigned long long)npts;
                     for (int pt=0; pt<npts; ++pt)
                     {
-                        double a = have ? line_point(r, loc_w, (double)pt, b.wres) : 0.;
+                        double a = have ? line_point(A, B, recs + ii, loc_w, (double)pt, b.wres) : 0.;
                         for (int o=16; o>0; o>>=1) a += __shfl_down_sync(0xffffffffu, a, o);
                         if (lane == 0) sh_acc[g*ppb + pt] += a;
                     }
@@ -439,8 +464,7 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
 #pragma unroll 2
                     for (unsigned i=R.loc_lo; i<R.loc_hi; ++i)
                     {
-                        LineRec const r = recs[i];
-                        a += line_point(r, loc_w, (double)pt, b.wres);
+                        a += line_point(wa[i], wb[i], recs + i, loc_w, (double)pt, b.wres);
                         ++evals;
                     }
                     sh_acc[g*ppb + pt] += a;

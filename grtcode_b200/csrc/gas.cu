@@ -376,6 +376,8 @@ struct grt_gas
     LineRec *d_sorted_recs = nullptr;    // binned methods: records in sorted order
     int *d_seg_begin = nullptr;
     int *d_seg_end = nullptr;
+    double2 *d_wing_a = nullptr;         // binned methods: 32-byte far-wing records, sorted order
+    float4 *d_wing_b = nullptr;
     unsigned short *d_segkey = nullptr;  // [2][layers*lines] segment ids of the second sort pass
     void *d_sort_temp = nullptr;
     size_t sort_temp_bytes = 0;
@@ -605,7 +607,8 @@ segment_keys_kernel(unsigned const *gidx, SegmentMap const map, unsigned long lo
 __global__ void __launch_bounds__(256)
 sort_finish_kernel(unsigned const *gidx, double const *vkey, LineRec const *recs,
                    unsigned long long const num_lines, unsigned long long const total,
-                   unsigned *perm, double *vsorted, LineRec *sorted_recs)
+                   unsigned *perm, double *vsorted, LineRec *sorted_recs, double2 *wing_a,
+                   float4 *wing_b)
 {
     unsigned long long const pos = (unsigned long long)blockIdx.x*blockDim.x + threadIdx.x;
     if (pos >= total) return;
@@ -617,6 +620,7 @@ sort_finish_kernel(unsigned const *gidx, double const *vkey, LineRec const *recs
     uint4 *dst = reinterpret_cast<uint4 *>(sorted_recs + pos);
     uint4 const a = src[0], b = src[1], c = src[2], d = src[3];
     dst[0] = a; dst[1] = b; dst[2] = c; dst[3] = d;
+    wing_record(recs[gi], wing_a + pos, wing_b + pos);
 }
 
 static int sort_temp(grt_gas *g, size_t const bytes)
@@ -683,7 +687,8 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
             ++launches;
             // d_perm holds global indices in segment order
             sort_finish_kernel<<<(unsigned)((N*L + 255)/256), 256, 0, st>>>(
-                g->d_perm, g->d_vkey, g->d_recs, N, N*L, g->d_perm, g->d_vsorted, g->d_sorted_recs);
+                g->d_perm, g->d_vkey, g->d_recs, N, N*L, g->d_perm, g->d_vsorted, g->d_sorted_recs,
+                g->d_wing_a, g->d_wing_b);
             ++launches;
         }
         else
@@ -720,7 +725,8 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
                                                      g->d_perm, g->d_vidx, (int)(N*L), 0, seg_bits,
                                                      st));
             sort_finish_kernel<<<(unsigned)((N*L + 255)/256), 256, 0, st>>>(
-                g->d_vidx, g->d_vkey, g->d_recs, N, N*L, g->d_perm, g->d_vsorted, g->d_sorted_recs);
+                g->d_vidx, g->d_vkey, g->d_recs, N, N*L, g->d_perm, g->d_vsorted, g->d_sorted_recs,
+                g->d_wing_a, g->d_wing_b);
             launches += 4;
         }
     }
@@ -730,6 +736,8 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
     bp.vs = g->d_vsorted;
     bp.perm = g->d_perm;
     bp.sorted_recs = g->d_sorted_recs;
+    bp.wing_a = g->d_wing_a;
+    bp.wing_b = g->d_wing_b;
     bp.num_lines = N;
     bp.num_slots = N > 0 ? slots : 0;
     for (int sl=0; sl<=GRT_MAX_MOLS; ++sl)
@@ -841,7 +849,7 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_work_counter);
     cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
     cudaFree(g->d_sorted_recs);
-    cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_segkey); cudaFree(g->d_sort_temp); cudaFree(g->d_evals); cudaFree(g->d_ranges);
+    cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_segkey); cudaFree(g->d_wing_a); cudaFree(g->d_wing_b); cudaFree(g->d_sort_temp); cudaFree(g->d_evals); cudaFree(g->d_ranges);
     for (double *t : g->owned_tables) cudaFree(t);
     for (int k=0; k<5; ++k) if (g->ev[k]) cudaEventDestroy(g->ev[k]);
     delete g;
@@ -1024,8 +1032,10 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
         if (method != 2 && need > g->binned_capacity)
         {
             cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
-            cudaFree(g->d_sorted_recs); cudaFree(g->d_segkey);
+            cudaFree(g->d_sorted_recs); cudaFree(g->d_segkey); cudaFree(g->d_wing_a); cudaFree(g->d_wing_b);
             g->d_segkey = nullptr;
+            g->d_wing_a = nullptr;
+            g->d_wing_b = nullptr;
             g->d_vkey = g->d_vsorted = nullptr;
             g->d_vidx = g->d_perm = nullptr;
             g->d_sorted_recs = nullptr;
@@ -1035,6 +1045,8 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
             GRT_CUDA(cudaMalloc(&g->d_vidx, sizeof(unsigned)*need));
             GRT_CUDA(cudaMalloc(&g->d_perm, sizeof(unsigned)*need));
             GRT_CUDA(cudaMalloc(&g->d_segkey, sizeof(unsigned short)*2*need));
+            GRT_CUDA(cudaMalloc(&g->d_wing_a, sizeof(double2)*need));
+            GRT_CUDA(cudaMalloc(&g->d_wing_b, sizeof(float4)*need));
             g->binned_capacity = need;
         }
         line_prep_kernel<<<grid, 256, 0, st>>>(lv, L, lay, g->meta, g->w0, g->dw, g->nw, fsteps,

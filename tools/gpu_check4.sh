@@ -1,0 +1,10 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests/test_gpu_parity.py tests/test_driver.py -m gpu -q 2>&1 | tail -3
+for m in 0 1; do
+  GRT_METHOD=$m timeout 300 python tools/profile_c1.py 2>&1 | tail -1 | cut -c1-320 | sed "s/^/  c1 method=$m /"
+done
+make -B -C grtcode_b200/csrc EXTRA=-DGRT_BIN_MINBLOCKS=3 > gpurun_out/variant_build.log 2>&1 && make -C grtcode_b200/host >> gpurun_out/variant_build.log 2>&1
+for m in 0; do
+  GRT_METHOD=$m timeout 300 python tools/profile_c1.py 2>&1 | tail -1 | cut -c1-320 | sed "s/^/  minblocks=3 c1 method=$m /"
+done
