@@ -27,6 +27,7 @@ namespace grt {
 
 constexpr int kBinThreads = 256;          // one warp per bin of a gather group
 constexpr int kNip = 3;                 // spectral_bin-internal.h:30
+constexpr int kBinLanePerLine = 16;     // bins of up to 16 points: local lines lane per line
 
 struct BinGeometry
 {
@@ -295,28 +296,32 @@ __device__ __forceinline__ void wing_record(LineRec const &r, double2 *a, float4
     *b = make_float4(r.repwid, r.yq, r.yrrtpi, limit);
 }
 
-// S*N_s*K at one point of one line: rfm_voigt_line_shape for a single abscissa
+// acc += S*N_s*K at one point of one line: rfm_voigt_line_shape for a single abscissa
 // (RFM_voigt.c:97-106 pure Lorentz, :109-278 Voigt) with the scale of kernels.c:459 in c.
-// `full` is only dereferenced for the samples inside |x| < XLIM0.
-__device__ __forceinline__ double line_point(double2 const A, float4 const B, LineRec const *full,
-                                             double const inw, double const i_d,
-                                             double const inwres)
+// t2 = fl(w + fl(i*wres)), the grid wavenumber as RFM_voigt.c:165 forms it (the same for
+// every line, so the callers compute it once per point).  `full` is only dereferenced for the
+// samples inside |x| < XLIM0.
+__device__ __forceinline__ void line_point(double &acc, double2 const A, float4 const B,
+                                           LineRec const *full, double const t2)
 {
     // float -> double by integer ops (exact for the positive normal values here): the
     // conversion unit shares the XU pipe with the reciprocal of the division
-    float const xi = abscissa(inw, i_d, inwres, A.x, widen_positive(B.x));
+    float const xi = abscissa_from(t2, A.x, widen_positive(B.x));
     float const ax = fabsf(xi);
     if (ax >= B.w)
     {
         // far wing (RFM_voigt.c:168-171): almost every remote sample
-        return A.y*widen_positive(div_exact(B.z, ax*ax + B.y));
+        acc = fma(A.y, widen_positive(div_exact(B.z, ax*ax + B.y)), acc);
     }
-    if (B.w != B.w)
+    else if (B.w != B.w)
     {
-        return A.y/widen_positive(xi*xi + B.y);
+        acc += A.y/widen_positive(xi*xi + B.y);
     }
-    LineRec const r = *full;
-    return r.c*voigt_core(xi, r.y, r.xlim0, r.xlim1);
+    else
+    {
+        LineRec const r = *full;
+        acc = fma(r.c, voigt_core(xi, r.y, r.xlim0, r.xlim1), acc);
+    }
 }
 
 // bin_quad_interp (kernel_utils.c:81-103) at grid point j.
@@ -387,6 +392,8 @@ __global__ void __launch_bounds__(kBinThreads, GRT_BIN_MINBLOCKS)
 bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
 {
     extern __shared__ double sh_acc[];          // [kBinGroup][points per bin]
+    // coarse grids only: per-lane partial sums of the local lines, [kBinGroup][ppb][32]
+    double *sh_loc = sh_acc + kBinGroup*p.bins.ppb;
     __shared__ double sh_rem[kBinGroup][kNip];
     BinGeometry const &b = p.bins;
     unsigned long long const k0 = (unsigned long long)blockIdx.x*kBinGroup;
@@ -397,6 +404,10 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
     int const g = tid >> 5;                      // the warp's bin inside the group
     int const ppb = b.ppb;
     for (int q=tid; q<kBinGroup*ppb; q+=kBinThreads) sh_acc[q] = 0.;
+    if (ppb <= kBinLanePerLine)
+    {
+        for (int q=tid; q<kBinGroup*ppb*32; q+=kBinThreads) sh_loc[q] = 0.;
+    }
     __syncthreads();
     unsigned long long evals = 0;
     double rem[kNip] = {0., 0., 0.};
@@ -405,6 +416,9 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
         unsigned long long const k = k0 + g;
         double const rem_w = bin_w(b, k, 0);
         double const rem_res = __dsub_rn(bin_w(b, k, 1), rem_w);
+        double rem_t[kNip];
+#pragma unroll
+        for (int l=0; l<kNip; ++l) rem_t[l] = __dadd_rn(rem_w, __dmul_rn((double)l, rem_res));
         int const npts = bin_points(b, k);
         double const loc_w = __dadd_rn(b.w0, __dmul_rn((double)bin_left(b, k), b.wres));
         for (int s=0; s<p.num_slots; ++s)
@@ -427,29 +441,28 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
                     double2 const A = wa[i];
                     float4 const B = wb[i];
 #pragma unroll
-                    for (int l=0; l<kNip; ++l) rem[l] += line_point(A, B, recs + i, rem_w, (double)l, rem_res);
+                    for (int l=0; l<kNip; ++l) line_point(rem[l], A, B, recs + i, rem_t[l]);
                     evals += kNip;
                 }
             }
             // local lines on the bin's grid points
-            if (npts <= 16)
+            if (ppb <= kBinLanePerLine)
             {
                 // coarse grid: a lane per line (consecutive lines of the sorted list sit at
                 // nearly the same distance from a grid point, so the warp takes the same
-                // Voigt branch), each point's sum over the 32 lines by shuffles
-                for (unsigned i0=R.loc_lo; i0<R.loc_hi; i0+=32)
+                // Voigt branch); every lane keeps its own partial sum per grid point in shared
+                // memory (lane-contiguous, conflict-free), summed over the lanes once per bin
+                double *mine = sh_loc + (size_t)g*ppb*32 + lane;
+                for (unsigned i=R.loc_lo + lane; i<R.loc_hi; i+=32)
                 {
-                    unsigned const i = i0 + lane;
-                    bool const have = i < R.loc_hi;
-                    unsigned const ii = have ? i : R.loc_lo;
-                    double2 const A = wa[ii];
-                    float4 const B = wb[ii];
-                    if (have) evals += (unsigned long long)npts;
+                    double2 const A = wa[i];
+                    float4 const B = wb[i];
+                    evals += (unsigned long long)npts;
                     for (int pt=0; pt<npts; ++pt)
                     {
-                        double a = have ? line_point(A, B, recs + ii, loc_w, (double)pt, b.wres) : 0.;
-                        for (int o=16; o>0; o>>=1) a += __shfl_down_sync(0xffffffffu, a, o);
-                        if (lane == 0) sh_acc[g*ppb + pt] += a;
+                        double a = mine[pt*32];
+                        line_point(a, A, B, recs + i, __dadd_rn(loc_w, __dmul_rn((double)pt, b.wres)));
+                        mine[pt*32] = a;
                     }
                 }
             }
@@ -460,16 +473,27 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
                 {
                     int const pt = pbase + lane;
                     if (pt >= npts) continue;
+                    double const loc_t = __dadd_rn(loc_w, __dmul_rn((double)pt, b.wres));
                     double a = 0.;
 #pragma unroll 2
                     for (unsigned i=R.loc_lo; i<R.loc_hi; ++i)
                     {
-                        a += line_point(wa[i], wb[i], recs + i, loc_w, (double)pt, b.wres);
+                        line_point(a, wa[i], wb[i], recs + i, loc_t);
                         ++evals;
                     }
                     sh_acc[g*ppb + pt] += a;
                 }
             }
+        }
+    }
+    if (ppb <= kBinLanePerLine && g < ng)
+    {
+        __syncwarp();
+        for (int pt=0; pt<ppb; ++pt)
+        {
+            double a = sh_loc[((size_t)g*ppb + pt)*32 + lane];
+            for (int o=16; o>0; o>>=1) a += __shfl_down_sync(0xffffffffu, a, o);
+            if (lane == 0) sh_acc[g*ppb + pt] += a;
         }
     }
 #pragma unroll

@@ -752,7 +752,7 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
     bp.tau = tau_dev;
     bp.evals = g->d_evals;
     if (bp.bins.n > 0x7fffffffull) return fail("too many spectral bins");
-    size_t const smem = sizeof(double)*(size_t)bp.bins.ppb*kBinGroup;
+    size_t const smem = sizeof(double)*(size_t)bp.bins.ppb*kBinGroup*(bp.bins.ppb <= kBinLanePerLine ? 33 : 1);
     if (smem > 40*1024) return fail("spectral resolution too fine for the binned methods");
     size_t const nranges = (size_t)L*bp.bins.n*(size_t)std::max(bp.num_slots, 1);
     if (nranges > g->ranges_capacity)
