@@ -352,6 +352,7 @@ struct grt_gas
     // device buffers
     double *d_lines = nullptr;           // 7 arrays of num_lines
     uint16_t *d_slotiso = nullptr;
+    unsigned *d_core_order = nullptr;    // line_sample: records molecule by molecule (core kernel)
     uint64_t num_lines = 0;
     double *d_tips = nullptr;
     double *d_layer = nullptr;           // LayerView backing store
@@ -471,6 +472,21 @@ static int finalize_lines(grt_gas *g, int const method)
     if (!g->h_tips.empty())
     {
         GRT_CUDA(cudaMemcpyAsync(g->d_tips, g->h_tips.data(), sizeof(double)*g->h_tips.size(),
+                                 cudaMemcpyHostToDevice, g->stream));
+    }
+    if (g->d_core_order) { GRT_CUDA(cudaFree(g->d_core_order)); g->d_core_order = nullptr; }
+    if (method == 2 && n > 0)
+    {
+        // The core kernel walks one record per thread: neighbouring threads should hold lines
+        // of the same molecule at neighbouring wavenumbers (same Doppler width, so the same
+        // number of core samples and the same Voigt region at the same distance), which the
+        // merged centre-sorted list interleaves with the other molecules' lines.
+        std::vector<unsigned> co((size_t)n);
+        std::iota(co.begin(), co.end(), 0u);
+        std::stable_sort(co.begin(), co.end(),
+                         [&](unsigned a, unsigned b) { return (si[a] >> 8) < (si[b] >> 8); });
+        GRT_CUDA(cudaMalloc(&g->d_core_order, sizeof(unsigned)*n));
+        GRT_CUDA(cudaMemcpyAsync(g->d_core_order, co.data(), sizeof(unsigned)*n,
                                  cudaMemcpyHostToDevice, g->stream));
     }
     GRT_CUDA(cudaStreamSynchronize(g->stream));
@@ -840,6 +856,7 @@ int grt_gas_destroy(grt_gas *g)
     cudaStreamSynchronize(g->stream);
     cudaFree(g->d_lines);
     cudaFree(g->d_slotiso);
+    cudaFree(g->d_core_order);
     cudaFree(g->d_tips);
     cudaFree(g->d_layer);
     cudaFree(g->d_inputs);
@@ -1075,6 +1092,8 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     sp.lay = lay;
     sp.tab = g->tab;
     sp.tau = tau_dev;
+    sp.core_order = g->d_core_order;
+    if (char const *env = getenv("GRT_CORE_ORDER")) { if (env[0] == '0') sp.core_order = nullptr; }
 
     // Points per thread (PTS): LN*PTS points per warp tile; NL layers per work item.  Wider
     // tiles amortise the per-line work better; narrower ones waste fewer lanes at window

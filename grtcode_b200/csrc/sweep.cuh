@@ -45,6 +45,7 @@ struct SweepParams
     unsigned const *tile_first;  // per tile: first record whose window may reach it
     unsigned const *tile_last;   // per tile: one past the last such record
     unsigned int *work_counter;
+    unsigned const *core_order;  // core kernel: thread -> record (molecule-major), or null
     LayerView lay;
     Tables tab;
     double *tau;               // [layers][nw]
@@ -989,16 +990,17 @@ wing_sweep_kernel(SweepParams const p)
 // K3c: samples with |x| < XLIM1 (Humlicek regions 2, 3 and CPF12) of every Voigt-branch
 // record, plus every sample of the rare records flagged kHwCoreOnly.  One thread per
 // record walks outwards from the line centre (fc, fc-1, fc+1, ...): the records of a warp
-// are neighbours in the centre-sorted list, so at the same distance their |x| -- and
+// are neighbouring lines of one molecule (core_order), so at the same distance their |x| -- and
 // with it the branch of RFM_voigt.c:172-277 they take -- mostly agree and the warp stays
 // converged inside the expensive CPF12 sums.  Contributions are scattered with double
 // atomics (a few per cent of all samples).
 __global__ void __launch_bounds__(128)
 core_sweep_kernel(SweepParams const p)
 {
-    uint64_t const rec_id = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+    uint64_t const tid = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     int const layer = blockIdx.y;
-    if (rec_id >= p.num_lines) return;
+    if (tid >= p.num_lines) return;
+    uint64_t const rec_id = p.core_order != nullptr ? p.core_order[tid] : tid;
     LineRec const *rp = p.recs + (size_t)layer*p.num_lines + rec_id;
     float4 const B = *reinterpret_cast<float4 const *>(&rp->repwid);   // repwid, yq, yrrtpi, fc
     float4 const C = *reinterpret_cast<float4 const *>(&rp->hw0);      // hw0, y, xlim0, xlim1

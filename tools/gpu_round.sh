@@ -18,4 +18,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
 bash tools/gpu_prof.sh > gpurun_out/prof.log 2>&1
 ./tools/ubench/pipes > gpurun_out/ubench_pipes.txt 2>&1
 python tools/profile_c1.py > gpurun_out/c1.log 2>&1
+GRT_METHOD=0 python tools/profile_c1.py > gpurun_out/c1_wavenumber_sweep.log 2>&1
+GRT_METHOD=1 python tools/profile_c1.py > gpurun_out/c1_line_sweep.log 2>&1
 tail -3 gpurun_out/pytest_gpu.log; tail -c 600 gpurun_out/bench_full.log; tail -c 400 gpurun_out/bench_reference.log; tail -2 gpurun_out/c1.log
