@@ -111,6 +111,10 @@ def cpu_reference_sample(args, col, threads=None, reps: int = 1):
     from grtcode_b200 import workloads as W
     from oracle import ref as R
     from tests import parity
+    if threads is None:
+        # every host core this process may run on, set explicitly: torchrun exports
+        # OMP_NUM_THREADS=1 to its workers, which would otherwise time a one-thread reference
+        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
     lw, sw = W.circ1_bands(args.dw, args.scale)
     kind = "reference" if R.available() else "port"
     # twelve 20 cm-1 windows per band, spread over the band (~10-15 s of host work in all)
