@@ -19,3 +19,58 @@ def test_per_line_voigt_matches_the_restatement_bit_for_bit(built):
     """voigt_line_eval (hoisted constants, fp32x2 CPF12, slow-path-free division) ==
     voigt_core (RFM_voigt.c:109-277 sample by sample) on 2^28 (x, Y) pairs over all regions."""
     assert built.selftest_voigt(1 << 28, seed=4321) == 0
+
+
+def _tau(tmp, w0, wn, dw, levels, lines, seed, method, env):
+    """tau through the C API with the library's measurement knobs set as in `env`."""
+    import os
+    import numpy as np
+    from grtcode_b200 import synth
+    from tests import parity
+    ds = parity.build_dataset(str(tmp), w0, wn, lines, seed)
+    mols = tuple(lines.keys())
+    col = synth.make_column(levels, np.random.default_rng(seed), molecules=mols)
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        got = parity.gpu_column(ds, w0, wn, dw, col, mols, solvers=False, method=method)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    return got["tau"], got["stats"]
+
+
+@pytest.mark.parametrize("dw,levels", [(0.1, 30), (0.01, 8)])
+def test_sweep_variants_agree(built, tmp_path, dw, levels):
+    """Whole-warp lines, two and four lines at a time, every tile width: the same samples
+    summed in a different order (sweep.cuh, template parameters PTS and LN)."""
+    import numpy as np
+    from grtcode_b200 import synth
+    from tests import parity
+    lines = {synth.H2O: 2500, synth.CO2: 3500, synth.O3: 2000}
+    span = (600., 1000.) if dw == 0.1 else (700., 760.)
+    ref, st = _tau(tmp_path, *span, dw, levels, lines, 41, 2,
+                   {"GRT_SWEEP_LANES": "32", "GRT_SWEEP_PTS": "2" if dw == 0.1 else "8"})
+    for lanes, pts in ((32, 4), (32, 16), (16, 4), (16, 8), (16, 16), (8, 4), (8, 8), (8, 16)):
+        tau, st2 = _tau(tmp_path, *span, dw, levels, lines, 41, 2,
+                        {"GRT_SWEEP_LANES": str(lanes), "GRT_SWEEP_PTS": str(pts)})
+        assert st2["samples"] == st["samples"]
+        rel = parity.relative_error(tau, ref)
+        assert rel.max() <= 1e-12, (lanes, pts, float(rel.max()))
+    tau, _ = _tau(tmp_path, *span, dw, levels, lines, 41, 2, {"GRT_CORE_ORDER": "0"})
+    assert parity.relative_error(tau, ref).max() <= 1e-12
+
+
+@pytest.mark.parametrize("method", [0, 1])
+def test_binned_sort_paths_agree(built, tmp_path, method):
+    """Two device-wide radix passes against CUB's segmented sort: both stable, so the same
+    permutation and bit-identical optical depths."""
+    import numpy as np
+    from grtcode_b200 import synth
+    lines = {synth.H2O: 3000, synth.CO2: 4000, synth.O3: 1, synth.CH4: 2500}
+    a, _ = _tau(tmp_path, 500., 900., 0.1, 20, lines, 43, method, {"GRT_BIN_SORT": "d"})
+    b, _ = _tau(tmp_path, 500., 900., 0.1, 20, lines, 43, method, {"GRT_BIN_SORT": "s"})
+    assert np.array_equal(a, b)
