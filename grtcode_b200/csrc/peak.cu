@@ -105,6 +105,26 @@ __global__ void selftest_kernel(unsigned long long n, unsigned long long seed,
         unpack2(div_exact2_seeded(pack2(a, a2), pack2(b, b2)), p1, p2);
         if (__float_as_uint(p1) != __float_as_uint(q2)) ++local;
         if (__float_as_uint(p2) != __float_as_uint(__fdiv_rn(a2, b2))) ++local;
+        // XU-free |x|: random (t2, v, REPWID) of the sweep's ranges, and exact ties (a double
+        // half-way between two neighbouring floats, times one)
+        {
+            double const v0 = 1. + (double)(lo >> 4)*1e-4;                    // 1 .. 26844 cm-1
+            double const dv = ((double)(hi >> 8) - 8388608.)*3e-6 + 1e-9;     // +-25 cm-1
+            float const rw = __uint_as_float(((127u + 4u + (lo & 7u)) << 23) | (hi & 0x7fffffu));
+            double const rwd = widen_positive(rw);
+            double const t2 = v0 + dv;
+            float const want = __double2float_rn(__dmul_rn(fabs(__dsub_rn(t2, v0)), rwd));
+            if (want >= 64.f && want < 3e7f &&
+                __float_as_uint(abs_abscissa_alu(t2, v0, rwd)) != __float_as_uint(want)) ++local;
+            float const fl = __uint_as_float(((127u + 6u + lo%18u) << 23) | (hi & 0x7fffffu));
+            float const fn = __uint_as_float(__float_as_uint(fl) + 1u);
+            double const mid = 0.5*((double)fl + (double)fn);
+            double const near_mid = __hiloint2double(__double2hiint(mid), __double2loint(mid) + (int)(lo & 3u) - 1);
+            if (__float_as_uint(abs_abscissa_alu(mid, 0., 1.)) != __float_as_uint(__double2float_rn(mid))) ++local;
+            if (__float_as_uint(abs_abscissa_alu(near_mid, 0., 1.)) !=
+                __float_as_uint(__double2float_rn(near_mid))) ++local;
+            if (__float_as_uint(abs_abscissa_alu((double)fn, 0., 1.)) != __float_as_uint(fn)) ++local;
+        }
         // x*x + yq must round twice (RFM_voigt.c:166,170): the packed add of scalar products
         float s1, s2;
         unpack2(add2(mul2_unfused(pack2(a, a2), pack2(a, a2)), pack2(b, b2)), s1, s2);

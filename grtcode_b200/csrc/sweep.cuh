@@ -276,6 +276,12 @@ struct LineGrid<PTS, false, LN>
     }
 };
 
+// How many of every four point pairs of the fast class take the XU-free conversion (the XU
+// pipe and the issue slots are traded against each other; measured).
+#ifndef GRT_F2F_MIX
+#define GRT_F2F_MIX 0
+#endif
+
 // Line classes of the gather, decided once per (line, tile) by the lane that owns the
 // line in the staged batch.
 enum LineClass { kClsNone = 0, kClsFast, kClsFarEdge, kClsR1, kClsNear, kClsLorentzFull,
@@ -327,7 +333,9 @@ __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileC
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        f32x2 const xi = ((j/2) % 4 < GRT_F2F_MIX)
+            ? pack2(abs_abscissa_alu(grid.t2(j), A.x, repwid), abs_abscissa_alu(grid.t2(j + 1), A.x, repwid))
+            : abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
         f32x2 const xq = mul2_unfused(xi, xi);
         // GRT_SEED_MIX of every four pairs take the XU-free division (voigt.cuh)
         f32x2 const k = ((j/2) % 4 < GRT_SEED_MIX) ? div_exact2_seeded(yr2, add2(xq, yq2))
