@@ -124,6 +124,42 @@ __device__ __forceinline__ void block_accumulate(double v, double *dst, double *
     }
 }
 
+// The fused column kernels reduce one value per thread, level and direction: every warp
+// parks its own sum in shared memory (no barrier per level) and the block adds them up and
+// issues its atomics once, at the end of the kernel.
+struct LevelSums
+{
+    double v[2][GRT_MAX_LAYERS + 1][kSolverThreads/32];
+};
+
+__device__ __forceinline__ void warp_accumulate(double v, LevelSums &sums, int const dir,
+                                                int const level)
+{
+    for (int o=16; o>0; o>>=1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) sums.v[dir][level][threadIdx.x >> 5] = v;
+}
+
+__device__ __forceinline__ void clear_levels(LevelSums &sums)
+{
+    double *flat = &sums.v[0][0][0];
+    for (int t=threadIdx.x; t<(int)(sizeof(LevelSums)/sizeof(double)); t+=blockDim.x) flat[t] = 0.;
+    __syncthreads();
+}
+
+__device__ __forceinline__ void flush_levels(LevelSums const &sums, int const num_levels,
+                                             double *flux_up, double *flux_down)
+{
+    __syncthreads();
+    for (int t=threadIdx.x; t<2*num_levels; t+=blockDim.x)
+    {
+        int const dir = t/num_levels;
+        int const level = t - dir*num_levels;
+        double s = 0.;
+        for (int k=0; k<(int)(blockDim.x >> 5); ++k) s += sums.v[dir][level][k];
+        atomicAdd(dir ? &flux_down[level] : &flux_up[level], s);
+    }
+}
+
 // FUSED = false: tau/omega are the caller's total optics, spectral fluxes are
 // stored (drop-in calculate_lw_fluxes).  FUSED = true: tau is the gas optical
 // depth; Rayleigh is mixed in on the fly (as column_calculation does through
@@ -136,7 +172,8 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
           double const *tau, double const *omega, double const *emis, double *flux_up,
           double *flux_down, uint64_t const first, uint64_t const last)
 {
-    __shared__ double warp_sums[kSolverThreads/32];
+    __shared__ LevelSums sums;
+    if (FUSED) clear_levels(sums);
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     bool const live = i < nw;
     uint64_t const ii = live ? i : nw - 1;
@@ -193,7 +230,7 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         }
         if (FUSED)
         {
-            block_accumulate(f*weight, &flux_down[j+1], warp_sums);
+            warp_accumulate(f*weight, sums, 1, j + 1);
         }
         else if (live)
         {
@@ -211,7 +248,7 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     }
     if (FUSED)
     {
-        block_accumulate(f*weight, &flux_up[L], warp_sums);
+        warp_accumulate(f*weight, sums, 0, L);
     }
     else if (live)
     {
@@ -232,13 +269,14 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         }
         if (FUSED)
         {
-            block_accumulate(f*weight, &flux_up[j], warp_sums);
+            warp_accumulate(f*weight, sums, 0, j);
         }
         else if (live)
         {
             flux_up[(size_t)j*nw + ii] = f;
         }
     }
+    if (FUSED) flush_levels(sums, num_levels, flux_up, flux_down);
 }
 
 
@@ -315,10 +353,11 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
           double const *alb_dir, double const *alb_dif, double const tsi, double const *solar,
           double *flux_up, double *flux_down, uint64_t const first, uint64_t const last)
 {
-    __shared__ double warp_sums[kSolverThreads/32];
+    __shared__ LevelSums sums;
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     bool const live = i < nw;
     if (!FUSED && !live) return;
+    if (FUSED) clear_levels(sums);
     uint64_t const ii = live ? i : nw - 1;
     int const L = num_levels - 1;
     double const w = w0 + (double)ii*dw;
@@ -354,7 +393,7 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     }
 
     // Adding (shortwave.c:242-330).
-    double Rdd[MAXL + 1], Rfd[MAXL + 1], Rfu[MAXL];
+    double Rdd[MAXL + 1], Rfd[MAXL + 1];
     Rdd[L] = alb_dir[ii];
     Rfd[L] = alb_dif[ii];
     for (int j=L-1; j>=0; --j)
@@ -364,12 +403,9 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         Rdd[j] = R_dir[j] + (A*Rdd[j+1] + (T_dir[j] - A)*Rfd[j+1])*T_dif[j]*B;
         Rfd[j] = R_dif[j] + T_dif[j]*T_dif[j]*Rfd[j+1]*B;
     }
-    Rfu[0] = R_dif[0];
-    for (int j=1; j<L; ++j)
-    {
-        double const B = 1./(1. - R_dif[j]*Rfu[j-1]);
-        Rfu[j] = R_dif[j] + T_dif[j]*T_dif[j]*Rfu[j-1]*B;
-    }
+    // Rfu (reflectivity of the layers above a level to diffuse light from below,
+    // shortwave.c:262-268) is a top-down recursion: it is advanced inside the level loop
+    // below (the same operations in the same order) instead of being stored per layer.
     double const scale = solar[ii]*mu_dir;
     double weight = 0.;
     if (FUSED)
@@ -386,8 +422,8 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         double const down = tsi*(dir_beam*scale);
         if (FUSED)
         {
-            block_accumulate(up*weight, &flux_up[0], warp_sums);
-            block_accumulate(down*weight, &flux_down[0], warp_sums);
+            warp_accumulate(up*weight, sums, 0, 0);
+            warp_accumulate(down*weight, sums, 1, 0);
         }
         else
         {
@@ -395,12 +431,19 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
             flux_down[ii] = down;
         }
     }
+    double rfu_above = 0.;          // Rfu[j-2]
+    double rfu = R_dif[0];          // Rfu[j-1]
     for (int j=1; j<num_levels; ++j)
     {
         if (j > 1)
         {
-            double const C = 1./(1. - R_dif[j-1]*Rfu[j-2]);
-            dif_beam = (dir_beam*R_dir[j-1]*Rfu[j-2] + dif_beam)*T_dif[j-1]*C +
+            // Rfu[j-1] from Rfu[j-2]
+            double const Bu = 1./(1. - R_dif[j-1]*rfu);
+            double const next = R_dif[j-1] + T_dif[j-1]*T_dif[j-1]*rfu*Bu;
+            rfu_above = rfu;
+            rfu = next;
+            double const C = 1./(1. - R_dif[j-1]*rfu_above);
+            dif_beam = (dir_beam*R_dir[j-1]*rfu_above + dif_beam)*T_dif[j-1]*C +
                        dir_beam*(T_dir[j-1] - T_pure[j-1]);
         }
         else
@@ -408,15 +451,15 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
             dif_beam = dir_beam*(T_dir[j-1] - T_pure[j-1]);
         }
         dir_beam *= T_pure[j-1];
-        double const B = 1./(1. - Rfd[j]*Rfu[j-1]);
+        double const B = 1./(1. - Rfd[j]*rfu);
         double const R = (dir_beam*Rdd[j] + dif_beam*Rfd[j])*B;
-        double const T = dir_beam*(1. + Rdd[j]*Rfu[j-1]*B) + dif_beam*B;
+        double const T = dir_beam*(1. + Rdd[j]*rfu*B) + dif_beam*B;
         double const up = tsi*(R*scale);
         double const down = tsi*(T*scale);
         if (FUSED)
         {
-            block_accumulate(up*weight, &flux_up[j], warp_sums);
-            block_accumulate(down*weight, &flux_down[j], warp_sums);
+            warp_accumulate(up*weight, sums, 0, j);
+            warp_accumulate(down*weight, sums, 1, j);
         }
         else
         {
@@ -424,6 +467,7 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
             flux_down[(size_t)j*nw + ii] = down;
         }
     }
+    if (FUSED) flush_levels(sums, num_levels, flux_up, flux_down);
 }
 
 
