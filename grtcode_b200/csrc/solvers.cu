@@ -362,8 +362,18 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     int const L = num_levels - 1;
     double const w = w0 + (double)ii*dw;
 
+    // Layer reflectivities / transmittances and, in the same bottom-up loop, the adding
+    // recursions from the surface (shortwave.c:242-260): a layer's five values are in
+    // registers when Rdd / Rfd need them, so the per-thread arrays (local memory, the traffic
+    // that bounds this kernel) are written once here and read once by the level loop below.
+    // The layers are independent, so their order does not change any value.
     double R_dir[MAXL], R_dif[MAXL], T_dir[MAXL], T_dif[MAXL], T_pure[MAXL];
-    for (int j=0; j<L; ++j)
+    double Rdd[MAXL + 1], Rfd[MAXL + 1];
+    double rdd_below = alb_dir[ii];
+    double rfd_below = alb_dif[ii];
+    Rdd[L] = rdd_below;
+    Rfd[L] = rfd_below;
+    for (int j=L-1; j>=0; --j)
     {
         size_t const o = (size_t)j*nw + ii;
         double omega, g, tau;
@@ -388,20 +398,23 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         double const f = g*g;
         double const os = (1. - f)*omega/(1. - omega*f);
         double const ts = tau*(1. - omega*f);
-        eddington(os, ts, mu_dir, gs, &R_dir[j], &T_dir[j], &T_pure[j]);
-        eddington(os, ts, mu_dif, gs, &R_dif[j], &T_dif[j], nullptr);
-    }
-
-    // Adding (shortwave.c:242-330).
-    double Rdd[MAXL + 1], Rfd[MAXL + 1];
-    Rdd[L] = alb_dir[ii];
-    Rfd[L] = alb_dif[ii];
-    for (int j=L-1; j>=0; --j)
-    {
-        double const A = T_pure[j];
-        double const B = 1./(1. - R_dif[j]*Rfd[j+1]);
-        Rdd[j] = R_dir[j] + (A*Rdd[j+1] + (T_dir[j] - A)*Rfd[j+1])*T_dif[j]*B;
-        Rfd[j] = R_dif[j] + T_dif[j]*T_dif[j]*Rfd[j+1]*B;
+        double r_dir, t_dir, t_pure, r_dif, t_dif;
+        eddington(os, ts, mu_dir, gs, &r_dir, &t_dir, &t_pure);
+        eddington(os, ts, mu_dif, gs, &r_dif, &t_dif, nullptr);
+        R_dir[j] = r_dir;
+        T_dir[j] = t_dir;
+        T_pure[j] = t_pure;
+        R_dif[j] = r_dif;
+        T_dif[j] = t_dif;
+        // Adding (shortwave.c:242-260).
+        double const A = t_pure;
+        double const B = 1./(1. - r_dif*rfd_below);
+        double const rdd = r_dir + (A*rdd_below + (t_dir - A)*rfd_below)*t_dif*B;
+        double const rfd = r_dif + t_dif*t_dif*rfd_below*B;
+        Rdd[j] = rdd;
+        Rfd[j] = rfd;
+        rdd_below = rdd;
+        rfd_below = rfd;
     }
     // Rfu (reflectivity of the layers above a level to diffuse light from below,
     // shortwave.c:262-268) is a top-down recursion: it is advanced inside the level loop
