@@ -14,6 +14,7 @@
 // Rayleigh/total optics or spectral fluxes: they mix on the fly and reduce the
 // fluxes to broadband values inside the kernel.
 #include <cmath>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace grt {
@@ -345,8 +346,15 @@ __device__ void eddington(double const omega, double const tau, double const mu,
     }
 }
 
+// Resident blocks per SM the compiler must allow.  The solver is latency-bound on its
+// per-thread layer arrays (local memory that spills to DRAM: L2 hit rate 21 %): measured on
+// config 2, 1 / 2 / 3 / 4 / 6 / 8 / 10 blocks give 54.5 / 32.2 / 23.5 / 18.8 / 14.1 / 12.4 /
+// 12.1 ms, so the register budget is capped at 48 (a few spilled words) for ten blocks.
+#ifndef GRT_SW_MINBLOCKS
+#define GRT_SW_MINBLOCKS 10
+#endif
 template <int MAXL, bool FUSED>
-__global__ void __launch_bounds__(kSolverThreads)
+__global__ void __launch_bounds__(kSolverThreads, GRT_SW_MINBLOCKS)
 sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const nw,
           LayerDensity const dens, double const *omega_in, double const *g_in,
           double const *tau_in, double const mu_dir, double const mu_dif,
@@ -536,9 +544,30 @@ static int launch_sw(cudaStream_t st, int num_levels, double w0, double dw, uint
                      double *down, uint64_t first, uint64_t last)
 {
     unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
+    // Measurement knob: resident blocks per SM, enforced with idle dynamic shared memory (the
+    // per-thread layer arrays of the resident threads are what has to fit in L2).
+    size_t dyn = 0;
+    if (char const *env = getenv("GRT_SW_BLOCKS_PER_SM"))
+    {
+        int const want = atoi(env);
+        if (want >= 1 && want <= 16)
+        {
+            dyn = (size_t)(227*1024)/(size_t)want - (FUSED ? sizeof(LevelSums) : 0) - 1024;
+            dyn &= ~(size_t)255;
+            if (num_levels - 1 <= 64)
+            {
+                GRT_CUDA(cudaFuncSetAttribute(sw_kernel<64, FUSED>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+            }
+            else
+            {
+                dyn = 0;
+            }
+        }
+    }
     if (num_levels - 1 <= 64)
     {
-        sw_kernel<64, FUSED><<<blocks, kSolverThreads, 0, st>>>(
+        sw_kernel<64, FUSED><<<blocks, kSolverThreads, dyn, st>>>(
             num_levels, w0, dw, nw, dens, omega, g, tau, mu_dir, mu_dif, alb_dir, alb_dif, tsi,
             solar, up, down, first, last);
     }
