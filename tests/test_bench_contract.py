@@ -1,0 +1,45 @@
+"""The reference arm of bench.py (runs on the host cores, no GPU needed): JSON contract and
+thread count."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(env_extra, *args):
+    env = dict(os.environ)
+    env.update(env_extra)
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference",
+                          *args], env=env, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stderr[-2000:]
+    return out.stdout
+
+
+def test_reference_arm_line_and_threads(built, tmp_path):
+    """One bounded sample per band.  torchrun exports OMP_NUM_THREADS=1 to its workers; the
+    arm must still time the reference on every host core and say how many it used."""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("compiled reference not built (no /root/reference on this machine)")
+    text = _run({"OMP_NUM_THREADS": "1", "GRT_CPU_WINDOWS": "1",
+                 "GRT_BENCH_DATA": str(tmp_path)}, "--steps", "1", "--warmup", "0")
+    lines = [l for l in text.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["higher_is_better"] is True
+    assert d["unit"] == "pts*layers/s" and d["value"] > 0.
+    assert d["config"]["workload"].startswith("BASELINE config 2")
+    assert d["cpu_baseline"]["kind"] == "reference"
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+
+
+def test_reference_arm_other_ranks_do_nothing(built):
+    """Under torchrun only rank 0 runs the reference; the others exit 0 without output."""
+    text = _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}, "--gpus", "2")
+    assert [l for l in text.splitlines() if l.startswith("{")] == []
