@@ -4,9 +4,9 @@
  * the work is done by hand-written sm_100a CUDA kernels (include/grt_sm100.h).
  * Differences a caller can observe:
  *   - `device` must be a GPU id; HOST_ONLY returns GRTCODE_VALUE_ERR;
- *   - optical_depth_method: only line_sample is implemented on the GPU so far;
- *     the reference's default (NULL -> wavenumber_sweep) returns GRTCODE_VALUE_ERR
- *     at calculate_optical_depth time rather than silently changing algorithm;
+ *   - optical_depth_method: all three methods run on the GPU (NULL -> wavenumber_sweep as in
+ *     the reference, gas_optics.c:73-76); where the reference's binned methods read
+ *     uninitialised memory the result is the empty range;
  *   - GasOptics_t members differ (the struct is library-owned state; callers
  *     allocate it, e.g. through malloc_struct, and never touch the fields). */
 #ifndef GAS_OPTICS_H_
