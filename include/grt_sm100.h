@@ -80,7 +80,7 @@ int grt_gas_add_cia(grt_gas *gas, int species0, int species1, double const *cros
  * x_mol[GRT_MAX_MOLS][num_levels] (row = HITRAN id - 1), x_cfc[GRT_MAX_CFCS][num_levels]
  * (row = cfc id), x_cia[GRT_NUM_CIA_SPECIES][num_levels]; writes (overwrites)
  * tau_dev[num_layers][num_wpoints].  method follows enum OpticalDepthMethod
- * (gas-optics/src/gas_optics.h:88-93); only line_sample (2) is implemented. */
+ * (gas-optics/src/gas_optics.h:88-93): wavenumber_sweep (0), line_sweep (1), line_sample (2). */
 int grt_gas_optical_depth(grt_gas *gas, double const *p_atm, double const *t,
                           double const *x_mol, double const *x_cfc, double const *x_cia,
                           int method, double *tau_dev);
