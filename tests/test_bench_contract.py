@@ -43,3 +43,17 @@ def test_reference_arm_other_ranks_do_nothing(built):
     """Under torchrun only rank 0 runs the reference; the others exit 0 without output."""
     text = _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}, "--gpus", "2")
     assert [l for l in text.splitlines() if l.startswith("{")] == []
+
+
+def test_product_arm_fails_loudly_without_a_gpu(built):
+    """There is no CPU path in the product: without a CUDA device bench.py must stop with an
+    error, not fall back to anything (skipped where a GPU is visible)."""
+    from grtcode_b200 import api
+    api.load()
+    if api.num_gpus() > 0:
+        pytest.skip("a GPU is visible here")
+    proc = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1",
+                           "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert proc.returncode != 0
+    assert "no CUDA device visible" in proc.stderr
+    assert not [l for l in proc.stdout.splitlines() if l.startswith("{")]
