@@ -241,6 +241,290 @@ void ora_line_sample(uint64_t nlines, int nlay, double const *vnn, double const 
     }
 }
 
+/* ---- the two binned methods (library default wavenumber_sweep, and line_sweep) ---------
+ * Spectral bins of gas-optics/src/spectral_bin.c:30-96: bins of `width` cm-1 holding
+ * ppb = floor(width/wres) + 1 grid points (the last one what is left), three interpolation
+ * wavenumbers per bin (first point, midpoint, last point).
+ * shape[0..4] = ppb, last_ppb, number of bins, do_interp, do_last_interp. */
+#define ORA_NIP 3            /* spectral_bin-internal.h:30 */
+
+void ora_bins_shape(uint64_t nw, double wres, double width, uint64_t *shape)
+{
+    uint64_t const ppb = (uint64_t)(floor(width/wres) + 1);
+    uint64_t last = nw % ppb;
+    if (last == 0) last = ppb;
+    uint64_t n = nw/ppb;
+    if (ppb != last) ++n;
+    shape[0] = ppb;
+    shape[1] = last;
+    shape[2] = n;
+    shape[3] = ppb > 3;
+    shape[4] = last > 3;
+}
+
+/* spectral_bin.c:73-84: l, r = first / last grid index of each bin, w = its three
+ * interpolation wavenumbers. */
+void ora_bins_fill(uint64_t nw, double w0, double wres, double width, uint64_t *l, uint64_t *r,
+                   double *w)
+{
+    uint64_t shape[5];
+    ora_bins_shape(nw, wres, width, shape);
+    uint64_t const ppb = shape[0], last = shape[1], n = shape[2];
+    for (uint64_t i=0; i<n; ++i)
+    {
+        uint64_t const pts = i + 1 < n ? ppb : last;
+        l[i] = i*ppb;
+        r[i] = l[i] + pts - 1;
+        double const first = w0 + (double)(ppb*i)*wres;
+        double const final = first + (double)((int)pts - 1)*wres;
+        w[ORA_NIP*i] = first;
+        w[ORA_NIP*i + 2] = final;
+        w[ORA_NIP*i + 1] = 0.5f*(first + final);
+    }
+}
+
+/* kernels.c:135-172: per layer, the four line arrays ordered by centre; equal centres keep
+ * their order (the reference's insertion sort only moves an element past strictly larger
+ * ones). */
+void ora_sort_lines(uint64_t nlines, int nlay, double *vnn, double *snn, double *gamma,
+                    double *alpha)
+{
+#pragma omp parallel for schedule(dynamic)
+    for (int k=0; k<nlay; ++k)
+    {
+        double *v = vnn + (uint64_t)k*nlines, *s = snn + (uint64_t)k*nlines;
+        double *g = gamma + (uint64_t)k*nlines, *a = alpha + (uint64_t)k*nlines;
+        for (uint64_t i=1; i<nlines; ++i)
+        {
+            double const cv = v[i], cs = s[i], cg = g[i], ca = a[i];
+            uint64_t j = i;
+            for (; j > 0 && v[j-1] > cv; --j)
+            {
+                v[j] = v[j-1]; s[j] = s[j-1]; g[j] = g[j-1]; a[j] = a[j-1];
+            }
+            v[j] = cv; s[j] = cs; g[j] = cg; a[j] = ca;
+        }
+    }
+}
+
+/* kernel_utils.c:26-76.  Returns 0 when val lies outside the array; the reference then
+ * leaves left = 0, right = size - 1 and its callers ignore the error. */
+static int ora_bracket(uint64_t size, double const *a, double val, uint64_t *left,
+                       uint64_t *right)
+{
+    uint64_t lo = 0, hi = size - 1;
+    if (val < a[lo] || val > a[hi])
+    {
+        *left = lo;
+        *right = hi;
+        return 0;
+    }
+    if (a[lo] == val) hi = lo;
+    else if (a[hi] == val) lo = hi;
+    else
+    {
+        while (hi - lo > 1)
+        {
+            uint64_t const mid = lo + (hi - lo)/2;
+            if (a[mid] == val) { lo = hi = mid; break; }
+            if (val > a[mid]) lo = mid; else hi = mid;
+        }
+    }
+    *left = lo;
+    *right = hi;
+    return 1;
+}
+
+/* One line on the grid points of bin j (fine mesh) or on its three interpolation points. */
+static void ora_line_on_bin(double v, double sn, double g, double a, double w, uint64_t npts,
+                            double wres, double *dst, double *scratch)
+{
+    ora_voigt(w, npts, wres, v, g, a, scratch);
+    for (uint64_t q=0; q<npts; ++q) dst[q] += sn*scratch[q];
+}
+
+/* calc_optical_depth_bin_sweep, kernels.c:177-304 (lines sorted per layer).  "Local" lines
+ * (bracketed by the edges of bins j-1 .. j+1) go onto the bin's grid points, "remote" ones
+ * (out to 25 bins either side) onto its three interpolation points in bins_tau.  Where the
+ * reference hands bracket() an empty sub-array (kernels.c:251, 281: undefined there) the
+ * range is taken as empty. */
+void ora_bin_sweep(uint64_t nlines, int nlay, double const *vnn, double const *snn,
+                   double const *gamma, double const *alpha, double const *ns, uint64_t nw,
+                   double w0, double wres, double width, double *tau, double *bins_tau)
+{
+    uint64_t shape[5];
+    ora_bins_shape(nw, wres, width, shape);
+    uint64_t const nb = shape[2];
+    uint64_t *bl = (uint64_t *)malloc(sizeof(uint64_t)*nb), *br = (uint64_t *)malloc(sizeof(uint64_t)*nb);
+    double *bw = (double *)malloc(sizeof(double)*ORA_NIP*nb);
+    ora_bins_fill(nw, w0, wres, width, bl, br, bw);
+    uint64_t const none = (uint64_t)(-1);
+#pragma omp parallel for schedule(dynamic) collapse(2)
+    for (int i=0; i<nlay; ++i)
+    {
+        for (uint64_t j=0; j<nb; ++j)
+        {
+            double const *v = vnn + (uint64_t)i*nlines, *s = snn + (uint64_t)i*nlines;
+            double const *g = gamma + (uint64_t)i*nlines, *a = alpha + (uint64_t)i*nlines;
+            double *scratch = (double *)malloc(sizeof(double)*(shape[0] + ORA_NIP));
+            uint64_t reach = 1;
+            double const leftw = j > reach ? bw[ORA_NIP*(j - reach)] : bw[0];
+            double const rightw = j >= (nb - 1) - reach ? bw[ORA_NIP*nb - 1]
+                                                        : bw[ORA_NIP*(j + reach + 1) - 1];
+            uint64_t left = 0, right = 0, tmp;
+            if (leftw <= v[nlines-1] && rightw >= v[0])
+            {
+                ora_bracket(nlines, v, leftw, &left, &tmp);
+                ora_bracket(nlines - left, v + left, rightw, &tmp, &right);
+                right += left;
+                for (uint64_t k=left; k<=right; ++k)
+                {
+                    ora_line_on_bin(v[k], s[k]*ns[i], g[k], a[k], w0 + bl[j]*wres,
+                                    br[j] - bl[j] + 1, wres, tau + (uint64_t)i*nw + bl[j], scratch);
+                }
+            }
+            else if (leftw > v[nlines-1]) left = nlines;
+            else right = none;
+
+            reach = 25;
+            double const rem_w = bw[ORA_NIP*j];
+            double const rem_res = bw[ORA_NIP*j + 1] - rem_w;
+            double *rem = bins_tau + ((uint64_t)i*nb + j)*ORA_NIP;
+            double const leftw_r = j > reach ? bw[ORA_NIP*(j - reach)] : bw[0];
+            if (leftw >= v[0] && leftw_r <= v[nlines-1] && left > 0)
+            {
+                uint64_t left_r;
+                ora_bracket(left, v, leftw_r, &left_r, &tmp);
+                for (uint64_t k=left_r; k<left; ++k)
+                {
+                    ora_line_on_bin(v[k], s[k]*ns[i], g[k], a[k], rem_w, ORA_NIP, rem_res, rem, scratch);
+                }
+            }
+            double const rightw_r = j >= (nb - 1) - reach ? bw[ORA_NIP*nb - 1]
+                                                          : bw[ORA_NIP*(j + reach + 1) - 1];
+            if (rightw <= v[nlines-1] && rightw_r >= v[0])
+            {
+                uint64_t const start = right == none ? 0 : right;    /* right + f */
+                if (start < nlines)
+                {
+                    uint64_t right_r;
+                    ora_bracket(nlines - start, v + start, rightw_r, &tmp, &right_r);
+                    right_r += start;
+                    for (uint64_t k=(right == none ? 0 : right + 1); k<=right_r; ++k)
+                    {
+                        ora_line_on_bin(v[k], s[k]*ns[i], g[k], a[k], rem_w, ORA_NIP, rem_res, rem,
+                                        scratch);
+                    }
+                }
+            }
+            free(scratch);
+        }
+    }
+    free(bl); free(br); free(bw);
+}
+
+/* calc_optical_depth_line_sweep, kernels.c:308-406 (no sorting): every line goes onto the
+ * grid points of the bins within 1.5 cm-1 of it and onto the interpolation points of the bins
+ * out to 25 cm-1.  Serial per layer instead of atomics.  A bin index equal to the number of
+ * bins (a line at the very end of the grid, kernels.c:346-350: out of bounds there) is
+ * dropped. */
+void ora_line_sweep(uint64_t nlines, int nlay, double const *vnn, double const *snn,
+                    double const *gamma, double const *alpha, double const *ns, uint64_t nw,
+                    double w0, double wres, double width, double *tau, double *bins_tau)
+{
+    uint64_t shape[5];
+    ora_bins_shape(nw, wres, width, shape);
+    uint64_t const nb = shape[2];
+    uint64_t *bl = (uint64_t *)malloc(sizeof(uint64_t)*nb), *br = (uint64_t *)malloc(sizeof(uint64_t)*nb);
+    double *bw = (double *)malloc(sizeof(double)*ORA_NIP*nb);
+    ora_bins_fill(nw, w0, wres, width, bl, br, bw);
+    double const bin_width = wres*(double)shape[0];
+    double const maxw = w0 + (double)nw*wres;
+#pragma omp parallel for schedule(dynamic)
+    for (int i=0; i<nlay; ++i)
+    {
+        double *scratch = (double *)malloc(sizeof(double)*(shape[0] + ORA_NIP));
+        for (uint64_t j=0; j<nlines; ++j)
+        {
+            uint64_t const o = (uint64_t)i*nlines + j;
+            double const sn = snn[o]*ns[i];
+            double cut = 1.5f;
+            double lo = vnn[o] - cut;
+            if (lo < w0) lo = w0;
+            uint64_t const left = (uint64_t)floor((lo - w0)/bin_width);
+            double hi = vnn[o] + cut;
+            if (hi > maxw) hi = maxw;
+            uint64_t const right = (uint64_t)floor((hi - w0)/bin_width);
+            for (uint64_t k=left; k<=right && k<nb; ++k)
+            {
+                ora_line_on_bin(vnn[o], sn, gamma[o], alpha[o], w0 + bl[k]*wres, br[k] - bl[k] + 1,
+                                wres, tau + (uint64_t)i*nw + bl[k], scratch);
+            }
+            cut = 25.f;
+            lo = vnn[o] - cut;
+            if (lo < w0) lo = w0;
+            uint64_t const left_r = (uint64_t)floor((lo - w0)/bin_width);
+            for (uint64_t k=left_r; k<left && k<nb; ++k)
+            {
+                ora_line_on_bin(vnn[o], sn, gamma[o], alpha[o], bw[ORA_NIP*k], ORA_NIP,
+                                bw[ORA_NIP*k + 1] - bw[ORA_NIP*k],
+                                bins_tau + ((uint64_t)i*nb + k)*ORA_NIP, scratch);
+            }
+            hi = vnn[o] + cut;
+            if (hi > maxw) hi = maxw;
+            uint64_t const right_r = (uint64_t)floor((hi - w0)/bin_width);
+            for (uint64_t k=right+1; k<=right_r && k<nb; ++k)
+            {
+                ora_line_on_bin(vnn[o], sn, gamma[o], alpha[o], bw[ORA_NIP*k], ORA_NIP,
+                                bw[ORA_NIP*k + 1] - bw[ORA_NIP*k],
+                                bins_tau + ((uint64_t)i*nb + k)*ORA_NIP, scratch);
+            }
+        }
+        free(scratch);
+    }
+    free(bl); free(br); free(bw);
+}
+
+/* interpolate + interpolate_last_bin (kernels.c:514-581) with bin_quad_interp /
+ * bin_no_interp (kernel_utils.c:81-118): the remote sums of every bin, interpolated
+ * quadratically in wavenumber and clamped at zero (or copied when a bin has at most three
+ * points), are added to tau. */
+void ora_bins_interpolate(int nlay, uint64_t nw, double w0, double wres, double width,
+                          double const *bins_tau, double *tau)
+{
+    uint64_t shape[5];
+    ora_bins_shape(nw, wres, width, shape);
+    uint64_t const nb = shape[2];
+    uint64_t *bl = (uint64_t *)malloc(sizeof(uint64_t)*nb), *br = (uint64_t *)malloc(sizeof(uint64_t)*nb);
+    double *bw = (double *)malloc(sizeof(double)*ORA_NIP*nb);
+    ora_bins_fill(nw, w0, wres, width, bl, br, bw);
+    for (int i=0; i<nlay; ++i)
+    {
+        for (uint64_t j=0; j<nb; ++j)
+        {
+            int const quad = j + 1 < nb ? (int)shape[3] : (int)shape[4];
+            double const *x = bw + ORA_NIP*j;
+            double const *y = bins_tau + ((uint64_t)i*nb + j)*ORA_NIP;
+            double *t = tau + (uint64_t)i*nw;
+            for (uint64_t f=bl[j]; f<=br[j]; ++f)
+            {
+                if (!quad)
+                {
+                    t[f] += y[f - bl[j]];
+                    continue;
+                }
+                double const w = w0 + f*wres;
+                double q = (w - x[1])*(w - x[2])*y[0]/((x[0] - x[1])*(x[0] - x[2])) +
+                           (w - x[0])*(w - x[2])*y[1]/((x[1] - x[0])*(x[1] - x[2])) +
+                           (w - x[0])*(w - x[1])*y[2]/((x[2] - x[0])*(x[2] - x[1]));
+                if (q < 0.f) q = 0.f;
+                t[f] += q;
+            }
+        }
+    }
+    free(bl); free(br); free(bw);
+}
+
 /* kernels.c:469-491 with the argument order of launch.c:165-170. */
 void ora_h2o_continuum(uint64_t nw, int nlay, double *tau, double const *CS, double const *T,
                        double const *Ps, double const *N, double const *T0, double const *CF,

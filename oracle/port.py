@@ -5,7 +5,8 @@ file parsing and orchestration are restated here in numpy:
 
 * HITRAN records   -> parse_hitran      (gas-optics/src/parse_HITRAN_file.c:224-413)
 * CSV tables       -> read_table        (utilities/src/parse_csv.c:55-166)
-* launch()         -> gas_optical_depth (gas-optics/src/launch.c:40-226, line_sample)
+* launch()         -> gas_optical_depth (gas-optics/src/launch.c:40-226, all three
+                      optical_depth_methods: kernels.c:135-465, 514-581)
 * column solve     -> column_fluxes     (framework/src/driver.c:360-424)
 
 Parity status: pinned against the compiled reference (tests/test_oracle.py) and
@@ -56,6 +57,14 @@ def lib():
                                       _dp, _dp]
         L.ora_line_sample.argtypes = [C.c_uint64, C.c_int, _dp, _dp, _dp, _dp, _dp, C.c_double,
                                       C.c_double, C.c_uint64, _dp]
+        _up = C.POINTER(C.c_uint64)
+        L.ora_bins_shape.argtypes = [C.c_uint64, C.c_double, C.c_double, _up]
+        L.ora_sort_lines.argtypes = [C.c_uint64, C.c_int, _dp, _dp, _dp, _dp]
+        for fn in (L.ora_bin_sweep, L.ora_line_sweep):
+            fn.argtypes = [C.c_uint64, C.c_int, _dp, _dp, _dp, _dp, _dp, C.c_uint64, C.c_double,
+                           C.c_double, C.c_double, _dp, _dp]
+        L.ora_bins_interpolate.argtypes = [C.c_int, C.c_uint64, C.c_double, C.c_double, C.c_double,
+                                           _dp, _dp]
         L.ora_h2o_continuum.argtypes = [C.c_uint64, C.c_int, _dp, _dp, _dp, _dp, _dp, _dp, _dp,
                                         _dp, _dp]
         L.ora_o3_continuum.argtypes = [C.c_uint64, C.c_int, _dp, _dp, _dp]
@@ -149,10 +158,17 @@ def solar_flux(path: str, w0: float, dw: float, nw: int) -> np.ndarray:
     return c/total
 
 
-class GasOptics:
-    """launch() of gas-optics/src/launch.c with optical_depth_method = line_sample."""
+WAVENUMBER_SWEEP, LINE_SWEEP, LINE_SAMPLE = 0, 1, 2      # gas_optics.h:88-93
+BIN_WIDTH = 1.                                           # gas_optics.c:73
 
-    def __init__(self, num_levels, w0, wn, dw, hitran, h2o_ctm_dir=None, o3_ctm=None):
+
+class GasOptics:
+    """launch() of gas-optics/src/launch.c; method as enum OpticalDepthMethod (the drivers
+    use line_sample, the library default is wavenumber_sweep)."""
+
+    def __init__(self, num_levels, w0, wn, dw, hitran, h2o_ctm_dir=None, o3_ctm=None,
+                 method=LINE_SAMPLE):
+        self.method = method
         self.levels = num_levels
         self.w0, self.wn, self.dw = w0, wn, dw
         self.nw = grid_size(w0, wn, dw)
@@ -197,6 +213,9 @@ class GasOptics:
                                tavg.ctypes.data_as(_dp))
         tau = np.zeros((nlay, self.nw))
         taup = tau.ctypes.data_as(_dp)
+        shape = (C.c_uint64*5)()
+        L.ora_bins_shape(self.nw, self.dw, BIN_WIDTH, shape)
+        bins_tau = np.zeros((nlay, int(shape[2]), 3))       # launch.c:61-64: both zeroed
         for mol, ln in self.mols:
             x, xp = _d(self.x.get(mol, np.zeros(self.levels)))
             ps, ns = np.zeros(nlay), np.zeros(nlay)
@@ -213,8 +232,16 @@ class GasOptics:
                                   _d(ln["d"])[1], pavg.ctypes.data_as(_dp),
                                   tavg.ctypes.data_as(_dp), ps.ctypes.data_as(_dp),
                                   *[a.ctypes.data_as(_dp) for a in arr])
-                L.ora_line_sample(nl, nlay, *[a.ctypes.data_as(_dp) for a in arr],
-                                  ns.ctypes.data_as(_dp), self.w0, self.dw, self.nw, taup)
+                ptrs = [a.ctypes.data_as(_dp) for a in arr]
+                if self.method == LINE_SAMPLE:
+                    L.ora_line_sample(nl, nlay, *ptrs, ns.ctypes.data_as(_dp), self.w0, self.dw,
+                                      self.nw, taup)
+                else:
+                    if self.method == WAVENUMBER_SWEEP:
+                        L.ora_sort_lines(nl, nlay, *ptrs)                   # launch.c:138
+                    sweep = L.ora_bin_sweep if self.method == WAVENUMBER_SWEEP else L.ora_line_sweep
+                    sweep(nl, nlay, *ptrs, ns.ctypes.data_as(_dp), self.nw, self.w0, self.dw,
+                          BIN_WIDTH, taup, bins_tau.ctypes.data_as(_dp))
             if mol == 1 and self.h2o is not None:
                 h = self.h2o
                 L.ora_h2o_continuum(self.nw, nlay, taup, _d(h["S296"])[1],
@@ -230,6 +257,10 @@ class GasOptics:
             x1, x1p = _d(self.x_cia.get(a, np.zeros(self.levels)))
             x2, x2p = _d(self.x_cia.get(b, np.zeros(self.levels)))
             L.ora_cia(self.nw, nlay, pp, tavg.ctypes.data_as(_dp), x1p, x2p, _d(xs)[1], taup)
+        if self.method != LINE_SAMPLE:
+            # launch.c:212-218: the remote sums are interpolated onto the grid last
+            L.ora_bins_interpolate(nlay, self.nw, self.w0, self.dw, BIN_WIDTH,
+                                   bins_tau.ctypes.data_as(_dp), taup)
         return tau
 
 

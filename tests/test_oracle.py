@@ -208,6 +208,36 @@ def test_port_matches_reference_column(port, ref, tmp_path, case):
 
 
 @needs_ref
+@pytest.mark.parametrize("method", [P.WAVENUMBER_SWEEP, P.LINE_SWEEP],
+                         ids=["wavenumber_sweep", "line_sweep"])
+@pytest.mark.parametrize("case", ["dense", "sparse", "fine", "coarse"])
+def test_port_matches_reference_binned_methods(port, ref, tmp_path, method, case):
+    """The restatement of sort_lines / calc_optical_depth_bin_sweep / _line_sweep /
+    interpolate (kernels.c:135-406, 514-581; bracket and the bin interpolators of
+    kernel_utils.c; create_spectral_bins) against the compiled reference.  "sparse": molecules
+    with a handful of lines (bracket's out-of-range returns); "fine": 101 points per bin;
+    "coarse": 2 points per bin, i.e. no interpolation (bin_no_interp)."""
+    lines, w0, wn, dw, levels = {
+        "dense": ({1: 600, 2: 900, 3: 500}, 400., 900., 0.1, 8),
+        "sparse": ({1: 40, 5: 5, 7: 12}, 1000., 1400., 0.05, 6),
+        "fine": ({1: 60, 2: 80}, 1000., 1012., 0.01, 5),
+        "coarse": ({1: 200, 2: 300}, 500., 900., 1., 6),
+    }[case]
+    ds = synth.make_dataset(str(tmp_path), w0, wn, lines, seed=31)
+    mols = tuple(lines)
+    col = synth.make_column(levels, np.random.default_rng(31), molecules=mols)
+    want = parity.oracle_column(ds, w0, wn, dw, col, mols, solvers=False, method=method)
+    go = P.GasOptics(levels, w0, wn, dw, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm, method=method)
+    for m in mols:
+        go.add_molecule(m)
+        go.set_ppmv("mol", m, col.ppmv[m])
+    tau = go.optical_depth(col.p, col.t)
+    rel = parity.relative_error(tau, want["tau"])
+    assert rel.max() <= 1e-12, (case, method, float(rel.max()),
+                                np.unravel_index(int(rel.argmax()), rel.shape))
+
+
+@needs_ref
 def test_reference_unit_pins_through_compiled_reference(ref):
     """The compiled reference itself against test_kernels.c:160-241 (sanity of the
     oracle build: flags, tips shim, struct layouts)."""
