@@ -222,3 +222,28 @@ def test_full_size_fine_grid_chunks_reproduce_the_whole(built, tmp_path):
     rel = parity.relative_error(sub, ref)
     print(f"chunk vs whole: max rel {rel.max():.3e} over {sub.size} points")
     assert rel.max() <= 1e-9
+
+
+# ---- committed outputs of the reference (tests/golden/reference_outputs.json) -------------
+
+@pytest.mark.parametrize("name,method", [("wavenumber_sweep", 0), ("line_sweep", 1),
+                                         ("line_sample", 2)])
+def test_golden_reference_outputs(built, name, method):
+    """The CUDA path against outputs of the compiled reference committed as a fixture
+    (tools/make_golden_outputs.py), i.e. without oracle/_ref: optical depths of the three
+    methods with continua, one CFC and one CIA pair, and the broadband fluxes."""
+    from tests.test_oracle import _golden_case
+    g, c, ds, mols, col = _golden_case()
+    got = parity.gpu_column(ds, c["w0"], c["wn"], c["dw"], col, mols, solvers=(method == 2),
+                            method=method)
+    want = np.array(g["tau"][name])
+    rel = parity.relative_error(got["tau"], want)
+    assert rel.max() <= TAU_RTOL, f"{name}: tau max rel {rel.max():.3e}"
+    if method == 2:
+        bb = g["broadband_W_m2"]
+        assert np.abs(got["lw_bb_up"] - np.array(bb["lw_up"])).max() <= FLUX_ATOL
+        assert np.abs(got["lw_bb_dn"] - np.array(bb["lw_dn"])).max() <= FLUX_ATOL
+        assert np.abs(got["sw_bb_up"] - np.array(bb["sw_up"])).max() <= FLUX_ATOL
+        assert np.abs(got["sw_bb_dn"] - np.array(bb["sw_dn"])).max() <= FLUX_ATOL
+        dw = c["dw"]
+        assert np.abs(parity.R.broadband(got["lw_up"], dw) - np.array(bb["lw_up"])).max() <= 1e-9

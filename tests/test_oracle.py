@@ -237,6 +237,67 @@ def test_port_matches_reference_binned_methods(port, ref, tmp_path, method, case
                                 np.unravel_index(int(rel.argmax()), rel.shape))
 
 
+def _golden_case():
+    """tests/golden/reference_outputs.json (tools/make_golden_outputs.py): outputs of the
+    compiled reference on a tiny seeded case, with the inputs regenerated from the seeds."""
+    import hashlib
+    import json
+    import tempfile
+    g = json.load(open(os.path.join(GOLD, "reference_outputs.json")))
+    c = g["case"]
+    tmp = tempfile.mkdtemp(prefix="grt_golden_")
+    lines = {int(k): v for k, v in c["lines"].items()}
+    ds = synth.make_dataset(tmp, c["w0"], c["wn"], lines, seed=c["seed"], cfcs=tuple(c["cfcs"]),
+                            cias=tuple(tuple(x) for x in c["cias"]))
+    assert hashlib.sha256(open(ds.hitran, "rb").read()).hexdigest() == g["hitran_sha256"], \
+        "the synthetic input generator no longer reproduces the golden inputs"
+    mols = tuple(lines)
+    col = synth.make_column(c["levels"], np.random.default_rng(c["seed"]), molecules=mols,
+                            cfcs=tuple(ds.cfc.keys()))
+    return g, c, ds, mols, col
+
+
+@pytest.mark.parametrize("name,method", [("wavenumber_sweep", 0), ("line_sweep", 1),
+                                         ("line_sample", 2)])
+def test_port_matches_golden_reference_outputs(port, name, method):
+    """No /root/reference, no oracle/_ref needed: the restatement against committed outputs of
+    the reference for the paths its own tests leave unpinned (optical depths of the three
+    methods incl. continua, CFC and CIA; broadband fluxes)."""
+    g, c, ds, mols, col = _golden_case()
+    go = P.GasOptics(c["levels"], c["w0"], c["wn"], c["dw"], ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm,
+                     method=method)
+    for m in mols:
+        go.add_molecule(m)
+        go.set_ppmv("mol", m, col.ppmv[m])
+    for k, path in ds.cfc.items():
+        go.add_cfc(k, path)
+        go.set_ppmv("cfc", k, col.cfc_ppmv[k])
+    for (a, b), path in ds.cia.items():
+        go.add_cia(a, b, path)
+    for k in (0, 1):
+        go.set_ppmv("cia", k, col.cia_ppmv[k])
+    tau = go.optical_depth(col.p, col.t)
+    want = np.array(g["tau"][name])
+    assert tau.shape == want.shape
+    assert parity.relative_error(tau, want).max() <= 1e-12
+    if method != 2:
+        return
+    nw = tau.shape[1]
+    om_r, g_r, tau_r = P.rayleigh(col.p, c["w0"], c["dw"], nw)
+    g_t, om_t, tau_t = P.add_optics([(np.zeros_like(tau), np.zeros_like(tau), tau),
+                                     (g_r, om_r, tau_r)])
+    up, dn = P.lw_fluxes(c["w0"], c["dw"], tau_t, om_t, col.t_surf, col.t_layer, col.t,
+                         np.full(nw, col.emissivity))
+    bb = g["broadband_W_m2"]
+    assert np.abs(P.broadband(up, c["dw"]) - np.array(bb["lw_up"])).max() <= 1e-9
+    assert np.abs(P.broadband(dn, c["dw"]) - np.array(bb["lw_dn"])).max() <= 1e-9
+    sol = P.solar_flux(ds.solar, c["w0"], c["dw"], nw)
+    alb = np.full(nw, col.albedo)
+    up, dn = P.sw_fluxes(om_t, g_t, tau_t, col.mu0, 0.5, alb, alb, col.tsi, sol)
+    assert np.abs(P.broadband(up, c["dw"]) - np.array(bb["sw_up"])).max() <= 1e-9
+    assert np.abs(P.broadband(dn, c["dw"]) - np.array(bb["sw_dn"])).max() <= 1e-9
+
+
 @needs_ref
 def test_reference_unit_pins_through_compiled_reference(ref):
     """The compiled reference itself against test_kernels.c:160-241 (sanity of the
