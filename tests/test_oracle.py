@@ -257,6 +257,18 @@ def _golden_case():
     return g, c, ds, mols, col
 
 
+def test_port_voigt_matches_golden_reference_outputs(port):
+    """rfm_voigt_line_shape (unpinned in the reference's own tests) against committed outputs of
+    the compiled reference: every branch of RFM_voigt.c:97-278."""
+    g = json.load(open(os.path.join(GOLD, "reference_outputs.json")))
+    assert len(g["voigt"]) == 18
+    for c in g["voigt"]:
+        k = P.voigt(c["w"], c["n"], c["wres"], c["center"], c["gamma"], c["alpha"])
+        want = np.array(c["K"])
+        # float arithmetic throughout: identical up to the last bit of libm's double exp
+        assert parity.relative_error(k, want).max() <= 1e-12, c["gamma"]
+
+
 @pytest.mark.parametrize("name,method", [("wavenumber_sweep", 0), ("line_sweep", 1),
                                          ("line_sample", 2)])
 def test_port_matches_golden_reference_outputs(port, name, method):

@@ -26,6 +26,11 @@ CASE = dict(w0=950., wn=990., dw=0.1, levels=4, lines={1: 60, 2: 80, 3: 40}, see
             cfcs=["CFC11"], cias=[[0, 0]])
 
 
+VOIGT_CASES = [(1000.03, 1e-7, 9e-4), (1000.03, 5e-4, 9e-4), (1000.03, 2e-3, 9e-4),
+               (1000.03, 8e-3, 9e-4), (1000.03, 0.03, 9e-4), (1000.03, 0.09, 9e-4),
+               (50.01, 0.08, 7e-5), (20000.4, 0.05, 0.03), (1000.03, 0., 9e-4)]
+
+
 def build(root):
     ds = synth.make_dataset(root, CASE["w0"], CASE["wn"], {int(k): v for k, v in CASE["lines"].items()},
                             seed=CASE["seed"], cfcs=tuple(CASE["cfcs"]),
@@ -53,6 +58,16 @@ def main():
             if method == 2:
                 bb = lambda f: [float(x) for x in R.broadband(f, CASE["dw"])]
                 out["broadband_W_m2"] = {k: bb(want[k]) for k in ("lw_up", "lw_dn", "sw_up", "sw_dn")}
+        # rfm_voigt_line_shape itself: nine (centre, gamma, alpha) triples covering every branch
+        # (far wing, regions 1-3, both CPF12 forms, pure Lorentz, Y = 0), 41 points each
+        r = R.Ref(threads=1)
+        out["voigt"] = []
+        for v, gamma, alpha in VOIGT_CASES:
+            for wres in (0.1, 0.001):
+                w = v - 20*wres + 0.37*wres
+                k = r.voigt(w, 41, wres, v, gamma, alpha)
+                out["voigt"].append({"w": w, "n": 41, "wres": wres, "center": v, "gamma": gamma,
+                                     "alpha": alpha, "K": [float(x) for x in k]})
         path = os.path.join(ROOT, "tests", "golden", "reference_outputs.json")
         json.dump(out, open(path, "w"))
         print(path, os.path.getsize(path), "bytes")
