@@ -237,6 +237,40 @@ def test_port_matches_reference_binned_methods(port, ref, tmp_path, method, case
                                 np.unravel_index(int(rel.argmax()), rel.shape))
 
 
+@needs_ref
+@pytest.mark.parametrize("layers", [1, 7, 200])
+@pytest.mark.parametrize("case", ["simple", "thick", "thin", "strong", "decades",
+                                  "pure_absorption", "conservative", "mixed_branches"])
+def test_port_solvers_on_the_reference_test_cases(port, case, layers):
+    """The restated solvers on the inputs of longwave/test/test_longwave.c and
+    shortwave/test/test_shortwave.c (plus the branch cases of tests/test_gpu_solvers.py) against
+    the reference's FAST build, which evaluates the same formulas without the range checks and
+    floating-point traps that leave the checked build's output undefined on some of them."""
+    from tests import test_gpu_solvers as S
+    fast = R.Ref(fast=True)
+    rg = fast.grid(S.W0, S.WN, S.DW)
+    n = int(rg.n)
+    if case in ("simple", "thick", "thin", "strong", "decades"):
+        tau = S._tau_case(case, layers, n, np.random.default_rng(11))
+        t_lay, t_lev, t_surf = S._atmosphere(layers)
+        emis = np.full(n, 0.98)
+        ro = R.RefOptics(fast, layers, rg)
+        ro.tau[:] = tau
+        want = R.lw_fluxes(fast, ro, t_surf, t_lay, t_lev, emis)
+        ro.close()
+        got = P.lw_fluxes(S.W0, S.DW, tau, np.zeros_like(tau), t_surf, t_lay, t_lev, emis)
+        assert S._rel(got[0], want[0]) <= 1e-12 and S._rel(got[1], want[1]) <= 1e-12
+    tau, omega, g = S._sw_optics(case, layers, n, np.random.default_rng(13))
+    alb = np.full(n, 0.35)
+    solar = np.full(n, 1./(S.DW*(n - 1)))
+    ro = R.RefOptics(fast, layers, rg)
+    ro.tau[:], ro.omega[:], ro.g[:] = tau, omega, g
+    want = R.sw_fluxes(fast, ro, 0.8, 0.5, alb, alb, 1361., solar)
+    ro.close()
+    got = P.sw_fluxes(omega, g, tau, 0.8, 0.5, alb, alb, 1361., solar)
+    assert S._rel(got[0], want[0]) <= 1e-12 and S._rel(got[1], want[1]) <= 1e-12
+
+
 def _golden_case():
     """tests/golden/reference_outputs.json (tools/make_golden_outputs.py): outputs of the
     compiled reference on a tiny seeded case, with the inputs regenerated from the seeds."""
