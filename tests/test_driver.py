@@ -11,7 +11,7 @@ import pytest
 from grtcode_b200 import column_io, synth
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-BIN = os.path.join(os.path.dirname(HERE), "grtcode_b200", "grt_lbl")
+BIN = os.environ.get("GRT_LBL_BIN", os.path.join(os.path.dirname(HERE), "grtcode_b200", "grt_lbl"))
 MOLS = (synth.H2O, synth.CO2, synth.O3)
 
 
