@@ -57,3 +57,25 @@ def test_product_arm_fails_loudly_without_a_gpu(built):
     assert proc.returncode != 0
     assert "no CUDA device visible" in proc.stderr
     assert not [l for l in proc.stdout.splitlines() if l.startswith("{")]
+
+
+def test_reference_arm_under_torchrun(built, tmp_path):
+    """Launched exactly as the driver launches it for N > 1 (torchrun, one process per GPU):
+    rank 0 alone prints the line, timed on every host core although torchrun exports
+    OMP_NUM_THREADS=1; the other rank exits 0 without output."""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("compiled reference not built (no /root/reference on this machine)")
+    env = dict(os.environ)
+    env.update({"GRT_CPU_WINDOWS": "1", "GRT_BENCH_DATA": str(tmp_path)})
+    env.pop("OMP_NUM_THREADS", None)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "bench.py"),
+           "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"]
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
