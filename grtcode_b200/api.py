@@ -113,6 +113,13 @@ def load():
                                           C.POINTER(Optics)]
     L.get_num_molecules.argtypes = [C.POINTER(GasOpticsStruct), C.POINTER(C.c_int)]
     L.gas_optics_stats.argtypes = [C.POINTER(GasOpticsStruct), C.POINTER(C.c_uint64)]
+    L.gas_optics_patch_counts.argtypes = [C.POINTER(GasOpticsStruct), C.POINTER(C.c_uint64)]
+    L.gas_optics_class_histogram.argtypes = [C.POINTER(GasOpticsStruct), C.POINTER(C.c_uint64)]
+    L.gas_optics_debug_records.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, C.c_uint64,
+                                           C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                           _dbl_p]
+    L.gas_optics_debug_line_order.argtypes = [C.POINTER(GasOpticsStruct), C.c_uint64,
+                                              C.POINTER(C.c_uint64)]
     L.rayleigh_scattering.argtypes = [C.POINTER(Optics), _dbl_p]
     L.create_longwave.argtypes = [C.POINTER(Longwave), C.c_int, C.POINTER(SpectralGrid),
                                   C.POINTER(C.c_int)]
@@ -334,6 +341,41 @@ class GasOptics:
         _check(self.L.gas_optics_stats(C.byref(self.s), out), "gas_optics_stats")
         return {"records": out[0], "samples": out[1], "launches": out[2], "lorentz": out[3],
                 "prep_ns": out[4], "wing_ns": out[5], "core_ns": out[6], "core_samples": out[7]}
+
+    def patch_counts(self) -> tuple[int, int]:
+        """(records the host re-evaluated with its libm in the last call, since creation)."""
+        out = (C.c_uint64*2)()
+        _check(self.L.gas_optics_patch_counts(C.byref(self.s), out), "gas_optics_patch_counts")
+        return int(out[0]), int(out[1])
+
+    def class_histogram(self) -> dict:
+        """Line-tile visits per wing-sweep line class of the last line_sample call (needs
+        GRT_CLASS_HIST=1 in the environment of that call)."""
+        out = (C.c_uint64*8)()
+        _check(self.L.gas_optics_class_histogram(C.byref(self.s), out),
+               "gas_optics_class_histogram")
+        names = ("fast", "region1", "far_edge", "near", "lorentz", "lorentz_edge")
+        d = {n: int(out[k]) for k, n in enumerate(names)}
+        d["tile_points"] = int(out[6])
+        return d
+
+    def debug_records(self, layer: int, first: int, count: int):
+        """(REPWID float32[count], Y float32[count], shifted centre float64[count]) of K1's
+        records of one layer, in device line order."""
+        rep = np.empty(count, dtype=np.float32)
+        y = np.empty(count, dtype=np.float32)
+        v = np.empty(count, dtype=np.float64)
+        _check(self.L.gas_optics_debug_records(
+            C.byref(self.s), layer, first, count, rep.ctypes.data_as(C.POINTER(C.c_float)),
+            y.ctypes.data_as(C.POINTER(C.c_float)), _dp(v)), "gas_optics_debug_records")
+        return rep, y, v
+
+    def debug_line_order(self, count: int) -> np.ndarray:
+        order = np.empty(count, dtype=np.uint64)
+        _check(self.L.gas_optics_debug_line_order(
+            C.byref(self.s), count, order.ctypes.data_as(C.POINTER(C.c_uint64))),
+            "gas_optics_debug_line_order")
+        return order
 
     def close(self):
         if self._live:

@@ -96,8 +96,6 @@ class ColumnEngine:
             for c, v in col.cia_ppmv.items():
                 go.set_ppmv("cia", c, v)
             go.optical_depth(col.p, col.t, part["gas"])
-            st = go.stats()
-            launches += st["launches"]
             h2d += 8*self.levels*(2 + 53 + 21 + 2)
             name = part["band"].name[:2]
             if name == "lw":
@@ -119,7 +117,10 @@ class ColumnEngine:
                                                col.tsi, part["solar"] if send else None,
                                                window=part["window"])
                 h2d += 2*8*part["n"] if send else 0
-            launches += 1
+            # the sweep kernels were only enqueued by calculate_optical_depth: their event
+            # times are read after the solver call, which synchronised the stream
+            st = go.stats()
+            launches += st["launches"] + 1
             out[name] = (up, dn, st)
         self.launches = launches
         self.h2d = h2d

@@ -97,7 +97,7 @@ struct PrepMeta
 
 
 // Q(T) exactly as grtcode_b200/host/tips.c:grt_tips_q evaluates it.
-__device__ double tips_q(double const *tab, int const tmin, int const nt, double const T)
+__host__ __device__ inline double tips_q(double const *tab, int const tmin, int const nt, double const T)
 {
     double t = T;
     double const lo = (double)tmin;
@@ -105,10 +105,42 @@ __device__ double tips_q(double const *tab, int const tmin, int const nt, double
     if (!(t >= lo)) t = lo;
     if (t >= hi) return tab[nt-1];
     int const it = (int)t;
-    double const f = __dsub_rn(t, (double)it);
+    // plain operators: this translation unit is compiled -fmad=false (device) and
+    // -ffp-contract=off (host), so nothing is fused on either side
+    double const f = t - (double)it;
     int const idx = it - tmin;
-    double const d = __dsub_rn(tab[idx+1], tab[idx]);
-    return __dadd_rn(tab[idx], __dmul_rn(f, d));
+    double const d = tab[idx+1] - tab[idx];
+    double const fd = f*d;
+    return tab[idx] + fd;
+}
+
+
+// Layer quantities of curtis_godson.c:25-120 and kernels.c:52-66, one function per value so
+// that the host can re-evaluate them for the few records it patches (see patch_near_ties).
+__host__ __device__ inline double layer_density(double const p0, double const p1)
+{
+    double dp = p0 - p1;
+    dp = dp >= 0. ? dp : -dp;
+    return 2.147822334314468e+25*dp;
+}
+
+__host__ __device__ inline double layer_mean(double const a0, double const a1)
+{
+    return 0.5*(a0 + a1);
+}
+
+__host__ __device__ inline double layer_partial_pressure(double const x0, double const x1,
+                                                         double const p0, double const p1)
+{
+    double const third = (double)(1.f/3.f);
+    double const sixth = (double)(1.f/6.f);
+    return third*(x0*p0 + x1*p1) + sixth*(x0*p1 + x1*p0);
+}
+
+__host__ __device__ inline double layer_species_density(double const n, double const x0,
+                                                        double const x1)
+{
+    return n*0.5*(x0 + x1);
 }
 
 
@@ -122,23 +154,19 @@ __global__ void column_prep_kernel(int const num_layers, ColumnInputs const in,
     int const levels = L + 1;
     double const p0 = in.p[i];
     double const p1 = in.p[i+1];
-    double dp = p0 - p1;
-    dp = dp >= 0. ? dp : -dp;
-    double const n = 2.147822334314468e+25*dp;
-    double const pavg = 0.5*(p0 + p1);
-    double const tavg = 0.5*(in.t[i] + in.t[i+1]);
+    double const n = layer_density(p0, p1);
+    double const pavg = layer_mean(p0, p1);
+    double const tavg = layer_mean(in.t[i], in.t[i+1]);
     out.n[i] = n;
     out.pavg[i] = pavg;
     out.tavg[i] = tavg;
-    double const third = (double)(1.f/3.f);
-    double const sixth = (double)(1.f/6.f);
     for (int s=0; s<meta.num_slots; ++s)
     {
         double const *x = in.x_mol + (size_t)(meta.slots[s].mol_id - 1)*levels;
         double const x0 = x[i];
         double const x1 = x[i+1];
-        out.ps[s*L+i] = third*(x0*p0 + x1*p1) + sixth*(x0*p1 + x1*p0);
-        out.ns[s*L+i] = n*0.5*(x0 + x1);
+        out.ps[s*L+i] = layer_partial_pressure(x0, x1, p0, p1);
+        out.ns[s*L+i] = layer_species_density(n, x0, x1);
         for (int k=0; k<meta.slots[s].num_iso; ++k)
         {
             double const *tab = meta.tips + ((size_t)s*kMaxIso + k)*meta.tips_nt;
@@ -179,17 +207,152 @@ struct PrepStats
     unsigned long long core;      // samples handled by the core kernel (upper bound)
 };
 
+// What one (line, layer) pair adds to PrepStats.
+struct RecordCounts
+{
+    unsigned long long samples;
+    unsigned long long core;
+    unsigned rec;
+    unsigned lor;
+};
 
-// K1: one thread per (line, layer).  Formulas and operation order of
+// Base parameters of one line and the layer quantities of its molecule.
+struct LineInputs
+{
+    double v0, delta, s0, en, nair, yair, yself;   // parse_HITRAN_file.h:28-44
+    double T, P, Ps, Ns, qinv, mass;
+};
+
+// Records K1 flags for re-evaluation on the host (see patch_near_ties): the product
+// REPWID*gamma lies within kTieUlps double ulps of a float rounding boundary, so a last-bit
+// difference between this GPU's pow() and the host libm's -- the one the reference calls --
+// could round Y = (float)(REPWID*gamma) (RFM_voigt.c:95) the other way and move every sample
+// of the line by 6e-8 relative.  libdevice pow is within 2 ulp and glibc within 1 ulp of the
+// true value; the multiplications that follow add one rounding each.
+constexpr unsigned kTieUlps = 64;
+constexpr unsigned kTieInline = 254;       // flagged indices copied back with the counter
+
+struct TieList
+{
+    unsigned count;
+    unsigned pad;
+    unsigned long long idx[kTieInline];    // layer*num_lines + line
+};
+
+__host__ __device__ inline bool near_float_tie(double const g)
+{
+#ifdef __CUDA_ARCH__
+    unsigned const lo = (unsigned)__double2loint(g) & 0x1fffffffu;
+#else
+    unsigned long long bits;
+    memcpy(&bits, &g, sizeof(bits));
+    unsigned const lo = (unsigned)bits & 0x1fffffffu;
+#endif
+    // the float rounding of a normal double is decided by its low 29 mantissa bits
+    // against the half-way pattern 0x10000000
+    unsigned const d = lo >= 0x10000000u ? lo - 0x10000000u : 0x10000000u - lo;
+    return d <= kTieUlps;
+}
+
+// One 64-byte record from the line's base parameters: formulas and operation order of
 // calc_line_centers / calc_line_strengths / calc_lorentz_hw / calc_doppler_hw
 // (kernels.c:34-131) followed by the per-line part of rfm_voigt_line_shape
 // (RFM_voigt.c:94-109) and the window of calc_optical_depth_line_sample
-// (kernels.c:417,431-437).
+// (kernels.c:417,431-437).  The three transcendental values come from the caller:
+// ex_en = EXP(c2*en/T), ex_v = EXP(c2*v0/T), pw = POW(296.f/T, n) -- libdevice's in K1,
+// the host libm's in patch_near_ties.  Returns true when Y sits near a float tie.
+__host__ __device__ inline bool build_record(LineInputs const &in, double const ex_en,
+                                             double const ex_v, double const pw, double const w0,
+                                             double const wres, uint64_t const nw,
+                                             int const fsteps, LineRec &r, RecordCounts &cnt)
+{
+    double const v = in.v0 + in.delta*in.P;
+    double const S = in.s0*ex_en*(1. - ex_v)*in.qinv;
+    double const gamma = pw*(in.yair*(in.P - in.Ps) + in.yself*in.Ps);
+    double const kb = 1.380658E-16;
+    double const cl = 2.99792458E10;
+    double const alpha = (double)0.83255461115f*v*sqrt((2.*kb*in.T)/(in.mass*cl*cl));
+
+    float const repwid = (float)((double)kSqrln2/alpha);
+    double const yd = (double)repwid*gamma;
+    float const y = (float)yd;
+    r.v = v;
+    r.repwid = repwid;
+    r.y = y;
+    double const sn = S*in.Ns;
+    float const yq = y*y;
+    r.yq = yq;
+    r.yrrtpi = y*kRsqrpi;
+    r.a0 = (float)((double)yq + 0.5);                 // RFM_voigt.c:177-179
+    r.d0 = r.a0*r.a0;
+    r.d2 = (float)((double)(yq + yq) - 1.0);
+    voigt_limits(y, &r.xlim0, &r.xlim1);
+    // Grid points farther than hw0 from fc have |x| >= XLIM0: |w_f - v| >=
+    // (|f - fc| - 1/2) wres, and 1.5 grid steps of slack cover the float rounding of x.
+    double const step = (double)repwid*wres;          // x per grid point
+    double const h0 = ceil((double)r.xlim0/step) + 2.;
+    // Conservative 16-bit companions for chunk classification near the centre: every
+    // point with |f - fc| < hw0in has |x| < XLIM0, every point with |f - fc| > hw1
+    // has |x| >= XLIM1 (so chunks between them are pure Humlicek region 1).
+    double h0in = floor((double)r.xlim0/step) - 2.;
+    double h1 = ceil((double)r.xlim1/step) + 2.;
+    if (!(h0in >= 0.)) h0in = 0.;
+    if (!(h0in <= 65535.)) h0in = 65535.;
+    if (!(h1 >= 0.)) h1 = 65535.;
+    if (!(h1 <= 65535.)) h1 = 65535.;
+    r.hw1_hw0in = (unsigned)h1 | ((unsigned)h0in << 16);
+    if (y >= kLorentzY)
+    {
+        r.hw0 = kHwLorentz;
+        r.c = sn*(double)(repwid*y)/3.14159265358979323846;
+    }
+    else
+    {
+        r.hw0 = h0 < (double)kHwMax ? (int)h0 : kHwMax;
+        r.c = sn*(double)(kRsqrpi*repwid);
+        // Vanishing (or NaN) Y: far-wing values may be zero or subnormal; let
+        // the line-core kernel evaluate the whole window with the full routine.
+        if (!(y >= 1e-18f)) r.hw0 = kHwCoreOnly;
+    }
+    cnt.samples = 0;
+    cnt.core = 0;
+    cnt.rec = 0;
+    cnt.lor = 0;
+    double const fcd = floor((2.*((v - w0)/wres) + 1.)/2.);
+    if (fcd >= 0. && fcd < (double)nw)
+    {
+        int const fc = (int)fcd;
+        r.fc = fc;
+        int const s = fc - fsteps < 0 ? 0 : fc - fsteps;
+        int const e = (uint64_t)(fc + fsteps) >= nw ? (int)(nw - 1) : fc + fsteps;
+        cnt.samples = (unsigned long long)(e - s + 1);
+        cnt.rec = 1;
+        if (y >= kLorentzY)
+        {
+            cnt.lor = 1;
+        }
+        else
+        {
+            double const h = (double)r.xlim1/((double)repwid*wres);
+            cnt.core = (unsigned long long)fmin(2.*h + 1., (double)(e - s + 1));
+            if (r.hw0 == kHwCoreOnly) cnt.core = cnt.samples;
+        }
+    }
+    else
+    {
+        r.fc = kSkip;
+    }
+    return near_float_tie(yd);
+}
+
+
+// K1: one thread per (line, layer).
 __global__ void __launch_bounds__(256)
 line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay,
                  PrepMeta const meta, double const w0, double const wres, uint64_t const nw,
                  int const fsteps, LineRec *recs, PrepStats *stats, double *vkey,
-                 unsigned *vidx)
+                 unsigned *vidx, TieList *ties, unsigned long long *tie_overflow,
+                 unsigned const tie_capacity)
 {
     uint64_t const j = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     int const i = blockIdx.y;
@@ -205,92 +368,42 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         int iso = si & 0xff;
         if (iso < 1) iso = 1;
         if (iso > kMaxIso) iso = kMaxIso;
-        double const T = lay.tavg[i];
-        double const P = lay.pavg[i];
-        double const Ps = lay.ps[slot*L+i];
-        double const Ns = lay.ns[slot*L+i];
-        double const q = lay.qinv[((size_t)slot*L + i)*kMaxIso + iso - 1];
-        double const v0 = lines.v0[j];
-        double const v = v0 + lines.delta[j]*P;
+        LineInputs in;
+        in.T = lay.tavg[i];
+        in.P = lay.pavg[i];
+        in.Ps = lay.ps[slot*L+i];
+        in.Ns = lay.ns[slot*L+i];
+        in.qinv = lay.qinv[((size_t)slot*L + i)*kMaxIso + iso - 1];
+        in.mass = meta.slots[slot].mass;
+        in.v0 = lines.v0[j];
+        in.delta = lines.delta[j];
+        in.s0 = lines.s0[j];
+        in.en = lines.en[j];
+        in.nair = lines.nair[j];
+        in.yair = lines.yair[j];
+        in.yself = lines.yself[j];
         double const c2 = (double)(-1.4387686f);
-        double const S = lines.s0[j]*exp(c2*lines.en[j]/T)*(1. - exp(c2*v0/T))*q;
-        double const gamma = pow(296./T, lines.nair[j])*(lines.yair[j]*(P - Ps) + lines.yself[j]*Ps);
-        double const kb = 1.380658E-16;
-        double const cl = 2.99792458E10;
-        double const m = meta.slots[slot].mass;
-        double const alpha = (double)0.83255461115f*v*sqrt((2.*kb*T)/(m*cl*cl));
-
-        float const repwid = (float)((double)kSqrln2/alpha);
-        float const y = (float)((double)repwid*gamma);
         LineRec r;
-        r.v = v;
-        r.repwid = repwid;
-        r.y = y;
-        double const sn = S*Ns;
-        float const yq = y*y;
-        r.yq = yq;
-        r.yrrtpi = y*kRsqrpi;
-        r.a0 = (float)((double)yq + 0.5);                 // RFM_voigt.c:177-179
-        r.d0 = r.a0*r.a0;
-        r.d2 = (float)((double)(yq + yq) - 1.0);
-        voigt_limits(y, &r.xlim0, &r.xlim1);
-        // Grid points farther than hw0 from fc have |x| >= XLIM0: |w_f - v| >=
-        // (|f - fc| - 1/2) wres, and 1.5 grid steps of slack cover the float rounding of x.
-        double const step = (double)repwid*wres;          // x per grid point
-        double const h0 = ceil((double)r.xlim0/step) + 2.;
-        // Conservative 16-bit companions for chunk classification near the centre: every
-        // point with |f - fc| < hw0in has |x| < XLIM0, every point with |f - fc| > hw1
-        // has |x| >= XLIM1 (so chunks between them are pure Humlicek region 1).
-        double h0in = floor((double)r.xlim0/step) - 2.;
-        double h1 = ceil((double)r.xlim1/step) + 2.;
-        if (!(h0in >= 0.)) h0in = 0.;
-        if (!(h0in <= 65535.)) h0in = 65535.;
-        if (!(h1 >= 0.)) h1 = 65535.;
-        if (!(h1 <= 65535.)) h1 = 65535.;
-        r.hw1_hw0in = (unsigned)h1 | ((unsigned)h0in << 16);
-        if (y >= kLorentzY)
+        RecordCounts cnt;
+        bool const tie = build_record(in, exp(c2*in.en/in.T), exp(c2*in.v0/in.T),
+                                      pow(296./in.T, in.nair), w0, wres, nw, fsteps, r, cnt);
+        my_samples = cnt.samples;
+        my_core = cnt.core;
+        my_rec = cnt.rec;
+        my_lor = cnt.lor;
+        size_t const gi = (size_t)i*lines.num_lines + j;
+        recs[gi] = r;
+        if (tie && ties != nullptr && r.fc != kSkip)
         {
-            r.hw0 = kHwLorentz;
-            r.c = sn*(double)(repwid*y)/3.14159265358979323846;
+            unsigned const k = atomicAdd(&ties->count, 1u);
+            if (k < kTieInline) ties->idx[k] = gi;
+            else if (k - kTieInline < tie_capacity) tie_overflow[k - kTieInline] = gi;
         }
-        else
-        {
-            r.hw0 = h0 < (double)kHwMax ? (int)h0 : kHwMax;
-            r.c = sn*(double)(kRsqrpi*repwid);
-            // Vanishing (or NaN) Y: far-wing values may be zero or subnormal; let
-            // the line-core kernel evaluate the whole window with the full routine.
-            if (!(y >= 1e-18f)) r.hw0 = kHwCoreOnly;
-        }
-        double const fcd = floor((2.*((v - w0)/wres) + 1.)/2.);
-        if (fcd >= 0. && fcd < (double)nw)
-        {
-            int const fc = (int)fcd;
-            r.fc = fc;
-            int const s = fc - fsteps < 0 ? 0 : fc - fsteps;
-            int const e = (uint64_t)(fc + fsteps) >= nw ? (int)(nw - 1) : fc + fsteps;
-            my_samples = (unsigned long long)(e - s + 1);
-            my_rec = 1;
-            if (y >= kLorentzY)
-            {
-                my_lor = 1;
-            }
-            else
-            {
-                double const h = (double)r.xlim1/((double)repwid*wres);
-                my_core = (unsigned long long)fmin(2.*h + 1., (double)(e - s + 1));
-                if (r.hw0 == kHwCoreOnly) my_core = my_samples;
-            }
-        }
-        else
-        {
-            r.fc = kSkip;
-        }
-        recs[(size_t)i*lines.num_lines + j] = r;
         if (vkey != nullptr)
         {
             // sort keys of the binned methods (sort_lines, kernels.c:135-172)
-            vkey[(size_t)i*lines.num_lines + j] = v;
-            vidx[(size_t)i*lines.num_lines + j] = (unsigned)((size_t)i*lines.num_lines + j);
+            vkey[gi] = r.v;
+            vidx[gi] = (unsigned)gi;
         }
     }
     // Block-level statistics (bench bookkeeping only).
@@ -321,6 +434,20 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
     }
 }
 
+// Patched records from the host replace K1's.
+struct RecordPatch
+{
+    unsigned long long idx;
+    unsigned long long pad;
+    LineRec rec;
+};
+
+__global__ void patch_records_kernel(RecordPatch const *patch, unsigned const count, LineRec *recs)
+{
+    unsigned const k = blockIdx.x*blockDim.x + threadIdx.x;
+    if (k < count) recs[patch[k].idx] = patch[k].rec;
+}
+
 
 }  // namespace grt
 
@@ -342,6 +469,9 @@ struct grt_gas
     std::vector<double> h_v0, h_delta, h_s0, h_en, h_nair, h_yair, h_yself;
     std::vector<uint16_t> h_slotiso;
     std::vector<double> h_sorted_v0;     // centres in device order (tile cost estimate)
+    std::vector<double> h_packed;        // the 7 base-parameter arrays in device order
+    std::vector<uint16_t> h_si;          // slot << 8 | iso in device order
+    std::vector<uint64_t> h_order;       // device position -> upload index
     bool dirty = true;
     double max_abs_delta = 0.;
 
@@ -389,7 +519,27 @@ struct grt_gas
     std::vector<double *> owned_tables;
     uint64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool timings_pending = false;        // ev[1..3] recorded, durations not read yet
+    int last_method = 2;
+
+    // near-tie records re-evaluated with the host libm (patch_near_ties)
+    TieList *d_ties = nullptr;
+    unsigned long long *d_tie_overflow = nullptr;
+    struct HostBlock                     // pinned: what the one mid-call sync brings back
+    {
+        TieList ties;
+        PrepStats stats;
+    } *h_block = nullptr;
+    RecordPatch *h_patch = nullptr;      // pinned
+    RecordPatch *d_patch = nullptr;
+    unsigned long long *h_tie_overflow = nullptr;   // pinned
+    uint64_t patched_total = 0;          // records patched since creation
+    uint64_t patched_last = 0;           // ... by the last call
+    unsigned long long *d_class_counts = nullptr;   // GRT_CLASS_HIST=1: visits per line class
+    unsigned long long h_class_counts[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
+
+constexpr unsigned kTieCapacity = 1u << 16;   // flagged records beyond the inline list
 
 
 static int upload_table(grt_gas *g, double const *host, double const **dev_out)
@@ -490,10 +640,79 @@ static int finalize_lines(grt_gas *g, int const method)
                                  cudaMemcpyHostToDevice, g->stream));
     }
     GRT_CUDA(cudaStreamSynchronize(g->stream));
+    g->h_packed.swap(packed);
+    g->h_order.swap(order);
+    g->h_si.swap(si);
     g->num_lines = n;
     g->meta.tips = g->d_tips;
     g->dirty = false;
     g->tiles_pts = 0;
+    return 0;
+}
+
+
+// The records K1 flagged (Y within a few double ulps of a float rounding boundary) are
+// rebuilt here with the HOST libm's exp and pow -- the functions the reference itself calls
+// (grtcode_config.h:25-47) -- and written over K1's.  Everything else in a record is IEEE
+// arithmetic that the GPU and the host round identically, so after the patch Y, and with it
+// every float the line shape is computed from, carries the bits the reference computes on
+// this machine.  A handful of records per column (probability ~2.4e-7 per record).
+static int patch_near_ties(grt_gas *g, unsigned const count, double const *p_atm,
+                           double const *t, double const *x_mol)
+{
+    cudaStream_t const st = g->stream;
+    uint64_t const N = g->num_lines;
+    int const levels = g->num_levels;
+    unsigned const extra = count > kTieInline ? count - kTieInline : 0u;
+    if (extra > kTieCapacity) return fail("too many near-tie records (%u)", count);
+    if (extra > 0)
+    {
+        GRT_CUDA(cudaMemcpyAsync(g->h_tie_overflow, g->d_tie_overflow,
+                                 sizeof(unsigned long long)*extra, cudaMemcpyDeviceToHost, st));
+        GRT_CUDA(cudaStreamSynchronize(st));
+    }
+    double const c2 = (double)(-1.4387686f);
+    int const fsteps = (int)std::ceil((double)25.f/g->dw);
+    double const *base = g->h_packed.data();
+    for (unsigned k=0; k<count; ++k)
+    {
+        unsigned long long const gi = k < kTieInline ? g->h_block->ties.idx[k]
+                                                     : g->h_tie_overflow[k - kTieInline];
+        int const i = (int)(gi/N);
+        uint64_t const j = gi - (uint64_t)i*N;
+        unsigned const si = g->h_si[j];
+        int const slot = (int)(si >> 8);
+        int iso = (int)(si & 0xff);
+        if (iso < 1) iso = 1;
+        if (iso > kMaxIso) iso = kMaxIso;
+        double const *x = x_mol + (size_t)(g->meta.slots[slot].mol_id - 1)*levels;
+        double const p0 = p_atm[i], p1 = p_atm[i+1];
+        LineInputs in;
+        in.T = layer_mean(t[i], t[i+1]);
+        in.P = layer_mean(p0, p1);
+        in.Ps = layer_partial_pressure(x[i], x[i+1], p0, p1);
+        in.Ns = layer_species_density(layer_density(p0, p1), x[i], x[i+1]);
+        double const *tab = g->h_tips.data() + ((size_t)slot*kMaxIso + iso - 1)*g->meta.tips_nt;
+        in.qinv = 1./tips_q(tab, g->meta.tips_tmin, g->meta.tips_nt, in.T);
+        in.mass = g->meta.slots[slot].mass;
+        in.v0 = base[0*N+j];
+        in.delta = base[1*N+j];
+        in.s0 = base[2*N+j];
+        in.en = base[3*N+j];
+        in.nair = base[4*N+j];
+        in.yair = base[5*N+j];
+        in.yself = base[6*N+j];
+        RecordPatch &out = g->h_patch[k];
+        RecordCounts cnt;
+        out.idx = gi;
+        out.pad = 0;
+        build_record(in, std::exp(c2*in.en/in.T), std::exp(c2*in.v0/in.T),
+                     std::pow(296./in.T, in.nair), g->w0, g->dw, g->nw, fsteps, out.rec, cnt);
+    }
+    GRT_CUDA(cudaMemcpyAsync(g->d_patch, g->h_patch, sizeof(RecordPatch)*count,
+                             cudaMemcpyHostToDevice, st));
+    patch_records_kernel<<<(count + 127)/128, 128, 0, st>>>(g->d_patch, count, g->d_recs);
+    GRT_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -561,13 +780,16 @@ template <int PTS, int NL, bool TBL, int LN>
 static int launch_wing_impl(SweepParams const &sp, int const sms, cudaStream_t const st)
 {
     using Cfg = SweepConfig<PTS, NL, LN>;
-    static bool configured = false;
-    if (!configured)
+    // the attribute is per device (a process may drive several GPUs): one flag per device id
+    static bool configured[64] = {};
+    int dev = 0;
+    GRT_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev])
     {
         GRT_CUDA(cudaFuncSetAttribute(wing_sweep_kernel<PTS, NL, TBL, LN>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       Cfg::kRingBytes + (TBL ? kMaxTableBytes : 0)));
-        configured = true;
+        if (dev >= 0 && dev < 64) configured[dev] = true;
     }
     int const smem = Cfg::kRingBytes + (TBL ? 8*sweep_table_entries<PTS, LN>(sp.fsteps) : 0);
     int per_sm = 0;
@@ -789,21 +1011,13 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
     GRT_CUDA(cudaGetLastError());
     ++launches;
     GRT_CUDA(cudaEventRecord(g->ev[3], st));
-    PrepStats hs;
-    unsigned long long evals = 0;
-    GRT_CUDA(cudaMemcpyAsync(&hs, g->d_stats, sizeof(PrepStats), cudaMemcpyDeviceToHost, st));
-    GRT_CUDA(cudaMemcpyAsync(&evals, g->d_evals, sizeof(evals), cudaMemcpyDeviceToHost, st));
-    GRT_CUDA(cudaStreamSynchronize(st));
-    float ms[3] = {0.f, 0.f, 0.f};
-    for (int k=0; k<3; ++k) GRT_CUDA(cudaEventElapsedTime(&ms[k], g->ev[k], g->ev[k+1]));
+    PrepStats const &hs = g->h_block->stats;
     g->stats[0] = (uint64_t)N*(uint64_t)L;
-    g->stats[1] = evals;
+    g->stats[1] = 0;                 // evaluations: read with the timings (grt_gas_last_stats)
     g->stats[2] = (uint64_t)launches;
     g->stats[3] = hs.lorentz;
-    g->stats[4] = (uint64_t)(ms[0]*1e6f);   // K0 + K1 [ns]
-    g->stats[5] = (uint64_t)(ms[2]*1e6f);   // bin gather [ns]
-    g->stats[6] = (uint64_t)(ms[1]*1e6f);   // sort [ns]
     g->stats[7] = 0;
+    g->timings_pending = true;
     return 0;
 }
 
@@ -844,6 +1058,12 @@ int grt_gas_create(grt_gas **gas, int device, int num_levels, double w0, double 
     GRT_CUDA(cudaMalloc(&g->d_inputs, sizeof(double)*input_doubles));
     GRT_CUDA(cudaMalloc(&g->d_stats, sizeof(PrepStats)));
     GRT_CUDA(cudaMalloc(&g->d_work_counter, sizeof(unsigned int)));
+    GRT_CUDA(cudaMalloc(&g->d_ties, sizeof(TieList)));
+    GRT_CUDA(cudaMalloc(&g->d_tie_overflow, sizeof(unsigned long long)*kTieCapacity));
+    GRT_CUDA(cudaMalloc(&g->d_patch, sizeof(RecordPatch)*(kTieInline + kTieCapacity)));
+    GRT_CUDA(cudaMallocHost(&g->h_block, sizeof(*g->h_block)));
+    GRT_CUDA(cudaMallocHost(&g->h_patch, sizeof(RecordPatch)*(kTieInline + kTieCapacity)));
+    GRT_CUDA(cudaMallocHost(&g->h_tie_overflow, sizeof(unsigned long long)*kTieCapacity));
     for (int k=0; k<5; ++k) GRT_CUDA(cudaEventCreate(&g->ev[k]));
     *gas = g;
     return 0;
@@ -864,6 +1084,9 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_stats);
     cudaFree(g->d_tile_order);
     cudaFree(g->d_work_counter);
+    cudaFree(g->d_ties); cudaFree(g->d_tie_overflow); cudaFree(g->d_patch);
+    cudaFree(g->d_class_counts);
+    cudaFreeHost(g->h_block); cudaFreeHost(g->h_patch); cudaFreeHost(g->h_tie_overflow);
     cudaFree(g->d_vkey); cudaFree(g->d_vsorted); cudaFree(g->d_vidx); cudaFree(g->d_perm);
     cudaFree(g->d_sorted_recs);
     cudaFree(g->d_seg_begin); cudaFree(g->d_seg_end); cudaFree(g->d_segkey); cudaFree(g->d_wing_a); cudaFree(g->d_wing_b); cudaFree(g->d_sort_temp); cudaFree(g->d_evals); cudaFree(g->d_ranges);
@@ -1025,6 +1248,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     uint64_t const N = g->num_lines;
     int const fsteps = (int)std::ceil((double)25.f/g->dw);
     GRT_CUDA(cudaMemsetAsync(g->d_stats, 0, sizeof(PrepStats), st));
+    GRT_CUDA(cudaMemsetAsync(g->d_ties, 0, 2*sizeof(unsigned), st));
     if (N > 0)
     {
         size_t const need = (size_t)N*L;
@@ -1066,12 +1290,34 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
             GRT_CUDA(cudaMalloc(&g->d_wing_b, sizeof(float4)*need));
             g->binned_capacity = need;
         }
+        bool patch = true;
+        if (char const *env = getenv("GRT_K1_PATCH")) patch = env[0] != '0';
         line_prep_kernel<<<grid, 256, 0, st>>>(lv, L, lay, g->meta, g->w0, g->dw, g->nw, fsteps,
                                                g->d_recs, g->d_stats,
                                                method != 2 ? g->d_vkey : nullptr,
-                                               method != 2 ? g->d_vidx : nullptr);
+                                               method != 2 ? g->d_vidx : nullptr,
+                                               patch ? g->d_ties : nullptr, g->d_tie_overflow,
+                                               kTieCapacity);
         ++launches;
     }
+    // The one host synchronisation of the call: K1's counters and its list of near-tie
+    // records come back; the sweep kernels below are only enqueued (later calls are ordered
+    // behind them on the library stream, and every call that hands data to the host
+    // synchronises).
+    GRT_CUDA(cudaMemcpyAsync(&g->h_block->ties, g->d_ties, sizeof(TieList), cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaMemcpyAsync(&g->h_block->stats, g->d_stats, sizeof(PrepStats),
+                             cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    g->patched_last = 0;
+    if (N > 0 && g->h_block->ties.count > 0)
+    {
+        GRT_TRY(patch_near_ties(g, g->h_block->ties.count, p_atm, t, x_mol));
+        g->patched_last = g->h_block->ties.count;
+        g->patched_total += g->patched_last;
+        ++launches;
+    }
+    g->last_method = method;
+    g->stats[2] = 0;
     if (method != 2)
     {
         return binned_optical_depth(g, method, lay, tau_dev, launches);
@@ -1094,7 +1340,6 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     sp.tau = tau_dev;
     sp.core_order = g->d_core_order;
     if (char const *env = getenv("GRT_CORE_ORDER")) { if (env[0] == '0') sp.core_order = nullptr; }
-
     // Points per thread (PTS): LN*PTS points per warp tile; NL layers per work item.  Wider
     // tiles amortise the per-line work better; narrower ones waste fewer lanes at window
     // ends and balance better (a window is 5001 points at 0.01 cm-1 but only 501 at 0.1,
@@ -1160,27 +1405,119 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
         ++launches;
     }
     GRT_CUDA(cudaEventRecord(g->ev[3], st));
+    if (char const *env = getenv("GRT_CLASS_HIST"))
+    {
+        if (env[0] == '1' && N > 0)
+        {
+            if (g->d_class_counts == nullptr)
+            {
+                GRT_CUDA(cudaMalloc(&g->d_class_counts, 8*sizeof(unsigned long long)));
+            }
+            GRT_CUDA(cudaMemsetAsync(g->d_class_counts, 0, 8*sizeof(unsigned long long), st));
+            dim3 grid((unsigned)((N + 255)/256), (unsigned)L);
+            class_histogram_kernel<<<grid, 256, 0, st>>>(sp, ln*pts, g->d_class_counts);
+        }
+    }
     GRT_CUDA(cudaGetLastError());
-    PrepStats hs;
-    GRT_CUDA(cudaMemcpyAsync(&hs, g->d_stats, sizeof(PrepStats), cudaMemcpyDeviceToHost, st));
-    GRT_CUDA(cudaStreamSynchronize(st));
+    PrepStats const &hs = g->h_block->stats;
     g->stats[0] = hs.records;
     g->stats[1] = hs.samples;
     g->stats[2] = (uint64_t)launches;
     g->stats[3] = hs.lorentz;
-    float ms[3] = {0.f, 0.f, 0.f};
-    for (int k=0; k<3; ++k) GRT_CUDA(cudaEventElapsedTime(&ms[k], g->ev[k], g->ev[k+1]));
-    g->stats[4] = (uint64_t)(ms[0]*1e6f);   // K0 + K1 [ns]
-    g->stats[5] = (uint64_t)(ms[1]*1e6f);   // K3 wing sweep [ns]
-    g->stats[6] = (uint64_t)(ms[2]*1e6f);   // K3c core sweep [ns]
     g->stats[7] = hs.core;
+    g->timings_pending = true;     // stats[4..6] are read from the events on demand
     return 0;
 }
 
-int grt_gas_last_stats(grt_gas const *g, uint64_t out[8])
+int grt_gas_last_stats(grt_gas *g, uint64_t out[8])
 {
     if (g == nullptr || out == nullptr) return fail("null argument");
+    if (g->timings_pending)
+    {
+        // waits for the kernels of the last grt_gas_optical_depth call
+        GRT_CUDA(cudaSetDevice(g->device));
+        GRT_CUDA(cudaEventSynchronize(g->ev[3]));
+        float ms[3] = {0.f, 0.f, 0.f};
+        for (int k=0; k<3; ++k) GRT_CUDA(cudaEventElapsedTime(&ms[k], g->ev[k], g->ev[k+1]));
+        g->stats[4] = (uint64_t)(ms[0]*1e6f);       // K0 + K1 (+ patch) [ns]
+        if (g->last_method == 2)
+        {
+            g->stats[5] = (uint64_t)(ms[1]*1e6f);   // K3 wing sweep [ns]
+            g->stats[6] = (uint64_t)(ms[2]*1e6f);   // K3c core sweep [ns]
+        }
+        else
+        {
+            g->stats[5] = (uint64_t)(ms[2]*1e6f);   // bin gather [ns]
+            g->stats[6] = (uint64_t)(ms[1]*1e6f);   // sort [ns]
+            unsigned long long evals = 0;
+            GRT_CUDA(cudaMemcpy(&evals, g->d_evals, sizeof(evals), cudaMemcpyDeviceToHost));
+            g->stats[1] = evals;
+        }
+        g->timings_pending = false;
+    }
     for (int k=0; k<8; ++k) out[k] = g->stats[k];
+    return 0;
+}
+
+/* Records the host re-evaluated with its own libm because Y sat near a float rounding
+ * boundary: out[0] = by the last grt_gas_optical_depth call, out[1] = since creation. */
+int grt_gas_patch_counts(grt_gas const *g, uint64_t out[2])
+{
+    if (g == nullptr || out == nullptr) return fail("null argument");
+    out[0] = g->patched_last;
+    out[1] = g->patched_total;
+    return 0;
+}
+
+/* Diagnostic read-back of K1's records for one layer: REPWID and Y (RFM_voigt.c:94-95) and
+ * the shifted centre of records [first, first + count) in the device line order
+ * (line_sample: merged, sorted by unshifted centre, ties in upload order; binned methods:
+ * molecule-major in upload order). */
+int grt_gas_debug_records(grt_gas *g, int layer, uint64_t first, uint64_t count, float *repwid,
+                          float *y, double *centre)
+{
+    if (g == nullptr) return fail("null gas handle");
+    if (layer < 0 || layer >= g->num_layers || first + count > g->num_lines)
+    {
+        return fail("record range outside the line list");
+    }
+    GRT_CUDA(cudaSetDevice(g->device));
+    GRT_CUDA(cudaStreamSynchronize(g->stream));
+    std::vector<LineRec> h((size_t)count);
+    GRT_CUDA(cudaMemcpy(h.data(), g->d_recs + (size_t)layer*g->num_lines + first,
+                        sizeof(LineRec)*count, cudaMemcpyDeviceToHost));
+    for (uint64_t k=0; k<count; ++k)
+    {
+        if (repwid) repwid[k] = h[k].repwid;
+        if (y) y[k] = h[k].y;
+        if (centre) centre[k] = h[k].v;
+    }
+    return 0;
+}
+
+/* Device order of the uploaded lines: order[k] = index, in upload order over all
+ * add_molecule calls, of the line at device position k. */
+int grt_gas_debug_line_order(grt_gas const *g, uint64_t count, uint64_t *order)
+{
+    if (g == nullptr || order == nullptr) return fail("null argument");
+    if (count != g->h_order.size()) return fail("line count mismatch");
+    for (uint64_t k=0; k<count; ++k) order[k] = g->h_order[k];
+    return 0;
+}
+
+/* GRT_CLASS_HIST=1 in the environment: line-tile visits of the wing sweep per line class
+ * during the last line_sample call: out[0..5] = fast, region 1, far edge, near, Lorentz
+ * (covered), Lorentz (edge); out[6] = points per tile; out[7] unused. */
+int grt_gas_class_histogram(grt_gas *g, uint64_t out[8])
+{
+    if (g == nullptr || out == nullptr) return fail("null argument");
+    if (g->d_class_counts == nullptr) return fail("class histogram not enabled (GRT_CLASS_HIST=1)");
+    GRT_CUDA(cudaSetDevice(g->device));
+    GRT_CUDA(cudaStreamSynchronize(g->stream));
+    GRT_CUDA(cudaMemcpy(g->h_class_counts, g->d_class_counts, sizeof(g->h_class_counts),
+                        cudaMemcpyDeviceToHost));
+    for (int k=0; k<8; ++k) out[k] = g->h_class_counts[k];
+    out[6] = (uint64_t)g->tiles_pts;
     return 0;
 }
 

@@ -634,6 +634,29 @@ __device__ unsigned long long g_dbg_visits[kTmCount];
 #define GRT_TM_END(slot, visits) do {} while (0)
 #endif
 
+// The class of one record against one tile [warp_base, warp_last] (see LineClass).
+__device__ __forceinline__ int classify_line(int const fc, int const hw0, unsigned const hh,
+                                             int const warp_base, int const warp_last,
+                                             int const fsteps, int const nw)
+{
+    bool const hit = (fc != kSkip) && (fc + fsteps >= warp_base) &&
+                     (fc - fsteps <= warp_last) && (hw0 != kHwCoreOnly);
+    if (!hit) return kClsNone;
+    int const s = max(fc - fsteps, 0);
+    int const e = min(fc + fsteps, nw - 1);
+    bool const covered = (s <= warp_base) && (e >= warp_last);
+    // nearest and farthest tile point from the line centre, in grid steps
+    int const dlo = max(max(warp_base - fc, fc - warp_last), 0);
+    int const dhi = max(fc - warp_base, warp_last - fc);
+    bool const far = (hw0 >= 0) && (dlo > hw0);
+    if (hw0 == kHwLorentz) return covered ? kClsLorentzFull : kClsLorentzEdge;
+    if (far) return covered ? kClsFast : kClsFarEdge;
+    int const hw1 = (int)(hh & 0xffffu);
+    int const hw0in = (int)(hh >> 16);
+    bool const r1 = covered && (dhi < hw0in) && (dlo > hw1) && (hw1 < 65535);
+    return r1 ? kClsR1 : kClsNear;
+}
+
 // One staged batch (cnt <= 32 records of one layer) against the warp's tile.  Lane b
 // classifies record b; the classes are then walked as bit masks, the dominant one
 // (kClsFast) with the next record's vectors prefetched while the current one computes.
@@ -646,36 +669,8 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
     int cls = kClsNone;
     if (t.lane < cnt)
     {
-        int const fc = stage[t.lane].fc;
-        int const hw0 = stage[t.lane].hw0;
-        bool const hit = (fc != kSkip) && (fc + t.fsteps >= t.warp_base) &&
-                         (fc - t.fsteps <= t.warp_last) && (hw0 != kHwCoreOnly);
-        if (hit)
-        {
-            int const s = max(fc - t.fsteps, 0);
-            int const e = min(fc + t.fsteps, t.nw - 1);
-            bool const covered = (s <= t.warp_base) && (e >= t.warp_last);
-            // nearest and farthest tile point from the line centre, in grid steps
-            int const dlo = max(max(t.warp_base - fc, fc - t.warp_last), 0);
-            int const dhi = max(fc - t.warp_base, t.warp_last - fc);
-            bool const far = (hw0 >= 0) && (dlo > hw0);
-            if (hw0 == kHwLorentz)
-            {
-                cls = covered ? kClsLorentzFull : kClsLorentzEdge;
-            }
-            else if (far)
-            {
-                cls = covered ? kClsFast : kClsFarEdge;
-            }
-            else
-            {
-                unsigned const hh = stage[t.lane].hw1_hw0in;
-                int const hw1 = (int)(hh & 0xffffu);
-                int const hw0in = (int)(hh >> 16);
-                bool const r1 = covered && (dhi < hw0in) && (dlo > hw1) && (hw1 < 65535);
-                cls = r1 ? kClsR1 : kClsNear;
-            }
-        }
+        cls = classify_line(stage[t.lane].fc, stage[t.lane].hw0, stage[t.lane].hw1_hw0in,
+                            t.warp_base, t.warp_last, t.fsteps, t.nw);
     }
     unsigned m = __ballot_sync(0xffffffffu, cls == kClsFast) & t.gmask;
     GRT_TM_END(kTmClassify, 1);
@@ -991,6 +986,42 @@ wing_sweep_kernel(SweepParams const p)
             atomicAdd(&g_dbg_visits[kTmItem], 1ull);
         }
 #endif
+    }
+}
+
+
+// Diagnostic (GRT_CLASS_HIST=1, tests): how many (line, tile) visits of the wing sweep fall
+// into each line class, counted with the sweep's own classify_line() by one thread per
+// record; the hot kernel itself carries no counters.
+__global__ void __launch_bounds__(256)
+class_histogram_kernel(SweepParams const p, int const tile_points, unsigned long long *counts)
+{
+    uint64_t const j = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+    int const layer = blockIdx.y;
+    unsigned long long mine[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (j < p.num_lines)
+    {
+        LineRec const *rp = p.recs + (size_t)layer*p.num_lines + j;
+        int const fc = rp->fc;
+        int const hw0 = rp->hw0;
+        unsigned const hh = rp->hw1_hw0in;
+        if (fc != kSkip)
+        {
+            int const t0 = max(fc - p.fsteps, 0)/tile_points;
+            int const t1 = min(fc + p.fsteps, p.nw - 1)/tile_points;
+            for (int t=t0; t<=t1; ++t)
+            {
+                int const cls = classify_line(fc, hw0, hh, t*tile_points,
+                                              t*tile_points + tile_points - 1, p.fsteps, p.nw);
+                mine[cls & 7] += 1ull;
+            }
+        }
+    }
+    for (int c=1; c<7; ++c)
+    {
+        unsigned long long v = mine[c];
+        for (int o=16; o>0; o>>=1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(&counts[c - 1], v);
     }
 }
 

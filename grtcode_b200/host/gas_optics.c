@@ -369,6 +369,41 @@ int gas_optics_stats(GasOptics_t const * const gas_optics, uint64_t out[8])
 {
     REQUIRE_PTR(gas_optics);
     REQUIRE_PTR(out);
-    GPU(grt_gas_last_stats((grt_gas const *)gas_optics->sm100, out));
+    GPU(grt_gas_last_stats((grt_gas *)gas_optics->sm100, out));
+    return GRTCODE_SUCCESS;
+}
+
+int gas_optics_patch_counts(GasOptics_t const * const gas_optics, uint64_t out[2])
+{
+    REQUIRE_PTR(gas_optics);
+    REQUIRE_PTR(out);
+    GPU(grt_gas_patch_counts((grt_gas const *)gas_optics->sm100, out));
+    return GRTCODE_SUCCESS;
+}
+
+int gas_optics_debug_records(GasOptics_t const * const gas_optics, int const layer,
+                             uint64_t const first, uint64_t const count, float * const repwid,
+                             float * const y, double * const centre)
+{
+    REQUIRE_PTR(gas_optics);
+    GPU(grt_gas_debug_records((grt_gas *)gas_optics->sm100, layer, first, count, repwid, y,
+                              centre));
+    return GRTCODE_SUCCESS;
+}
+
+int gas_optics_debug_line_order(GasOptics_t const * const gas_optics, uint64_t const count,
+                                uint64_t * const order)
+{
+    REQUIRE_PTR(gas_optics);
+    REQUIRE_PTR(order);
+    GPU(grt_gas_debug_line_order((grt_gas const *)gas_optics->sm100, count, order));
+    return GRTCODE_SUCCESS;
+}
+
+int gas_optics_class_histogram(GasOptics_t const * const gas_optics, uint64_t out[8])
+{
+    REQUIRE_PTR(gas_optics);
+    REQUIRE_PTR(out);
+    GPU(grt_gas_class_histogram((grt_gas *)gas_optics->sm100, out));
     return GRTCODE_SUCCESS;
 }

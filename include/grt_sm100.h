@@ -10,7 +10,8 @@
  * the message.  Pointers named *_dev are device pointers obtained from
  * grt_malloc(); all others are host pointers.  All work of one device is
  * ordered on one library-owned CUDA stream; calls that return data to the host
- * synchronise that stream before returning.
+ * synchronise that stream before returning (grt_gas_optical_depth only enqueues its
+ * sweep kernels: tau_dev is complete for every later call on the library stream).
  */
 #ifndef GRT_SM100_H_
 #define GRT_SM100_H_
@@ -92,7 +93,27 @@ int grt_gas_optical_depth(grt_gas *gas, double const *p_atm, double const *t,
  * with CUDA events on the library stream: out[4] = column + line preprocessing,
  * out[5] = far-wing sweep kernel, out[6] = line-core kernel; out[7] = upper bound of
  * the samples the line-core kernel evaluates. */
-int grt_gas_last_stats(grt_gas const *gas, uint64_t out[8]);
+int grt_gas_last_stats(grt_gas *gas, uint64_t out[8]);
+
+/* K1 evaluates exp/pow with CUDA's libdevice, the reference with the host libm
+ * (utilities/src/grtcode_config.h:25-47).  Records whose Y = (float)(REPWID*gamma)
+ * (gas-optics/src/RFM_voigt.c:95) lies within a few double ulps of a float rounding
+ * boundary are rebuilt on the host with the host libm and patched before the sweep, so
+ * that every float of the line shape has the reference's bits.  out[0] = records patched
+ * by the last grt_gas_optical_depth call, out[1] = since grt_gas_create.
+ * (GRT_K1_PATCH=0 in the environment disables the patch: tests only.) */
+int grt_gas_patch_counts(grt_gas const *gas, uint64_t out[2]);
+
+/* Diagnostics (tests): REPWID, Y and the shifted centre of K1's records
+ * [first, first + count) of one layer, in device line order; the device line order as
+ * indices into the upload order (all grt_gas_add_molecule calls concatenated); line-tile
+ * visits per line class of the last line_sample call when GRT_CLASS_HIST=1 is set
+ * (out[0..5] = fast, region 1, far edge, near, Lorentz covered, Lorentz edge;
+ * out[6] = grid points per tile). */
+int grt_gas_debug_records(grt_gas *gas, int layer, uint64_t first, uint64_t count,
+                          float *repwid, float *y, double *centre);
+int grt_gas_debug_line_order(grt_gas const *gas, uint64_t count, uint64_t *order);
+int grt_gas_class_histogram(grt_gas *gas, uint64_t out[8]);
 
 /* ---- Rayleigh + optics mixing: replaces rayleigh_scattering
  * (shortwave/src/rayleigh.c:100-144) and add_optics (utilities/src/optics.c:84-148). */

@@ -48,4 +48,14 @@ EXTERN int heating_rates(int const num_levels, fp_t const * const pressure,
                          fp_t const * const up, fp_t const * const down, fp_t * const rate);
 /* Counters of the last calculate_optical_depth call: see grt_gas_last_stats. */
 EXTERN int gas_optics_stats(GasOptics_t const * const gas_optics, uint64_t out[8]);
+/* Diagnostics behind the parity tests (grt_sm100.h: grt_gas_patch_counts,
+ * grt_gas_debug_records, grt_gas_debug_line_order, grt_gas_class_histogram). */
+EXTERN int gas_optics_patch_counts(GasOptics_t const * const gas_optics, uint64_t out[2]);
+EXTERN int gas_optics_debug_records(GasOptics_t const * const gas_optics, int const layer,
+                                    uint64_t const first, uint64_t const count,
+                                    float * const repwid, float * const y,
+                                    double * const centre);
+EXTERN int gas_optics_debug_line_order(GasOptics_t const * const gas_optics,
+                                       uint64_t const count, uint64_t * const order);
+EXTERN int gas_optics_class_histogram(GasOptics_t const * const gas_optics, uint64_t out[8]);
 #endif
