@@ -10,6 +10,16 @@ broadband integration.  metric = spectral points x layers / s of line-by-line ta
 N > 1 (torchrun): every rank runs its own columns on its own GPU, no data-path
 collective (columns are independent: "weak" scaling); NCCL is used only for the
 barrier and the max-over-ranks of the device time.
+
+Further legs in the same JSON line:
+  e2e_reference_api  the step through the reference's own signatures (spectral fluxes to host)
+  rfmip              the north-star target: RFMIP-IRF-shaped columns at 0.1 cm-1, 225 distinct
+                     columns per rank (8 ranks = the 1800-column job), with the reference's CPU
+                     path timed on full columns of the same shape at N = 1 (rfmip.cpu_baseline)
+  spectral_split     N > 1: one config-4 column split over the ranks + NCCL all-reduce (strong
+                     scaling, per-rank compute and all-reduce seconds)
+  cpu_baseline       the reference on a bounded sample of the step (per-column work only;
+                     setup reported separately on both sides)
 """
 from __future__ import annotations
 
@@ -331,36 +341,51 @@ def recorded_wing_traffic(args):
     return sum(r["dram_read_bytes"] + r["dram_write_bytes"] for r in rec)/len(rec)
 
 
-def rfmip_probe(args, bands2, device, rank, world, barrier, stream, torch, dist, ncols: int = 4):
-    """Secondary figure, BASELINE config 3 shape: RFMIP-IRF-like columns (61 levels, LW 1-3250
-    + SW 1-50000 cm-1 at 0.1 cm-1, the same synthetic line lists as config 2), `ncols` columns
-    per rank, end to end through the C API (host arrays in, broadband fluxes out).  Columns
-    are sharded over the ranks with no collective; columns/s is the whole-job figure."""
+def rfmip_column(gi: int, cfcs):
+    """Column `gi` of the 1800-column RFMIP-IRF job (100 sites x 18 experiments; one distinct
+    synthetic profile per site, perturbed per experiment in the spirit of the RFMIP
+    experiments: CO2 scaling, +-4 K)."""
     from grtcode_b200 import synth
     from grtcode_b200 import workloads as W
+    site, expt = gi % 100, gi // 100
+    rng = np.random.default_rng(7000 + site)
+    scale = (1., 4., 0.5, 2., 3., 8.)[expt % 6]
+    return synth.make_column(61, rng, molecules=W.MOLECULES, cfcs=cfcs, co2_scale=scale,
+                             dt=4.*(expt % 3 - 1))
+
+
+def rfmip_leg(args, bands2, device, rank, world, barrier, stream, torch, dist):
+    """North-star target, BASELINE config 3: RFMIP-IRF-shaped columns (61 levels, LW 1-3250 +
+    SW 1-50000 cm-1 at 0.1 cm-1, the config-2 synthetic line lists, 7 molecules + continua +
+    3 CIA pairs + 3 CFCs), end to end through the C API (host arrays in, broadband fluxes out),
+    GRT_RFMIP_COLUMNS (default 225) distinct columns per rank -- so that 8 ranks run the
+    whole 1800-column job -- sharded with no collective.  On one rank the reference's CPU path
+    is timed on GRT_RFMIP_CPU_COLUMNS (default 1) FULL columns of the same shape."""
+    from grtcode_b200 import workloads as W
     from grtcode_b200.column_engine import ColumnEngine
-    if os.environ.get("GRT_BENCH_RFMIP", "1") == "0":
+    ncols = int(os.environ.get("GRT_RFMIP_COLUMNS", "225"))
+    if os.environ.get("GRT_BENCH_RFMIP", "1") == "0" or ncols < 1:
         return None
     lw3, sw3 = W.circ1_bands(0.1, args.scale)
     lw3.dataset, sw3.dataset = bands2[0].dataset, bands2[1].dataset
     cfcs = tuple(bands2[0].dataset.cfc.keys())
-
-    def column(site: int, expt: int):
-        rng = np.random.default_rng(7000 + site)
-        scale = (1., 4., 0.5, 2., 3., 8.)[expt % 6]
-        return synth.make_column(61, rng, molecules=W.MOLECULES, cfcs=cfcs, co2_scale=scale,
-                                 dt=4.*(expt % 3 - 1))
-
-    eng = ColumnEngine((lw3, sw3), column(0, 0), device, W.MOLECULES)
-    eng.step(column(rank, 0), upload_surface=True)
+    t_setup = time.perf_counter()
+    eng = ColumnEngine((lw3, sw3), rfmip_column(0, cfcs), device, W.MOLECULES)
+    t_setup = time.perf_counter() - t_setup
+    eng.step(rfmip_column(rank*ncols, cfcs), upload_surface=True)
+    # the columns are built before the timed region (input generation is not the hot path)
+    cols = [rfmip_column(rank*ncols + k, cfcs) for k in range(ncols)]
     e0 = torch.cuda.Event(enable_timing=True)
     e1 = torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
     samples = 0
     kern = {}
-    for k in range(ncols):
-        out = eng.step(column(100*rank + k, k), upload_surface=True)
+    first_fluxes = None
+    for k, c in enumerate(cols):
+        out = eng.step(c, upload_surface=True)
+        if k == 0:
+            first_fluxes = out
         samples += sum(out[n][2]["samples"] for n in ("lw", "sw"))
         for n in ("lw", "sw"):
             for key in ("prep_ns", "wing_ns", "core_ns"):
@@ -368,19 +393,157 @@ def rfmip_probe(args, bands2, device, rank, world, barrier, stream, torch, dist,
                 kern[name] = kern.get(name, 0.) + out[n][2][key]*1e-6/ncols
     e1.record(stream)
     barrier()
+    secs_local = e0.elapsed_time(e1)*1e-3
+    secs = secs_local
+    per_rank = [secs_local]
+    if world > 1:
+        t = torch.tensor([secs], device=f"cuda:{device}", dtype=torch.float64)
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        per_rank = [float(x.item()) for x in allt]
+        secs = max(per_rank)
+    eng.close()
+    res = {"columns_per_s": world*ncols/secs, "ms_per_column_per_gpu": 1e3*secs/ncols,
+           "columns_timed_per_gpu": ncols, "columns_timed_total": world*ncols,
+           "seconds_timed": secs, "seconds_per_rank": [round(x, 4) for x in per_rank],
+           "setup_s": t_setup,
+           "voigt_samples_per_column": samples//ncols,
+           "kernel_ms_per_column": {k: round(v, 3) for k, v in kern.items()},
+           "config": "BASELINE config 3 shape: 61 levels, LW 1-3250 (n=32491) + SW 1-50000 "
+                     "(n=499991) at 0.1 cm-1, 7 molecules + continua + 3 CIA + 3 CFCs, distinct "
+                     "columns (site, experiment), block-sharded over the GPUs, no collective",
+           "seconds_for_1800_columns": 1800.*secs/(world*ncols),
+           "seconds_for_1800_columns_note": (
+               "measured: this run IS the 1800-column job" if world*ncols == 1800 else
+               f"{world*ncols} columns timed, scaled linearly to 1800 (columns are independent)")}
+    ncpu = int(os.environ.get("GRT_RFMIP_CPU_COLUMNS", "1"))
+    if rank == 0 and world == 1 and ncpu > 0 and not args.no_cpu_baseline:
+        res["cpu_baseline"] = rfmip_cpu_baseline(args, (lw3, sw3), cfcs, ncpu, first_fluxes)
+        res["vs_cpu"] = res["columns_per_s"]/res["cpu_baseline"]["columns_per_s"]
+        res["vs_cpu_note"] = ("one B200 against the reference's OpenMP path on this box's "
+                              f"{res['cpu_baseline']['cores']} host cores, same column shape, "
+                              "per-column work only on both sides (north_star target: >= 50)")
+    return res
+
+
+def rfmip_cpu_baseline(args, bands3, cfcs, ncols: int, gpu_first):
+    """The reference's CPU path on `ncols` FULL config-3-shaped columns (no windows): the
+    column loop of framework/src/driver.c:691-743 on oracle/_ref with every host core."""
+    from grtcode_b200 import workloads as W
+    from oracle import ref as R
+    if not R.available():
+        return {"unavailable": "oracle/_ref not built"}
+    threads = host_threads()
+    parts = [ReferenceBand(b, 61, W.MOLECULES, threads) for b in bands3]
+    secs = {"lw": 0., "sw": 0.}
+    err = 0.
+    for k in range(ncols):
+        col = rfmip_column(k, cfcs)
+        for part in parts:
+            dt, up, dn = part.column(col)
+            secs[part.band.name] += dt
+            if k == 0 and gpu_first is not None:
+                g = gpu_first[part.band.name]
+                err = max(err, float(np.abs(g[0] - up).max()), float(np.abs(g[1] - dn).max()))
+    total = sum(secs.values())
+    cores = parts[0].cores
+    for part in parts:
+        part.close()
+    return {"columns_per_s": ncols/total, "seconds_per_column": total/ncols, "columns_timed": ncols,
+            "cores": cores, "kind": "reference", "extrapolated": False,
+            "seconds_per_column_by_band": {k: v/ncols for k, v in secs.items()},
+            "setup_s": sum(p.setup_s for p in parts),
+            "max_abs_flux_difference_vs_gpu_W_m2": err,
+            "sample": f"{ncols} full column(s) of the RFMIP shape, LW+SW, line_sample, "
+                      "per-column chain (set_ppmv .. broadband); setup (parse, add_*) separate"}
+
+
+def spectral_split_leg(args, bands2, device, rank, world, barrier, torch, dist, sw_ms_one_gpu):
+    """BASELINE config 4 at N > 1: ONE column's 1-50000 cm-1 range at 0.01 cm-1 (the SW band
+    of config 2: same grid, line list and tables) split over the N ranks, each rank on its
+    chunk + halo, the partial broadband integrals summed by one NCCL all-reduce.  Strong
+    scaling: efficiency = (one-GPU time of the same band, measured in this run by every
+    rank) / (N x the slowest rank's time)."""
+    from grtcode_b200 import parallel as P
+    from grtcode_b200 import workloads as W
+    if world < 2 or os.environ.get("GRT_BENCH_SPLIT", "1") == "0":
+        return None
+    col = W.circ1_column()
+    sw = bands2[1]
+    t_setup = time.perf_counter()
+    part = P.SpectralSplitColumn([sw], col, device, W.MOLECULES, world, rank)
+    t_setup = time.perf_counter() - t_setup
+    part.run(W.perturbed(col, 0, 0))                   # warm-up (allocations, tile lists)
+    reps = 3
+    comp, red, tot = [], [], []
+    for k in range(reps):
+        barrier()
+        t0 = time.perf_counter()
+        part.run(W.perturbed(col, 0, 300 + k))
+        torch.cuda.synchronize(device)
+        t1 = time.perf_counter()
+        comp.append(part.compute_seconds)
+        red.append(part.reduce_seconds)
+        tot.append(t1 - t0)
+    mine = torch.tensor([min(comp), float(np.median(red)), min(tot),
+                         float(part.chunks["sw"].n), float(part.engine.parts[0]["go"].stats()["samples"])],
+                        device=f"cuda:{device}", dtype=torch.float64)
+    allv = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(allv, mine)
+    part.close()
+    rows = [[float(x) for x in v.tolist()] for v in allv]
+    slowest = max(r[2] for r in rows)
+    one = sw_ms_one_gpu*1e-3
+    return {"workload": "BASELINE config 4: one CIRC-1 column, 1-50000 cm-1 at 0.01 cm-1 "
+                        "(n=4999901), 7 molecules + continua + 3 CIA pairs, spectral range "
+                        "split over the ranks, NCCL all-reduce of the broadband fluxes",
+            "scaling": "strong", "n_gpus": world,
+            "seconds_one_gpu": one, "seconds_split": slowest,
+            "speedup": one/slowest, "efficiency": one/(world*slowest),
+            "compute_seconds_per_rank": [round(r[0], 5) for r in rows],
+            "allreduce_seconds_per_rank": [round(r[1], 6) for r in rows],
+            "points_per_rank": [int(r[3]) for r in rows],
+            "voigt_samples_per_rank": [int(r[4]) for r in rows],
+            "allreduce_bytes": 2*8*len(col.p), "setup_s": t_setup,
+            "limiter": "the slowest rank's compute time (chunk cost imbalance + the halo and "
+                       "fixed per-launch costs every rank repeats); the all-reduce is "
+                       f"{1e6*float(np.median([r[1] for r in rows])):.0f} us"}
+
+
+def reference_api_leg(args, eng, col0, rank, barrier, stream, torch, dist, world, device,
+                      pts_layers):
+    """e2e_reference_api: the config-2 step through the reference's own signatures only
+    (ColumnEngine.step_reference_api): spectral fluxes [levels x n] of both bands are copied
+    to (page-locked) host arrays every step -- 4.7 GB per column at config 2 -- instead of the
+    1.8 KB of broadband values the fused column calls return."""
+    from grtcode_b200 import workloads as W
+    if args.method != "line_sample":
+        return None
+    steps = max(1, min(args.steps, 3))
+    eng.step_reference_api(W.perturbed(col0, rank, 400))          # allocations, first touch
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for k in range(steps):
+        out = eng.step_reference_api(W.perturbed(col0, rank, 401 + k))
+    e1.record(stream)
+    barrier()
     secs = e0.elapsed_time(e1)*1e-3
     if world > 1:
         t = torch.tensor([secs], device=f"cuda:{device}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         secs = float(t.item())
-    eng.close()
-    return {"columns_per_s": world*ncols/secs, "ms_per_column_per_gpu": 1e3*secs/ncols,
-            "columns_timed_per_gpu": ncols, "voigt_samples_per_column": samples//ncols,
-            "kernel_ms_per_column": {k: round(v, 3) for k, v in kern.items()},
-            "config": "BASELINE config 3 shape: 61 levels, LW 1-3250 (n=32491) + SW 1-50000 "
-                      "(n=499991) at 0.1 cm-1, 7 molecules + continua + 3 CIA + 3 CFCs, "
-                      "columns sharded over the GPUs, no collective",
-            "seconds_for_1800_columns": 1800.*secs/(world*ncols)}
+    dw = args.dw
+    bb = {k: (float(np.sum(0.5*(v[0][0, :-1] + v[0][0, 1:])*dw)),
+              float(np.sum(0.5*(v[1][-1, :-1] + v[1][-1, 1:])*dw))) for k, v in out.items()}
+    return {"value": world*pts_layers*steps/secs, "unit": UNIT, "ms_per_step": 1e3*secs/steps,
+            "steps": steps, "h2d_bytes_per_step": eng.h2d_ref, "d2h_bytes_per_step": eng.d2h_ref,
+            "path": "set_*_ppmv, calculate_optical_depth, rayleigh_scattering, add_optics, "
+                    "calculate_lw_fluxes / calculate_sw_fluxes with host flux arrays "
+                    "(longwave.h:56-68, shortwave.h:56-69), page-locked",
+            "broadband_of_returned_spectra_W_m2": {k: {"up_toa": v[0], "down_sfc": v[1]}
+                                                   for k, v in bb.items()}}
 
 
 def run_ours(args):
@@ -472,7 +635,29 @@ def run_ours(args):
     secs_e2e, _, _, _, out_e2e = timed(True, 200)
     h2d, d2h = eng.h2d, eng.d2h
 
-    rfmip = rfmip_probe(args, (lw, sw), device, rank, world, barrier, stream, torch, dist)
+    # the same step through the reference's own signatures: Rayleigh + add_optics
+    # materialised, calculate_{lw,sw}_fluxes returning [levels x n] spectral fluxes to the host
+    ref_api = None
+    if os.environ.get("GRT_BENCH_REFAPI", "1") != "0":
+        ref_api = reference_api_leg(args, eng, col0, rank, barrier, stream, torch, dist, world,
+                                    device, pts_layers)
+    # one-GPU time of the 1-50000 cm-1 band alone (the config-4 column): the denominator of
+    # the spectral-split leg's strong-scaling efficiency
+    sw_ms = None
+    if world > 1:
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        eng.step(W.perturbed(col0, 0, 0), True, only=("sw",))
+        barrier()
+        e0.record(stream)
+        for k in range(3):
+            eng.step(W.perturbed(col0, 0, 300 + k), True, only=("sw",))
+        e1.record(stream)
+        barrier()
+        sw_ms = e0.elapsed_time(e1)/3.
+    eng.close()
+    rfmip = rfmip_leg(args, (lw, sw), device, rank, world, barrier, stream, torch, dist)
+    split = spectral_split_leg(args, (lw, sw), device, rank, world, barrier, torch, dist, sw_ms)
 
     if rank != 0:
         if world > 1:
@@ -509,6 +694,9 @@ def run_ours(args):
         roofline["xu_pipe"] = {"ops_per_sample": 2, "achieved_lane_ops_per_s": 2.*roofline["samples_per_s"],
                                "peak_lane_ops_per_s": xu_peak,
                                "frac": 2.*roofline["samples_per_s"]/xu_peak}
+    if args.method != "line_sample":
+        # the flop bookkeeping above is the wing sweep's: no roofline line for the binned methods
+        roofline = None
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3*secs/args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -522,10 +710,12 @@ def run_ours(args):
             "voigt_samples_per_step": samples_step,
             "setup_s": t_setup,
             "rfmip": rfmip,
+            "e2e_reference_api": ref_api,
+            "spectral_split": split,
             "fluxes_W_m2": {"lw_up_toa": float(out["lw"][0][0]), "lw_dn_sfc": float(out["lw"][1][-1]),
                             "sw_up_toa": float(out["sw"][0][0]), "sw_dn_sfc": float(out["sw"][1][-1])}}
     if world == 1 and not args.no_cpu_baseline:
-        _, info = cpu_reference_sample(args, col0)
+        _, info, _ = cpu_reference_sample(args, col0)
         line["cpu_baseline"] = info
     print(json.dumps(line))
     if world > 1:

@@ -401,9 +401,10 @@ class LongwaveSolver:
                "create_longwave")
         self._live = True
 
-    def fluxes(self, optics: OpticsObject, t_surf, t_layers, t_levels, emis):
-        up = np.empty((self.num_levels, self.n))
-        dn = np.empty((self.num_levels, self.n))
+    def fluxes(self, optics: OpticsObject, t_surf, t_layers, t_levels, emis, out=None):
+        """calculate_lw_fluxes; out = (up, down) preallocated float64[levels, n] arrays."""
+        up, dn = out if out is not None else (np.empty((self.num_levels, self.n)),
+                                              np.empty((self.num_levels, self.n)))
         _check(self.L.calculate_lw_fluxes(C.byref(self.s), C.byref(optics.o), float(t_surf),
                                           _dp(_f64(t_layers)), _dp(_f64(t_levels)),
                                           _dp(_f64(emis)), _dp(up), _dp(dn)),
@@ -446,9 +447,11 @@ class ShortwaveSolver:
                "create_shortwave")
         self._live = True
 
-    def fluxes(self, optics: OpticsObject, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar):
-        up = np.empty((self.num_levels, self.n))
-        dn = np.empty((self.num_levels, self.n))
+    def fluxes(self, optics: OpticsObject, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar,
+               out=None):
+        """calculate_sw_fluxes; out = (up, down) preallocated float64[levels, n] arrays."""
+        up, dn = out if out is not None else (np.empty((self.num_levels, self.n)),
+                                              np.empty((self.num_levels, self.n)))
         _check(self.L.calculate_sw_fluxes(C.byref(self.s), C.byref(optics.o), float(mu_dir),
                                           float(mu_dif), _dp(_f64(alb_dir)), _dp(_f64(alb_dif)),
                                           float(tsi), _dp(_f64(solar)), _dp(up), _dp(dn)),

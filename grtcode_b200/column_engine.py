@@ -79,22 +79,66 @@ class ColumnEngine:
         self.d2h = 0
         self.last = {}
 
-    def step(self, col, upload_surface: bool):
+    def _set_abundances(self, part, col):
+        go = part["go"]
+        for m, v in col.ppmv.items():
+            go.set_ppmv("mol", m, v)
+        for c, v in col.cfc_ppmv.items():
+            if c in part["band"].dataset.cfc:
+                go.set_ppmv("cfc", c, v)
+        for c, v in col.cia_ppmv.items():
+            go.set_ppmv("cia", c, v)
+
+    def step_reference_api(self, col):
+        """The same column through the reference's OWN entry points only
+        (column_calculation, framework/src/driver.c:360-424): calculate_optical_depth,
+        rayleigh_scattering, add_optics (which allocates its result, optics.c:84-148),
+        calculate_lw_fluxes / calculate_sw_fluxes returning the spectral fluxes
+        [levels x n] to host arrays (longwave.h:56-68, shortwave.h:56-69).  The host arrays
+        are page-locked and allocated once.  Returns {"lw"/"sw": (up, down)} spectral."""
+        api = _api
+        out = {}
+        h2d = d2h = 0
+        for part in self.parts:
+            self._set_abundances(part, col)
+            part["go"].optical_depth(col.p, col.t, part["gas"])
+            h2d += 8*self.levels*(2 + 53 + 21 + 2)
+            n = part["n"]
+            if "ray" not in part:
+                part["ray"] = api.OpticsObject(self.levels - 1, part["grid"], self.device)
+                part["flux_up"] = pinned(self.levels*n, 0.).reshape(self.levels, n)
+                part["flux_dn"] = pinned(self.levels*n, 0.).reshape(self.levels, n)
+            api.rayleigh_scattering(part["ray"], col.p)
+            tot = api.add_optics([part["gas"], part["ray"]])
+            dst = (part["flux_up"], part["flux_dn"])
+            if part["band"].name.startswith("lw"):
+                part["emis"][:] = col.emissivity
+                part["solver"].fluxes(tot, col.t_surf, col.t_layer, col.t, part["emis"], out=dst)
+                h2d += 8*n
+            else:
+                part["alb"][:] = col.albedo
+                part["solver"].fluxes(tot, col.mu0, 0.5, part["alb"], part["alb"], col.tsi,
+                                      part["solar"], out=dst)
+                h2d += 3*8*n
+            d2h += 2*8*self.levels*n
+            tot.close()
+            out[part["band"].name[:2]] = dst
+        self.h2d_ref, self.d2h_ref = h2d, d2h
+        return out
+
+    def step(self, col, upload_surface: bool, only=None):
         """One column.  upload_surface=True is the end-to-end form: every host array the
-        API takes is passed (and copied to the GPU) again.  Returns
-        {"lw"/"sw": (flux_up[levels], flux_down[levels], kernel stats)} in W m-2."""
+        API takes is passed (and copied to the GPU) again.  only: band names to run (default
+        all).  Returns {"lw"/"sw": (flux_up[levels], flux_down[levels], kernel stats)} in
+        W m-2."""
         out = {}
         launches = 0
         h2d = 0
         for part in self.parts:
+            if only is not None and part["band"].name[:2] not in only:
+                continue
             go = part["go"]
-            for m, v in col.ppmv.items():
-                go.set_ppmv("mol", m, v)
-            for c, v in col.cfc_ppmv.items():
-                if c in part["band"].dataset.cfc:
-                    go.set_ppmv("cfc", c, v)
-            for c, v in col.cia_ppmv.items():
-                go.set_ppmv("cia", c, v)
+            self._set_abundances(part, col)
             go.optical_depth(col.p, col.t, part["gas"])
             h2d += 8*self.levels*(2 + 53 + 21 + 2)
             name = part["band"].name[:2]
@@ -132,5 +176,9 @@ class ColumnEngine:
         for part in self.parts:
             part["solver"].close()
             part["gas"].close()
+            if "ray" in part:
+                part["ray"].close()
+                for key in ("flux_up", "flux_dn"):
+                    _api.cuda_layer().grt_host_free(C.c_void_p(part[key].ctypes.data))
             part["go"].close()
         self.parts = []

@@ -260,7 +260,9 @@ class SpectralSplitColumn:
         names = sorted(out)
         up = np.stack([out[k][0] for k in names])
         dn = np.stack([out[k][1] for k in names])
+        t1 = time.perf_counter()
         up, dn = reduce_broadband(up, dn, group)
+        self.reduce_seconds = time.perf_counter() - t1
         return {k: (up[i], dn[i]) for i, k in enumerate(names)}
 
     def close(self):

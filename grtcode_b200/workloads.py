@@ -103,7 +103,10 @@ def circ1_bands(dw: float = 0.01, scale: float = 1.) -> tuple[Band, Band]:
 
 
 def materialise(band: Band, root: str, seed: int) -> Band:
-    cfcs = CFCS if band.name.startswith("lw") else ()
+    # the CFC tables cover 500-1500 cm-1 and are zero elsewhere (no-extrapolation rule,
+    # utilities.c:173-246); both bands carry them (BASELINE config 4 names them for the
+    # full 1-50000 cm-1 range)
+    cfcs = CFCS
     band.dataset = synth.make_dataset(os.path.join(root, band.name), band.w0, band.wn, band.lines,
                                       seed=seed, cfcs=cfcs, cias=CIAS)
     return band
