@@ -6,7 +6,16 @@
 #include <cstring>
 #include "grt_sm100.h"
 
+// Working precision of the data arrays that cross the C ABI (grt_real in grt_sm100.h): double,
+// or float when the whole stack is compiled with the reference's -DSINGLE_PRECISION
+// (configure.ac:25-32, utilities/src/floating_point_type.h:23-29).
+#ifdef SINGLE_PRECISION
+#define GRT_SINGLE 1
+#endif
+
 namespace grt {
+
+typedef grt_real real_t;
 
 // Last error message of the calling thread (read by grt_last_error()).
 inline char *error_buffer()

@@ -117,30 +117,42 @@ __host__ __device__ inline double tips_q(double const *tab, int const tmin, int 
 
 // Layer quantities of curtis_godson.c:25-120 and kernels.c:52-66, one function per value so
 // that the host can re-evaluate them for the few records it patches (see patch_near_ties).
-__host__ __device__ inline double layer_density(double const p0, double const p1)
+// T is the reference's fp_t: double, or float in the single build, where every operation below
+// is a float operation as it is in the reference compiled with -DSINGLE_PRECISION.
+template <typename T>
+__host__ __device__ inline T layer_density(T const p0, T const p1)
 {
-    double dp = p0 - p1;
-    dp = dp >= 0. ? dp : -dp;
-    return 2.147822334314468e+25*dp;
+    T dp = p0 - p1;
+    dp = dp >= (T)0 ? dp : -dp;
+    return (T)2.147822334314468e+25*dp;
 }
 
-__host__ __device__ inline double layer_mean(double const a0, double const a1)
+template <typename T>
+__host__ __device__ inline T layer_mean(T const a0, T const a1)
 {
-    return 0.5*(a0 + a1);
+    return (T)0.5f*(a0 + a1);
 }
 
-__host__ __device__ inline double layer_partial_pressure(double const x0, double const x1,
-                                                         double const p0, double const p1)
+template <typename T>
+__host__ __device__ inline T layer_partial_pressure(T const x0, T const x1, T const p0, T const p1)
 {
-    double const third = (double)(1.f/3.f);
-    double const sixth = (double)(1.f/6.f);
+    T const third = (T)(1.f/3.f);
+    T const sixth = (T)(1.f/6.f);
     return third*(x0*p0 + x1*p1) + sixth*(x0*p1 + x1*p0);
 }
 
-__host__ __device__ inline double layer_species_density(double const n, double const x0,
-                                                        double const x1)
+template <typename T>
+__host__ __device__ inline T layer_species_density(T const n, T const x0, T const x1)
 {
-    return n*0.5*(x0 + x1);
+    return n*(T)0.5f*(x0 + x1);
+}
+
+// q = 1.f/Q(mol, T, iso) (kernels.c:62); Q is the substitute table evaluated in double
+// (host/tips.c) and returned in fp_t (oracle/tips_shim.c does the same for the reference).
+template <typename T>
+__host__ __device__ inline T layer_qinv(double const *tab, int const tmin, int const nt, T const t)
+{
+    return (T)1.f/(T)tips_q(tab, tmin, nt, (double)t);
 }
 
 
@@ -148,42 +160,47 @@ __host__ __device__ inline double layer_species_density(double const n, double c
 __global__ void column_prep_kernel(int const num_layers, ColumnInputs const in,
                                    PrepMeta const meta, LayerView const out, double const cia_c)
 {
+    typedef real_t T;
     int const i = blockIdx.x*blockDim.x + threadIdx.x;
     if (i >= num_layers) return;
     int const L = num_layers;
     int const levels = L + 1;
-    double const p0 = in.p[i];
-    double const p1 = in.p[i+1];
-    double const n = layer_density(p0, p1);
-    double const pavg = layer_mean(p0, p1);
-    double const tavg = layer_mean(in.t[i], in.t[i+1]);
-    out.n[i] = n;
-    out.pavg[i] = pavg;
-    out.tavg[i] = tavg;
+    T const p0 = (T)in.p[i];
+    T const p1 = (T)in.p[i+1];
+    T const n = layer_density<T>(p0, p1);
+    T const pavg = layer_mean<T>(p0, p1);
+    T const tavg = layer_mean<T>((T)in.t[i], (T)in.t[i+1]);
+    out.n[i] = (double)n;
+    out.pavg[i] = (double)pavg;
+    out.tavg[i] = (double)tavg;
     for (int s=0; s<meta.num_slots; ++s)
     {
         double const *x = in.x_mol + (size_t)(meta.slots[s].mol_id - 1)*levels;
-        double const x0 = x[i];
-        double const x1 = x[i+1];
-        out.ps[s*L+i] = layer_partial_pressure(x0, x1, p0, p1);
-        out.ns[s*L+i] = layer_species_density(n, x0, x1);
+        T const x0 = (T)x[i];
+        T const x1 = (T)x[i+1];
+        out.ps[s*L+i] = (double)layer_partial_pressure<T>(x0, x1, p0, p1);
+        out.ns[s*L+i] = (double)layer_species_density<T>(n, x0, x1);
         for (int k=0; k<meta.slots[s].num_iso; ++k)
         {
             double const *tab = meta.tips + ((size_t)s*kMaxIso + k)*meta.tips_nt;
             out.qinv[((size_t)s*L + i)*kMaxIso + k] =
-                1./tips_q(tab, meta.tips_tmin, meta.tips_nt, tavg);
+                (double)layer_qinv<T>(tab, meta.tips_tmin, meta.tips_nt, tavg);
         }
     }
     for (int c=0; c<meta.num_cfcs; ++c)
     {
         double const *x = in.x_cfc + (size_t)meta.cfc_id[c]*levels;
-        out.cfc[c*L+i] = 0.5*n*(x[i] + x[i+1]);
+        out.cfc[c*L+i] = (double)((T)0.5*n*((T)x[i] + (T)x[i+1]));
     }
     for (int c=0; c<meta.num_cias; ++c)
     {
+        // (the reference's single build overflows here: its constant c = 7.9e46 exceeds
+        // FLT_MAX, kernels.c:610-615; this build forms the factor in double in both
+        // precisions)
         double const *x1 = in.x_cia + (size_t)meta.cia_id[c][0]*levels;
         double const *x2 = in.x_cia + (size_t)meta.cia_id[c][1]*levels;
-        double v = cia_c*((p0*p0 - p1*p1)/tavg)*0.25*(x1[i] + x1[i+1])*(x2[i] + x2[i+1]);
+        double const pd0 = (double)p0, pd1 = (double)p1;
+        double v = cia_c*((pd0*pd0 - pd1*pd1)/(double)tavg)*0.25*(x1[i] + x1[i+1])*(x2[i] + x2[i+1]);
         v = (v >= 0) ? v : v*-1.;
         out.cia[c*L+i] = v;
     }
@@ -193,9 +210,11 @@ __global__ void column_prep_kernel(int const num_layers, ColumnInputs const in,
 }  // namespace grt
 
 #include "sweep.cuh"
+#ifndef GRT_SINGLE
 #include "binned.cuh"
 #include <cub/device/device_segmented_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
+#endif
 
 namespace grt {
 
@@ -216,11 +235,12 @@ struct RecordCounts
     unsigned lor;
 };
 
-// Base parameters of one line and the layer quantities of its molecule.
+// Base parameters of one line and the layer quantities of its molecule, in the build's fp_t.
+template <typename T>
 struct LineInputs
 {
-    double v0, delta, s0, en, nair, yair, yself;   // parse_HITRAN_file.h:28-44
-    double T, P, Ps, Ns, qinv, mass;
+    T v0, delta, s0, en, nair, yair, yself;   // parse_HITRAN_file.h:28-44
+    T t, P, Ps, Ns, qinv, mass;
 };
 
 // Records K1 flags for re-evaluation on the host (see patch_near_ties): the product
@@ -228,7 +248,8 @@ struct LineInputs
 // difference between this GPU's pow() and the host libm's -- the one the reference calls --
 // could round Y = (float)(REPWID*gamma) (RFM_voigt.c:95) the other way and move every sample
 // of the line by 6e-8 relative.  libdevice pow is within 2 ulp and glibc within 1 ulp of the
-// true value; the multiplications that follow add one rounding each.
+// true value; the multiplications that follow add one rounding each.  (Double build only: the
+// single build's tolerance is 1e-4.)
 constexpr unsigned kTieUlps = 64;
 constexpr unsigned kTieInline = 254;       // flagged indices copied back with the counter
 
@@ -254,32 +275,36 @@ __host__ __device__ inline bool near_float_tie(double const g)
     return d <= kTieUlps;
 }
 
+__host__ __device__ inline float sqrt_fp(float const x) { return sqrtf(x); }
+__host__ __device__ inline double sqrt_fp(double const x) { return sqrt(x); }
+
 // One 64-byte record from the line's base parameters: formulas and operation order of
 // calc_line_centers / calc_line_strengths / calc_lorentz_hw / calc_doppler_hw
 // (kernels.c:34-131) followed by the per-line part of rfm_voigt_line_shape
 // (RFM_voigt.c:94-109) and the window of calc_optical_depth_line_sample
-// (kernels.c:417,431-437).  The three transcendental values come from the caller:
-// ex_en = EXP(c2*en/T), ex_v = EXP(c2*v0/T), pw = POW(296.f/T, n) -- libdevice's in K1,
-// the host libm's in patch_near_ties.  Returns true when Y sits near a float tie.
-__host__ __device__ inline bool build_record(LineInputs const &in, double const ex_en,
-                                             double const ex_v, double const pw, double const w0,
-                                             double const wres, uint64_t const nw,
+// (kernels.c:417,431-437), in the reference's fp_t (T).  The three transcendental values come
+// from the caller: ex_en = EXP(c2*en/T), ex_v = EXP(c2*v0/T), pw = POW(296.f/T, n) --
+// libdevice's in K1, the host libm's in patch_near_ties.  Returns true when Y sits near a
+// float tie (double build).
+template <typename T>
+__host__ __device__ inline bool build_record(LineInputs<T> const &in, T const ex_en,
+                                             T const ex_v, T const pw, T const w0,
+                                             T const wres, uint64_t const nw,
                                              int const fsteps, LineRec &r, RecordCounts &cnt)
 {
-    double const v = in.v0 + in.delta*in.P;
-    double const S = in.s0*ex_en*(1. - ex_v)*in.qinv;
-    double const gamma = pw*(in.yair*(in.P - in.Ps) + in.yself*in.Ps);
-    double const kb = 1.380658E-16;
-    double const cl = 2.99792458E10;
-    double const alpha = (double)0.83255461115f*v*sqrt((2.*kb*in.T)/(in.mass*cl*cl));
+    T const v = in.v0 + in.delta*in.P;
+    T const S = in.s0*ex_en*((T)1.f - ex_v)*in.qinv;
+    T const gamma = pw*(in.yair*(in.P - in.Ps) + in.yself*in.Ps);
+    T const kb = (T)1.380658E-16;
+    T const cl = (T)2.99792458E10;
+    T const alpha = (T)0.83255461115f*v*sqrt_fp(((T)2.f*kb*in.t)/(in.mass*cl*cl));
 
-    float const repwid = (float)((double)kSqrln2/alpha);
-    double const yd = (double)repwid*gamma;
+    float const repwid = (float)((T)kSqrln2/alpha);
+    T const yd = (T)repwid*gamma;
     float const y = (float)yd;
-    r.v = v;
     r.repwid = repwid;
     r.y = y;
-    double const sn = S*in.Ns;
+    T const sn = S*in.Ns;
     float const yq = y*y;
     r.yq = yq;
     r.yrrtpi = y*kRsqrpi;
@@ -289,36 +314,57 @@ __host__ __device__ inline bool build_record(LineInputs const &in, double const 
     voigt_limits(y, &r.xlim0, &r.xlim1);
     // Grid points farther than hw0 from fc have |x| >= XLIM0: |w_f - v| >=
     // (|f - fc| - 1/2) wres, and 1.5 grid steps of slack cover the float rounding of x.
-    double const step = (double)repwid*wres;          // x per grid point
-    double const h0 = ceil((double)r.xlim0/step) + 2.;
+    // Single build: the grid wavenumber itself is a float sum, off by up to ~3 float ulps of
+    // the wavenumber (0.01 cm-1 at 50000 cm-1): that many more grid steps of slack.
+    double const step = (double)repwid*(double)wres;          // x per grid point
+    double slack = 2.;
+    if (sizeof(T) == sizeof(float))
+    {
+        double const av = (double)(v >= (T)0 ? v : -v) + 25.;
+        slack += ceil(3.*av*1.1920929e-07/(double)wres) + 1.;
+    }
+    double const h0 = ceil((double)r.xlim0/step) + slack;
     // Conservative 16-bit companions for chunk classification near the centre: every
     // point with |f - fc| < hw0in has |x| < XLIM0, every point with |f - fc| > hw1
     // has |x| >= XLIM1 (so chunks between them are pure Humlicek region 1).
-    double h0in = floor((double)r.xlim0/step) - 2.;
-    double h1 = ceil((double)r.xlim1/step) + 2.;
+    double h0in = floor((double)r.xlim0/step) - slack;
+    double h1 = ceil((double)r.xlim1/step) + slack;
     if (!(h0in >= 0.)) h0in = 0.;
     if (!(h0in <= 65535.)) h0in = 65535.;
     if (!(h1 >= 0.)) h1 = 65535.;
     if (!(h1 <= 65535.)) h1 = 65535.;
     r.hw1_hw0in = (unsigned)h1 | ((unsigned)h0in << 16);
+    double cline;
     if (y >= kLorentzY)
     {
         r.hw0 = kHwLorentz;
-        r.c = sn*(double)(repwid*y)/3.14159265358979323846;
+        cline = (double)sn*(double)(repwid*y)/3.14159265358979323846;
     }
     else
     {
         r.hw0 = h0 < (double)kHwMax ? (int)h0 : kHwMax;
-        r.c = sn*(double)(kRsqrpi*repwid);
+        cline = (double)(sn*(T)(kRsqrpi*repwid));
         // Vanishing (or NaN) Y: far-wing values may be zero or subnormal; let
         // the line-core kernel evaluate the whole window with the full routine.
         if (!(y >= 1e-18f)) r.hw0 = kHwCoreOnly;
     }
+#ifdef GRT_SINGLE
+    r.v = (float)v;
+    r.c = (float)cline;
+    r.cy = r.c*r.yrrtpi;
+    r.pad_a = 0.f;
+    // a float c*Y/sqrt(pi) that underflows would drop the line from the far wing: such a line
+    // (optical depth below 1e-38 per sample) goes through the core kernel's full routine
+    if (r.hw0 >= 0 && !(r.cy >= 1.1754944e-38f) && r.c > 0.f) r.hw0 = kHwCoreOnly;
+#else
+    r.v = (double)v;
+    r.c = cline;
+#endif
     cnt.samples = 0;
     cnt.core = 0;
     cnt.rec = 0;
     cnt.lor = 0;
-    double const fcd = floor((2.*((v - w0)/wres) + 1.)/2.);
+    double const fcd = floor((double)(((T)2*((v - w0)/wres) + (T)1)/(T)2));
     if (fcd >= 0. && fcd < (double)nw)
     {
         int const fc = (int)fcd;
@@ -333,7 +379,7 @@ __host__ __device__ inline bool build_record(LineInputs const &in, double const 
         }
         else
         {
-            double const h = (double)r.xlim1/((double)repwid*wres);
+            double const h = (double)r.xlim1/((double)repwid*(double)wres);
             cnt.core = (unsigned long long)fmin(2.*h + 1., (double)(e - s + 1));
             if (r.hw0 == kHwCoreOnly) cnt.core = cnt.samples;
         }
@@ -342,7 +388,7 @@ __host__ __device__ inline bool build_record(LineInputs const &in, double const 
     {
         r.fc = kSkip;
     }
-    return near_float_tie(yd);
+    return sizeof(T) == sizeof(double) && near_float_tie((double)yd);
 }
 
 
@@ -368,25 +414,32 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         int iso = si & 0xff;
         if (iso < 1) iso = 1;
         if (iso > kMaxIso) iso = kMaxIso;
-        LineInputs in;
-        in.T = lay.tavg[i];
-        in.P = lay.pavg[i];
-        in.Ps = lay.ps[slot*L+i];
-        in.Ns = lay.ns[slot*L+i];
-        in.qinv = lay.qinv[((size_t)slot*L + i)*kMaxIso + iso - 1];
-        in.mass = meta.slots[slot].mass;
-        in.v0 = lines.v0[j];
-        in.delta = lines.delta[j];
-        in.s0 = lines.s0[j];
-        in.en = lines.en[j];
-        in.nair = lines.nair[j];
-        in.yair = lines.yair[j];
-        in.yself = lines.yself[j];
-        double const c2 = (double)(-1.4387686f);
+        typedef real_t T;
+        LineInputs<T> in;
+        in.t = (T)lay.tavg[i];
+        in.P = (T)lay.pavg[i];
+        in.Ps = (T)lay.ps[slot*L+i];
+        in.Ns = (T)lay.ns[slot*L+i];
+        in.qinv = (T)lay.qinv[((size_t)slot*L + i)*kMaxIso + iso - 1];
+        in.mass = (T)meta.slots[slot].mass;
+        in.v0 = (T)lines.v0[j];
+        in.delta = (T)lines.delta[j];
+        in.s0 = (T)lines.s0[j];
+        in.en = (T)lines.en[j];
+        in.nair = (T)lines.nair[j];
+        in.yair = (T)lines.yair[j];
+        in.yself = (T)lines.yself[j];
+        T const c2 = (T)(-1.4387686f);
         LineRec r;
         RecordCounts cnt;
-        bool const tie = build_record(in, exp(c2*in.en/in.T), exp(c2*in.v0/in.T),
-                                      pow(296./in.T, in.nair), w0, wres, nw, fsteps, r, cnt);
+#ifdef GRT_SINGLE
+        bool const tie = build_record<T>(in, expf(c2*in.en/in.t), expf(c2*in.v0/in.t),
+                                         powf(296.f/in.t, in.nair), (T)w0, (T)wres, nw, fsteps,
+                                         r, cnt);
+#else
+        bool const tie = build_record<T>(in, exp(c2*in.en/in.t), exp(c2*in.v0/in.t),
+                                         pow(296./in.t, in.nair), w0, wres, nw, fsteps, r, cnt);
+#endif
         my_samples = cnt.samples;
         my_core = cnt.core;
         my_rec = cnt.rec;
@@ -402,7 +455,7 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         if (vkey != nullptr)
         {
             // sort keys of the binned methods (sort_lines, kernels.c:135-172)
-            vkey[gi] = r.v;
+            vkey[gi] = (double)r.v;
             vidx[gi] = (unsigned)gi;
         }
     }
@@ -472,6 +525,7 @@ struct grt_gas
     std::vector<double> h_packed;        // the 7 base-parameter arrays in device order
     std::vector<uint16_t> h_si;          // slot << 8 | iso in device order
     std::vector<uint64_t> h_order;       // device position -> upload index
+    std::vector<double> h_inputs;        // column inputs of the current call, widened
     bool dirty = true;
     double max_abs_delta = 0.;
 
@@ -542,9 +596,12 @@ struct grt_gas
 constexpr unsigned kTieCapacity = 1u << 16;   // flagged records beyond the inline list
 
 
-static int upload_table(grt_gas *g, double const *host, double const **dev_out)
+// Tables live on the device as double in both builds (a float table widens exactly).
+static int upload_table(grt_gas *g, real_t const *host_in, double const **dev_out)
 {
     double *d = nullptr;
+    std::vector<double> wide(host_in, host_in + g->nw);
+    double const *host = wide.data();
     GRT_CUDA(cudaMalloc(&d, sizeof(double)*g->nw));
     GRT_CUDA(cudaMemcpyAsync(d, host, sizeof(double)*g->nw, cudaMemcpyHostToDevice, g->stream));
     GRT_CUDA(cudaStreamSynchronize(g->stream));
@@ -687,13 +744,13 @@ static int patch_near_ties(grt_gas *g, unsigned const count, double const *p_atm
         if (iso > kMaxIso) iso = kMaxIso;
         double const *x = x_mol + (size_t)(g->meta.slots[slot].mol_id - 1)*levels;
         double const p0 = p_atm[i], p1 = p_atm[i+1];
-        LineInputs in;
-        in.T = layer_mean(t[i], t[i+1]);
-        in.P = layer_mean(p0, p1);
-        in.Ps = layer_partial_pressure(x[i], x[i+1], p0, p1);
-        in.Ns = layer_species_density(layer_density(p0, p1), x[i], x[i+1]);
+        LineInputs<double> in;
+        in.t = layer_mean<double>(t[i], t[i+1]);
+        in.P = layer_mean<double>(p0, p1);
+        in.Ps = layer_partial_pressure<double>(x[i], x[i+1], p0, p1);
+        in.Ns = layer_species_density<double>(layer_density<double>(p0, p1), x[i], x[i+1]);
         double const *tab = g->h_tips.data() + ((size_t)slot*kMaxIso + iso - 1)*g->meta.tips_nt;
-        in.qinv = 1./tips_q(tab, g->meta.tips_tmin, g->meta.tips_nt, in.T);
+        in.qinv = layer_qinv<double>(tab, g->meta.tips_tmin, g->meta.tips_nt, in.t);
         in.mass = g->meta.slots[slot].mass;
         in.v0 = base[0*N+j];
         in.delta = base[1*N+j];
@@ -706,8 +763,9 @@ static int patch_near_ties(grt_gas *g, unsigned const count, double const *p_atm
         RecordCounts cnt;
         out.idx = gi;
         out.pad = 0;
-        build_record(in, std::exp(c2*in.en/in.T), std::exp(c2*in.v0/in.T),
-                     std::pow(296./in.T, in.nair), g->w0, g->dw, g->nw, fsteps, out.rec, cnt);
+        build_record<double>(in, std::exp(c2*in.en/in.t), std::exp(c2*in.v0/in.t),
+                             std::pow(296./in.t, in.nair), g->w0, g->dw, g->nw, fsteps, out.rec,
+                             cnt);
     }
     GRT_CUDA(cudaMemcpyAsync(g->d_patch, g->h_patch, sizeof(RecordPatch)*count,
                              cudaMemcpyHostToDevice, st));
@@ -791,7 +849,7 @@ static int launch_wing_impl(SweepParams const &sp, int const sms, cudaStream_t c
                                       Cfg::kRingBytes + (TBL ? kMaxTableBytes : 0)));
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
-    int const smem = Cfg::kRingBytes + (TBL ? 8*sweep_table_entries<PTS, LN>(sp.fsteps) : 0);
+    int const smem = Cfg::kRingBytes + (TBL ? (int)sizeof(wn_t)*sweep_table_entries<PTS, LN>(sp.fsteps) : 0);
     int per_sm = 0;
     GRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wing_sweep_kernel<PTS, NL, TBL, LN>,
                                                            kSweepThreads, smem));
@@ -807,12 +865,13 @@ static int launch_wing_impl(SweepParams const &sp, int const sms, cudaStream_t c
 template <int PTS, int NL, int LN = 32>
 static int launch_wing(SweepParams const &sp, int const sms, cudaStream_t const st)
 {
-    bool table = 8*sweep_table_entries<PTS, LN>(sp.fsteps) <= kMaxTableBytes;
+    bool table = (int)sizeof(wn_t)*sweep_table_entries<PTS, LN>(sp.fsteps) <= kMaxTableBytes;
     if (char const *env = getenv("GRT_SWEEP_TABLE")) table = table && atoi(env) != 0;
     return table ? launch_wing_impl<PTS, NL, true, LN>(sp, sms, st)
                  : launch_wing_impl<PTS, NL, false, LN>(sp, sms, st);
 }
 
+#ifndef GRT_SINGLE
 // Segment id (layer*slots + molecule slot) of every entry of a list of global record indices.
 struct SegmentMap
 {
@@ -1020,6 +1079,12 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
     g->timings_pending = true;
     return 0;
 }
+#else
+static int binned_optical_depth(grt_gas *, int, grt::LayerView const &, double *, int)
+{
+    return fail("binned methods are not part of the single-precision build");
+}
+#endif
 
 extern "C" {
 
@@ -1097,9 +1162,9 @@ int grt_gas_destroy(grt_gas *g)
 }
 
 int grt_gas_add_molecule(grt_gas *g, int mol_id, double mass_g, int num_iso,
-                         uint64_t num_lines, int const *iso, double const *vnn,
-                         double const *snn, double const *yair, double const *yself,
-                         double const *en, double const *n_air, double const *delta,
+                         uint64_t num_lines, int const *iso, real_t const *vnn,
+                         real_t const *snn, real_t const *yair, real_t const *yself,
+                         real_t const *en, real_t const *n_air, real_t const *delta,
                          double const *q_table, int tmin, int nt)
 {
     if (g == nullptr) return fail("null gas handle");
@@ -1140,8 +1205,8 @@ int grt_gas_add_molecule(grt_gas *g, int mol_id, double mass_g, int num_iso,
     return 0;
 }
 
-int grt_gas_set_h2o_continuum(grt_gas *g, double const *s296, double const *ckds,
-                              double const *f296, double const *ckdf)
+int grt_gas_set_h2o_continuum(grt_gas *g, real_t const *s296, real_t const *ckds,
+                              real_t const *f296, real_t const *ckdf)
 {
     if (g == nullptr) return fail("null gas handle");
     GRT_CUDA(cudaSetDevice(g->device));
@@ -1153,7 +1218,7 @@ int grt_gas_set_h2o_continuum(grt_gas *g, double const *s296, double const *ckds
     return 0;
 }
 
-int grt_gas_set_o3_continuum(grt_gas *g, double const *cross_section)
+int grt_gas_set_o3_continuum(grt_gas *g, real_t const *cross_section)
 {
     if (g == nullptr) return fail("null gas handle");
     GRT_CUDA(cudaSetDevice(g->device));
@@ -1162,7 +1227,7 @@ int grt_gas_set_o3_continuum(grt_gas *g, double const *cross_section)
     return 0;
 }
 
-int grt_gas_add_cfc(grt_gas *g, int cfc_id, double const *cross_section)
+int grt_gas_add_cfc(grt_gas *g, int cfc_id, real_t const *cross_section)
 {
     if (g == nullptr) return fail("null gas handle");
     if (cfc_id < 0 || cfc_id >= GRT_MAX_CFCS) return fail("unrecognized CFC id %d", cfc_id);
@@ -1175,7 +1240,7 @@ int grt_gas_add_cfc(grt_gas *g, int cfc_id, double const *cross_section)
     return 0;
 }
 
-int grt_gas_add_cia(grt_gas *g, int species0, int species1, double const *cross_section)
+int grt_gas_add_cia(grt_gas *g, int species0, int species1, real_t const *cross_section)
 {
     if (g == nullptr) return fail("null gas handle");
     if (species0 < 0 || species0 >= GRT_NUM_CIA_SPECIES || species1 < 0 ||
@@ -1193,12 +1258,38 @@ int grt_gas_add_cia(grt_gas *g, int species0, int species1, double const *cross_
     return 0;
 }
 
-int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
-                          double const *x_mol, double const *x_cfc, double const *x_cia,
-                          int method, double *tau_dev)
+int grt_gas_optical_depth(grt_gas *g, real_t const *p_atm_in, real_t const *t_in,
+                          real_t const *x_mol_in, real_t const *x_cfc_in, real_t const *x_cia_in,
+                          int method, real_t *tau_dev)
 {
     if (g == nullptr) return fail("null gas handle");
     if (method < 0 || method > 2) return fail("unknown optical depth method %d", method);
+#ifdef GRT_SINGLE
+    if (method != 2)
+    {
+        return fail("the single-precision build provides optical_depth_method line_sample (the "
+                    "method of every reference driver, driver.c:618-624); wavenumber_sweep and "
+                    "line_sweep exist in the double build");
+    }
+#endif
+    // the column inputs, widened to double (exact) in one staging block
+    {
+        size_t const lv = (size_t)g->num_levels;
+        g->h_inputs.resize(lv*(2 + GRT_MAX_MOLS + GRT_MAX_CFCS + GRT_NUM_CIA_SPECIES));
+        double *q = g->h_inputs.data();
+        for (size_t k=0; k<lv; ++k) q[k] = (double)p_atm_in[k];
+        q += lv;
+        for (size_t k=0; k<lv; ++k) q[k] = (double)t_in[k];
+        q += lv;
+        for (size_t k=0; k<lv*GRT_MAX_MOLS; ++k) q[k] = (double)x_mol_in[k];
+        q += lv*GRT_MAX_MOLS;
+        for (size_t k=0; k<lv*GRT_MAX_CFCS; ++k) q[k] = (double)x_cfc_in[k];
+        q += lv*GRT_MAX_CFCS;
+        for (size_t k=0; k<lv*GRT_NUM_CIA_SPECIES; ++k) q[k] = (double)x_cia_in[k];
+    }
+    double const *p_atm = g->h_inputs.data();
+    double const *t = p_atm + g->num_levels;
+    double const *x_mol = t + g->num_levels;
     GRT_CUDA(cudaSetDevice(g->device));
     if (g->dirty || g->order_method != method) GRT_TRY(finalize_lines(g, method));
     int const L = g->num_layers;
@@ -1213,13 +1304,8 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     in.x_mol = d + 2*levels;
     in.x_cfc = in.x_mol + (size_t)GRT_MAX_MOLS*levels;
     in.x_cia = in.x_cfc + (size_t)GRT_MAX_CFCS*levels;
-    GRT_CUDA(cudaMemcpyAsync((void *)in.p, p_atm, sizeof(double)*levels, cudaMemcpyHostToDevice, st));
-    GRT_CUDA(cudaMemcpyAsync((void *)in.t, t, sizeof(double)*levels, cudaMemcpyHostToDevice, st));
-    GRT_CUDA(cudaMemcpyAsync((void *)in.x_mol, x_mol, sizeof(double)*GRT_MAX_MOLS*levels,
-                             cudaMemcpyHostToDevice, st));
-    GRT_CUDA(cudaMemcpyAsync((void *)in.x_cfc, x_cfc, sizeof(double)*GRT_MAX_CFCS*levels,
-                             cudaMemcpyHostToDevice, st));
-    GRT_CUDA(cudaMemcpyAsync((void *)in.x_cia, x_cia, sizeof(double)*GRT_NUM_CIA_SPECIES*levels,
+    // one copy: the staging block has the device layout (p, t, x_mol, x_cfc, x_cia)
+    GRT_CUDA(cudaMemcpyAsync((void *)in.p, p_atm, sizeof(double)*g->h_inputs.size(),
                              cudaMemcpyHostToDevice, st));
 
     LayerView lay;
@@ -1246,7 +1332,11 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     ++launches;
 
     uint64_t const N = g->num_lines;
+#ifdef GRT_SINGLE
+    int const fsteps = (int)std::ceil((double)(25.f/(float)g->dw));     // kernels.c:417, fp_t = float
+#else
     int const fsteps = (int)std::ceil((double)25.f/g->dw);
+#endif
     GRT_CUDA(cudaMemsetAsync(g->d_stats, 0, sizeof(PrepStats), st));
     GRT_CUDA(cudaMemsetAsync(g->d_ties, 0, 2*sizeof(unsigned), st));
     if (N > 0)
@@ -1320,7 +1410,7 @@ int grt_gas_optical_depth(grt_gas *g, double const *p_atm, double const *t,
     g->stats[2] = 0;
     if (method != 2)
     {
-        return binned_optical_depth(g, method, lay, tau_dev, launches);
+        return binned_optical_depth(g, method, lay, (double *)tau_dev, launches);
     }
 
     GRT_CUDA(cudaEventRecord(g->ev[1], st));

@@ -21,6 +21,12 @@ namespace grt {
 
 constexpr int kSolverThreads = 128;
 
+// Spectral arrays (optics in, fluxes out) carry the build's working precision (real_t: float
+// in the single build); every kernel computes in double and rounds once at its stores, and the
+// broadband sums of the fused kernels stay double until they are handed to the caller.
+template <bool FUSED> struct FluxOut { typedef real_t type; };
+template <> struct FluxOut<true> { typedef double type; };
+
 struct LevelTemps
 {
     double t_layers[GRT_MAX_LAYERS];
@@ -41,8 +47,8 @@ __device__ __forceinline__ double rayleigh_tau(double const w, double const n)
 }
 
 __global__ void rayleigh_kernel(int const num_layers, double const w0, double const dw,
-                                uint64_t const nw, LayerDensity const dens, double *omega,
-                                double *g, double *tau)
+                                uint64_t const nw, LayerDensity const dens, real_t *omega,
+                                real_t *g, real_t *tau)
 {
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     if (i >= nw) return;
@@ -50,9 +56,9 @@ __global__ void rayleigh_kernel(int const num_layers, double const w0, double co
     for (int j=0; j<num_layers; ++j)
     {
         size_t const o = (size_t)j*nw + i;
-        omega[o] = 1.;
-        g[o] = 0.;
-        tau[o] = rayleigh_tau(w, dens.n[j]);
+        omega[o] = (real_t)1.;
+        g[o] = (real_t)0.;
+        tau[o] = (real_t)rayleigh_tau(w, dens.n[j]);
     }
 }
 
@@ -60,29 +66,29 @@ __global__ void rayleigh_kernel(int const num_layers, double const w0, double co
 // ---- add_optics (optics.c:124-148) ------------------------------------------------
 struct OpticsList
 {
-    double const *g[8];
-    double const *omega[8];
-    double const *tau[8];
+    real_t const *g[8];
+    real_t const *omega[8];
+    real_t const *tau[8];
 };
 
 __global__ void add_optics_kernel(uint64_t const n, int const num_optics, OpticsList const in,
-                                  double *g_out, double *omega_out, double *tau_out)
+                                  real_t *g_out, real_t *omega_out, real_t *tau_out)
 {
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     if (i >= n) return;
     double g = 0., omega = 0., tau = 0.;
     for (int j=0; j<num_optics; ++j)
     {
-        double const gi = in.g[j][i];
-        double const oi = in.omega[j][i];
-        double const ti = in.tau[j][i];
+        double const gi = (double)in.g[j][i];
+        double const oi = (double)in.omega[j][i];
+        double const ti = (double)in.tau[j][i];
         g += gi*oi*ti;
         omega += oi*ti;
         tau += ti;
     }
-    g_out[i] = g/omega;
-    omega_out[i] = omega/tau;
-    tau_out[i] = tau;
+    g_out[i] = (real_t)(g/omega);
+    omega_out[i] = (real_t)(omega/tau);
+    tau_out[i] = (real_t)tau;
 }
 
 
@@ -170,9 +176,11 @@ template <bool FUSED>
 __global__ void __launch_bounds__(kSolverThreads)
 lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const nw,
           double const t_surf, LevelTemps const temps, LayerDensity const dens,
-          double const *tau, double const *omega, double const *emis, double *flux_up,
-          double *flux_down, uint64_t const first, uint64_t const last)
+          real_t const *tau, real_t const *omega, real_t const *emis,
+          typename FluxOut<FUSED>::type *flux_up, typename FluxOut<FUSED>::type *flux_down,
+          uint64_t const first, uint64_t const last)
 {
+    typedef typename FluxOut<FUSED>::type flux_t;
     __shared__ LevelSums sums;
     if (FUSED) clear_levels(sums);
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
@@ -198,13 +206,13 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         size_t const o = (size_t)j*nw + ii;
         if (FUSED)
         {
-            double const tg = tau[o];
+            double const tg = (double)tau[o];
             double const tr = rayleigh_tau(w, dens.n[j]);
             double const tt = tg + tr;
             double const om = tr/tt;
             return tt*(1. - om);
         }
-        return tau[o]*(1. - omega[o]);
+        return (double)tau[o]*(1. - (double)omega[o]);
     };
 
     double I[4] = {0., 0., 0., 0.};
@@ -214,7 +222,7 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     }
     else if (live)
     {
-        flux_down[ii] = 0.;
+        flux_down[ii] = (flux_t)0.;
     }
     for (int j=0; j<L; ++j)
     {
@@ -235,11 +243,11 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         }
         else if (live)
         {
-            flux_down[(size_t)(j+1)*nw + ii] = f;
+            flux_down[(size_t)(j+1)*nw + ii] = (flux_t)f;
         }
     }
     double const bs = planck(t_surf, w);
-    double const em = emis[ii];
+    double const em = (double)emis[ii];
     double f = 0.;
 #pragma unroll
     for (int s=0; s<4; ++s)
@@ -253,7 +261,7 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     }
     else if (live)
     {
-        flux_up[(size_t)L*nw + ii] = f;
+        flux_up[(size_t)L*nw + ii] = (flux_t)f;
     }
     for (int j=L-1; j>=0; --j)
     {
@@ -274,10 +282,10 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         }
         else if (live)
         {
-            flux_up[(size_t)j*nw + ii] = f;
+            flux_up[(size_t)j*nw + ii] = (flux_t)f;
         }
     }
-    if (FUSED) flush_levels(sums, num_levels, flux_up, flux_down);
+    if (FUSED) flush_levels(sums, num_levels, (double *)flux_up, (double *)flux_down);
 }
 
 
@@ -356,11 +364,13 @@ __device__ void eddington(double const omega, double const tau, double const mu,
 template <int MAXL, bool FUSED>
 __global__ void __launch_bounds__(kSolverThreads, GRT_SW_MINBLOCKS)
 sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const nw,
-          LayerDensity const dens, double const *omega_in, double const *g_in,
-          double const *tau_in, double const mu_dir, double const mu_dif,
-          double const *alb_dir, double const *alb_dif, double const tsi, double const *solar,
-          double *flux_up, double *flux_down, uint64_t const first, uint64_t const last)
+          LayerDensity const dens, real_t const *omega_in, real_t const *g_in,
+          real_t const *tau_in, double const mu_dir, double const mu_dif,
+          real_t const *alb_dir, real_t const *alb_dif, double const tsi, real_t const *solar,
+          typename FluxOut<FUSED>::type *flux_up, typename FluxOut<FUSED>::type *flux_down,
+          uint64_t const first, uint64_t const last)
 {
+    typedef typename FluxOut<FUSED>::type flux_t;
     __shared__ LevelSums sums;
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     bool const live = i < nw;
@@ -377,8 +387,8 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     // The layers are independent, so their order does not change any value.
     double R_dir[MAXL], R_dif[MAXL], T_dir[MAXL], T_dif[MAXL], T_pure[MAXL];
     double Rdd[MAXL + 1], Rfd[MAXL + 1];
-    double rdd_below = alb_dir[ii];
-    double rfd_below = alb_dif[ii];
+    double rdd_below = (double)alb_dir[ii];
+    double rfd_below = (double)alb_dif[ii];
     Rdd[L] = rdd_below;
     Rfd[L] = rfd_below;
     for (int j=L-1; j>=0; --j)
@@ -389,7 +399,7 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         {
             // add_optics of [gas, rayleigh] (optics.c:134-146): g = 0*tau_R/tau_R,
             // omega = tau_R/(tau_gas + tau_R).
-            double const tg = tau_in[o];
+            double const tg = (double)tau_in[o];
             double const tr = rayleigh_tau(w, dens.n[j]);
             tau = tg + tr;
             g = 0./tr;
@@ -397,9 +407,9 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         }
         else
         {
-            omega = omega_in[o];
-            g = g_in[o];
-            tau = tau_in[o];
+            omega = (double)omega_in[o];
+            g = (double)g_in[o];
+            tau = (double)tau_in[o];
         }
         // delta-Eddington scaling (shortwave.c:86-89).
         double const gs = g/(g + 1.);
@@ -427,7 +437,7 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     // Rfu (reflectivity of the layers above a level to diffuse light from below,
     // shortwave.c:262-268) is a top-down recursion: it is advanced inside the level loop
     // below (the same operations in the same order) instead of being stored per layer.
-    double const scale = solar[ii]*mu_dir;
+    double const scale = (double)solar[ii]*mu_dir;
     double weight = 0.;
     if (FUSED)
     {
@@ -448,8 +458,8 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         }
         else
         {
-            flux_up[ii] = up;
-            flux_down[ii] = down;
+            flux_up[ii] = (flux_t)up;
+            flux_down[ii] = (flux_t)down;
         }
     }
     double rfu_above = 0.;          // Rfu[j-2]
@@ -484,26 +494,26 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         }
         else
         {
-            flux_up[(size_t)j*nw + ii] = up;
-            flux_down[(size_t)j*nw + ii] = down;
+            flux_up[(size_t)j*nw + ii] = (flux_t)up;
+            flux_down[(size_t)j*nw + ii] = (flux_t)down;
         }
     }
-    if (FUSED) flush_levels(sums, num_levels, flux_up, flux_down);
+    if (FUSED) flush_levels(sums, num_levels, (double *)flux_up, (double *)flux_down);
 }
 
 
 // ---- broadband integration (driver.c:302-319) ----------------------------------------
 __global__ void __launch_bounds__(256)
-integrate_kernel(uint64_t const nw, double const dw, double const *flux, double *out)
+integrate_kernel(uint64_t const nw, double const dw, real_t const *flux, double *out)
 {
     __shared__ double warp_sums[8];
     int const level = blockIdx.y;
-    double const *f = flux + (size_t)level*nw;
+    real_t const *f = flux + (size_t)level*nw;
     double acc = 0.;
     for (uint64_t i=(uint64_t)blockIdx.x*blockDim.x + threadIdx.x; i + 1 < nw;
          i += (uint64_t)gridDim.x*blockDim.x)
     {
-        acc += 0.5*(f[i] + f[i+1])*dw;
+        acc += 0.5*((double)f[i] + (double)f[i+1])*dw;
     }
     block_accumulate(acc, &out[level], warp_sums);
 }
@@ -522,14 +532,29 @@ static int out_buffer(int device, double **buf)
     return 0;
 }
 
-static void number_densities(int num_layers, double const *p_atm, LayerDensity *d)
+// n of calc_number_densities (curtis_godson.c:25-34) in the build's fp_t.
+static void number_densities(int num_layers, real_t const *p_atm, LayerDensity *d)
 {
     for (int i=0; i<num_layers; ++i)
     {
-        double dp = p_atm[i] - p_atm[i+1];
-        dp = dp >= 0. ? dp : -dp;
-        d->n[i] = 2.147822334314468e+25*dp;
+        real_t dp = p_atm[i] - p_atm[i+1];
+        dp = dp >= (real_t)0 ? dp : -dp;
+        d->n[i] = (double)((real_t)2.147822334314468e+25*dp);
     }
+}
+
+// Broadband results: double on the device, handed to the caller in the build's precision.
+static int fetch_levels(cudaStream_t st, double const *buf, int num_levels, real_t *up, real_t *down)
+{
+    double host[2*(GRT_MAX_LAYERS + 1)];
+    GRT_CUDA(cudaMemcpyAsync(host, buf, sizeof(double)*2*num_levels, cudaMemcpyDeviceToHost, st));
+    GRT_CUDA(cudaStreamSynchronize(st));
+    for (int i=0; i<num_levels; ++i)
+    {
+        up[i] = (real_t)host[i];
+        if (down != nullptr) down[i] = (real_t)host[num_levels + i];
+    }
+    return 0;
 }
 
 }  // namespace grt
@@ -538,10 +563,11 @@ using namespace grt;
 
 template <bool FUSED>
 static int launch_sw(cudaStream_t st, int num_levels, double w0, double dw, uint64_t nw,
-                     LayerDensity const &dens, double const *omega, double const *g,
-                     double const *tau, double mu_dir, double mu_dif, double const *alb_dir,
-                     double const *alb_dif, double tsi, double const *solar, double *up,
-                     double *down, uint64_t first, uint64_t last)
+                     LayerDensity const &dens, real_t const *omega, real_t const *g,
+                     real_t const *tau, double mu_dir, double mu_dif, real_t const *alb_dir,
+                     real_t const *alb_dif, double tsi, real_t const *solar,
+                     typename FluxOut<FUSED>::type *up, typename FluxOut<FUSED>::type *down,
+                     uint64_t first, uint64_t last)
 {
     unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
     // Measurement knob: resident blocks per SM, enforced with idle dynamic shared memory (the
@@ -584,7 +610,7 @@ static int launch_sw(cudaStream_t st, int num_levels, double w0, double dw, uint
 extern "C" {
 
 int grt_rayleigh(int device, int num_layers, double w0, double dw, uint64_t nw,
-                 double const *p_atm, double *omega_dev, double *g_dev, double *tau_dev)
+                 real_t const *p_atm, real_t *omega_dev, real_t *g_dev, real_t *tau_dev)
 {
     if (num_layers < 1 || num_layers > GRT_MAX_LAYERS) return fail("bad layer count %d", num_layers);
     cudaStream_t st;
@@ -597,9 +623,9 @@ int grt_rayleigh(int device, int num_layers, double w0, double dw, uint64_t nw,
     return 0;
 }
 
-int grt_add_optics(int device, uint64_t n, int num_optics, double const *const *g_dev,
-                   double const *const *omega_dev, double const *const *tau_dev,
-                   double *g_out_dev, double *omega_out_dev, double *tau_out_dev)
+int grt_add_optics(int device, uint64_t n, int num_optics, real_t const *const *g_dev,
+                   real_t const *const *omega_dev, real_t const *const *tau_dev,
+                   real_t *g_out_dev, real_t *omega_out_dev, real_t *tau_out_dev)
 {
     if (num_optics < 1 || num_optics > 8) return fail("add_optics supports 1..8 objects");
     cudaStream_t st;
@@ -618,9 +644,9 @@ int grt_add_optics(int device, uint64_t n, int num_optics, double const *const *
 }
 
 int grt_lw_fluxes(int device, int num_levels, double w0, double dw, uint64_t nw, double t_surf,
-                  double const *t_layers, double const *t_levels, double const *tau_dev,
-                  double const *omega_dev, double const *emis_dev, double *flux_up_dev,
-                  double *flux_down_dev)
+                  real_t const *t_layers, real_t const *t_levels, real_t const *tau_dev,
+                  real_t const *omega_dev, real_t const *emis_dev, real_t *flux_up_dev,
+                  real_t *flux_down_dev)
 {
     if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
     cudaStream_t st;
@@ -637,10 +663,10 @@ int grt_lw_fluxes(int device, int num_levels, double w0, double dw, uint64_t nw,
     return 0;
 }
 
-int grt_sw_fluxes(int device, int num_levels, uint64_t nw, double const *omega_dev,
-                  double const *g_dev, double const *tau_dev, double mu_dir, double mu_dif,
-                  double const *alb_dir_dev, double const *alb_dif_dev, double tsi,
-                  double const *solar_dev, double *flux_up_dev, double *flux_down_dev)
+int grt_sw_fluxes(int device, int num_levels, uint64_t nw, real_t const *omega_dev,
+                  real_t const *g_dev, real_t const *tau_dev, double mu_dir, double mu_dif,
+                  real_t const *alb_dir_dev, real_t const *alb_dif_dev, double tsi,
+                  real_t const *solar_dev, real_t *flux_up_dev, real_t *flux_down_dev)
 {
     if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
     cudaStream_t st;
@@ -652,7 +678,7 @@ int grt_sw_fluxes(int device, int num_levels, uint64_t nw, double const *omega_d
 }
 
 int grt_integrate_flux(int device, int num_levels, uint64_t nw, double dw,
-                       double const *flux_dev, double *out)
+                       real_t const *flux_dev, real_t *out)
 {
     if (num_levels < 1 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
     cudaStream_t st;
@@ -665,15 +691,17 @@ int grt_integrate_flux(int device, int num_levels, uint64_t nw, double dw,
     if (bx < 1) bx = 1;
     integrate_kernel<<<dim3(bx, (unsigned)num_levels), 256, 0, st>>>(nw, dw, flux_dev, buf);
     GRT_CUDA(cudaGetLastError());
-    GRT_CUDA(cudaMemcpyAsync(out, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
+    double host[GRT_MAX_LAYERS + 1];
+    GRT_CUDA(cudaMemcpyAsync(host, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
     GRT_CUDA(cudaStreamSynchronize(st));
+    for (int i=0; i<num_levels; ++i) out[i] = (real_t)host[i];
     return 0;
 }
 
 int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
-                  double const *p_atm, double t_surf, double const *t_layers,
-                  double const *t_levels, double const *tau_gas_dev, double const *emis_dev,
-                  uint64_t first, uint64_t last, double *up, double *down)
+                  real_t const *p_atm, double t_surf, real_t const *t_layers,
+                  real_t const *t_levels, real_t const *tau_gas_dev, real_t const *emis_dev,
+                  uint64_t first, uint64_t last, real_t *up, real_t *down)
 {
     if (first > last || last >= nw) return fail("integration window outside the grid");
     if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
@@ -692,18 +720,14 @@ int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
                                                        tau_gas_dev, nullptr, emis_dev, buf,
                                                        buf + num_levels, first, last);
     GRT_CUDA(cudaGetLastError());
-    GRT_CUDA(cudaMemcpyAsync(up, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
-    GRT_CUDA(cudaMemcpyAsync(down, buf + num_levels, sizeof(double)*num_levels,
-                             cudaMemcpyDeviceToHost, st));
-    GRT_CUDA(cudaStreamSynchronize(st));
-    return 0;
+    return fetch_levels(st, buf, num_levels, up, down);
 }
 
 int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
-                  double const *p_atm, double const *tau_gas_dev, double mu_dir, double mu_dif,
-                  double const *alb_dir_dev, double const *alb_dif_dev, double tsi,
-                  double const *solar_dev, uint64_t first, uint64_t last, double *up,
-                  double *down)
+                  real_t const *p_atm, real_t const *tau_gas_dev, double mu_dir, double mu_dif,
+                  real_t const *alb_dir_dev, real_t const *alb_dif_dev, double tsi,
+                  real_t const *solar_dev, uint64_t first, uint64_t last, real_t *up,
+                  real_t *down)
 {
     if (first > last || last >= nw) return fail("integration window outside the grid");
     if (num_levels < 2 || num_levels > GRT_MAX_LAYERS + 1) return fail("bad level count");
@@ -717,11 +741,7 @@ int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
     GRT_TRY(launch_sw<true>(st, num_levels, w0, dw, nw, dens, nullptr, nullptr, tau_gas_dev,
                             mu_dir, mu_dif, alb_dir_dev, alb_dif_dev, tsi, solar_dev, buf,
                             buf + num_levels, first, last));
-    GRT_CUDA(cudaMemcpyAsync(up, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
-    GRT_CUDA(cudaMemcpyAsync(down, buf + num_levels, sizeof(double)*num_levels,
-                             cudaMemcpyDeviceToHost, st));
-    GRT_CUDA(cudaStreamSynchronize(st));
-    return 0;
+    return fetch_levels(st, buf, num_levels, up, down);
 }
 
 }  // extern "C"

@@ -48,8 +48,52 @@ struct SweepParams
     unsigned const *core_order;  // core kernel: thread -> record (molecule-major), or null
     LayerView lay;
     Tables tab;
-    double *tau;               // [layers][nw]
+    real_t *tau;               // [layers][nw] (float in the single build)
 };
+
+
+// ---- precision of the abscissa chain ---------------------------------------------------
+// Double build: the grid wavenumber, the line centre and the product with REPWID are double
+// and only the last step rounds to float (RFM_voigt.c:165 with fp_t = double).  Single build
+// (-DGRT_SINGLE, the reference's --enable-single-precision: fp_t = float,
+// utilities/src/floating_point_type.h:23-29): every one of those operations is a float
+// operation, in the same order -- in.w = s*wres + w0 (kernels.c:438), DWNO + i*WRES - WNOADJ,
+// times REPWID (RFM_voigt.c:165) -- so the float roundings of the reference's single build
+// (1e-4 cm-1 steps of the wavenumber at 2000 cm-1) are reproduced bit for bit; optical depth
+// is still accumulated in double and rounded to float once, at the store.
+#ifdef GRT_SINGLE
+typedef float wn_t;
+typedef float4 RecA;           // v, c, c*Y/sqrt(pi), -   (K1 writes the same 16 bytes)
+__device__ __forceinline__ float rec_v(RecA const a) { return a.x; }
+// c may be zero (absent species) or subnormal: a true conversion, once per line visit
+__device__ __forceinline__ double rec_c(RecA const a) { return (double)a.y; }
+__device__ __forceinline__ float rec_repwid(float4 const B) { return B.x; }
+#else
+typedef double wn_t;
+typedef double2 RecA;          // v, c
+__device__ __forceinline__ double rec_v(RecA const a) { return a.x; }
+__device__ __forceinline__ double rec_c(RecA const a) { return a.y; }
+__device__ __forceinline__ double rec_repwid(float4 const B) { return widen_positive(B.x); }
+#endif
+
+// fl(k*wres), fl(s*wres + w0) and fl(a + b) in the build's wavenumber type.
+__device__ __forceinline__ wn_t wn_index_times(int const k, wn_t const wres)
+{
+#ifdef GRT_SINGLE
+    return __fmul_rn((float)k, wres);
+#else
+    return __dmul_rn((double)k, wres);
+#endif
+}
+
+__device__ __forceinline__ wn_t wn_add(wn_t const a, wn_t const b)
+{
+#ifdef GRT_SINGLE
+    return __fadd_rn(a, b);
+#else
+    return __dadd_rn(a, b);
+#endif
+}
 
 
 // ---- 1-D bulk TMA + mbarrier plumbing (PTX ISA: cp.async.bulk, mbarrier) ------------
@@ -115,7 +159,7 @@ template <int PTS, bool TBL>
 struct GridCache
 {
     int s;
-    double t2[PTS];
+    wn_t t2[PTS];
 };
 
 #ifndef GRT_TBL_CACHE
@@ -134,7 +178,7 @@ __device__ __forceinline__ void reset_cache(GridCache<PTS, TBL> &gc)
 {
     gc.s = INT32_MIN;
 #pragma unroll
-    for (int j=0; j<PTS; ++j) gc.t2[j] = 0.;
+    for (int j=0; j<PTS; ++j) gc.t2[j] = (wn_t)0;
 }
 
 #if !GRT_TBL_CACHE
@@ -146,9 +190,11 @@ __device__ __forceinline__ void reset_cache(GridCache<PTS, true> &)
 
 // (float)((t2 - v)*REPWID): the last two double roundings and the float rounding of
 // RFM_voigt.c:165.
-__device__ __forceinline__ float abscissa_from(double const t2, double const v, double const repwid)
+__device__ __forceinline__ float abscissa_from(wn_t const t2, wn_t const v, wn_t const repwid)
 {
-#if GRT_DBG_NOF2F     // timing experiment only (wrong results): no FP64->FP32 conversion
+#ifdef GRT_SINGLE
+    return __fmul_rn(__fsub_rn(t2, v), repwid);
+#elif GRT_DBG_NOF2F     // timing experiment only (wrong results): no FP64->FP32 conversion
     return __int_as_float(__double2hiint(__dmul_rn(__dsub_rn(t2, v), repwid)));
 #else
     return __double2float_rn(__dmul_rn(__dsub_rn(t2, v), repwid));
@@ -165,8 +211,8 @@ struct TileCtx
     unsigned gmask;            // records of a staged batch that the lane's group walks
     int fsteps;
     int nw;
-    double w0;
-    double wres;
+    wn_t w0;
+    wn_t wres;
     double lane_pt;            // (double)(warp_base + sub)
     uint32_t iw_lane;          // shared-memory address of iw[warp_base + sub] (TBL kernels)
 };
@@ -175,6 +221,13 @@ struct TileCtx
 __device__ __forceinline__ double int_to_double(int const k)
 {
     return __dsub_rn(__hiloint2double(0x43300000, k), 4503599627370496.0);
+}
+
+__device__ __forceinline__ float lds_f32(uint32_t const addr)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
 }
 
 __device__ __forceinline__ double lds_f64(uint32_t const addr)
@@ -219,13 +272,20 @@ struct LineGrid<PTS, true, LN>
         {
             gc.s = fc;
             int const s = max(fc - t.fsteps, 0);
+#ifdef GRT_SINGLE
+            float const dwno = wn_add(wn_index_times(s, t.wres), t.w0);
+            uint32_t const a = t.iw_lane - 4u*(uint32_t)s;
+#pragma unroll
+            for (int j=0; j<PTS; ++j) gc.t2[j] = wn_add(dwno, lds_f32(a + (4u*LN)*(uint32_t)j));
+#else
             double const dwno = __dadd_rn(__dmul_rn(int_to_double(s), t.wres), t.w0);
             uint32_t const a = t.iw_lane - 8u*(uint32_t)s;
 #pragma unroll
             for (int j=0; j<PTS; ++j) gc.t2[j] = __dadd_rn(dwno, lds_f64(a + (8u*LN)*(uint32_t)j));
+#endif
         }
     }
-    __device__ __forceinline__ double t2(int const j) const
+    __device__ __forceinline__ wn_t t2(int const j) const
     {
         return gc.t2[j];
     }
@@ -234,17 +294,21 @@ struct LineGrid<PTS, true, LN>
 template <int PTS, int LN>
 struct LineGrid<PTS, true, LN>
 {
-    double dwno;
+    wn_t dwno;
     uint32_t a;
     __device__ __forceinline__ LineGrid(GridCache<PTS, true> &, TileCtx const &t, int const fc)
     {
         int const s = max(fc - t.fsteps, 0);
-        dwno = __dadd_rn(__dmul_rn(int_to_double(s), t.wres), t.w0);
-        a = t.iw_lane - 8u*(uint32_t)s;
+        dwno = wn_add(wn_index_times(s, t.wres), t.w0);
+        a = t.iw_lane - (uint32_t)sizeof(wn_t)*(uint32_t)s;
     }
-    __device__ __forceinline__ double t2(int const j) const
+    __device__ __forceinline__ wn_t t2(int const j) const
     {
+#ifdef GRT_SINGLE
+        return wn_add(dwno, lds_f32(a + (4u*LN)*(uint32_t)j));
+#else
         return __dadd_rn(dwno, lds_f64(a + (8u*LN)*(uint32_t)j));
+#endif
     }
 };
 #endif
@@ -260,6 +324,16 @@ struct LineGrid<PTS, false, LN>
         {
             gc.s = fc;
             int const s = max(fc - t.fsteps, 0);
+#ifdef GRT_SINGLE
+            float const dwno = wn_add(wn_index_times(s, t.wres), t.w0);
+            int const i0 = t.warp_base + t.sub - s;
+#pragma unroll
+            for (int j=0; j<PTS; ++j)
+            {
+                // out-of-window points (i < 0 on edge tiles) are predicated off by the caller
+                gc.t2[j] = wn_add(dwno, wn_index_times(i0 + LN*j, t.wres));
+            }
+#else
             double const sd = int_to_double(s);
             double const dwno = __dadd_rn(__dmul_rn(sd, t.wres), t.w0);
             double const i0 = __dsub_rn(t.lane_pt, sd);     // exact
@@ -268,9 +342,10 @@ struct LineGrid<PTS, false, LN>
             {
                 gc.t2[j] = __dadd_rn(dwno, __dmul_rn(i0 + (double)(LN*j), t.wres));
             }
+#endif
         }
     }
-    __device__ __forceinline__ double t2(int const j) const
+    __device__ __forceinline__ wn_t t2(int const j) const
     {
         return gc.t2[j];
     }
@@ -287,8 +362,8 @@ struct LineGrid<PTS, false, LN>
 enum LineClass { kClsNone = 0, kClsFast, kClsFarEdge, kClsR1, kClsNear, kClsLorentzFull,
                  kClsLorentzEdge };
 
-__device__ __forceinline__ f32x2 abscissa2(double const t2a, double const t2b, double const v,
-                                           double const repwid)
+__device__ __forceinline__ f32x2 abscissa2(wn_t const t2a, wn_t const t2b, wn_t const v,
+                                           wn_t const repwid)
 {
     return pack2(abscissa_from(t2a, v, repwid), abscissa_from(t2b, v, repwid));
 }
@@ -322,8 +397,67 @@ __device__ __forceinline__ void accumulate2(double &a0, double &a1, double const
 
 // kClsFast: the tile lies wholly inside the line's window and wholly in its far wing:
 // no predicates, PTS independent dependency chains in flight, two samples per packed op.
+#ifdef GRT_SINGLE
+// 1/q for q >= 1 (finite) without the reciprocal unit: integer seed (12.5 % off), three
+// Newton steps in packed FMAs -> 2^-22 relative.  The single build only needs K to ~1e-6
+// (the tolerance on tau is 1e-4 and the reference's own float sums are no better), so the
+// fast class alternates between this and MUFU.RCP to balance the XU pipe against the issue
+// slots (GRT_SP_SEED_PAIRS of every four point pairs take this form).
+__device__ __forceinline__ f32x2 rcp2_seeded(f32x2 const q)
+{
+    float qx, qy;
+    unpack2(q, qx, qy);
+    f32x2 r = pack2(__uint_as_float(0x7EF311C7u - __float_as_uint(qx)),
+                    __uint_as_float(0x7EF311C7u - __float_as_uint(qy)));
+    f32x2 const nq = pack2(-qx, -qy);
+    f32x2 const one = pack2(1.0f, 1.0f);
+    f32x2 e = fma2(nq, r, one);
+    r = fma2(r, e, r);
+    e = fma2(nq, r, one);
+    r = fma2(r, e, r);
+    e = fma2(nq, r, one);
+    return fma2(r, e, r);
+}
+
+__device__ __forceinline__ f32x2 rcp2_mufu(f32x2 const q)
+{
+    float qx, qy, rx, ry;
+    unpack2(q, qx, qy);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(qx));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(qy));
+    return pack2(rx, ry);
+}
+
+#ifndef GRT_SP_SEED_PAIRS
+#define GRT_SP_SEED_PAIRS 2
+#endif
+
+// kClsFast, single build: float abscissa chain (bit-identical to the reference's, see wn_t),
+// K*c = (c*Y/sqrt(pi))/(x*x + Y*Y) to float accuracy, float partial sums per staged batch
+// (flushed into the double accumulators by process_batch): no FP64 and no conversion in the
+// loop -- 4 packed float instructions + 2 reciprocals per two samples.
 template <int PTS, bool TBL, int LN>
-__device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileCtx const &t,
+__device__ __forceinline__ void line_fast(RecA const A, float4 const B, TileCtx const &t,
+                                          GridCache<PTS, TBL> &gc, f32x2 (&facc)[PTS/2])
+{
+    LineGrid<PTS, TBL, LN> const grid(gc, t, __float_as_int(B.w));
+    f32x2 const nv2 = pack2(-A.x, -A.x);
+    f32x2 const rep2 = pack2(B.x, B.x);
+    f32x2 const yq2 = pack2(B.y, B.y);
+    f32x2 const cy2 = pack2(A.z, A.z);
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        // fl(fl(t2 - v)*REPWID): a packed add feeding a packed multiply is not contracted
+        f32x2 const xi = mul2(add2(pack2(grid.t2(j), grid.t2(j + 1)), nv2), rep2);
+        f32x2 const q = fma2(xi, xi, yq2);
+        f32x2 const r = ((j/2) % 4 < GRT_SP_SEED_PAIRS) ? rcp2_seeded(q) : rcp2_mufu(q);
+        facc[j/2] = fma2(cy2, r, facc[j/2]);
+    }
+}
+#else
+template <int PTS, bool TBL, int LN>
+__device__ __forceinline__ void line_fast(RecA const A, float4 const B, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
     LineGrid<PTS, TBL, LN> const grid(gc, t, __float_as_int(B.w));
@@ -344,16 +478,19 @@ __device__ __forceinline__ void line_fast(double2 const A, float4 const B, TileC
     }
 }
 
+#endif
+
 // kClsR1: the tile lies wholly inside the window and every point has
 // XLIM1 <= |x| < XLIM0 (wide Doppler cores of the shortwave): region 1 only.
 template <int PTS, bool TBL, int LN>
-__device__ __forceinline__ void line_r1(double2 const A, float4 const B, float4 const C,
+__device__ __forceinline__ void line_r1(RecA const A, float4 const B, float4 const C,
                                         float4 const D, TileCtx const &t,
                                         GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
     // C = hw0, y, xlim0, xlim1;  D = a0, d0, d2, -
     LineGrid<PTS, TBL, LN> const grid(gc, t, __float_as_int(B.w));
-    double const repwid = widen_positive(B.x);
+    wn_t const repwid = rec_repwid(B);
+    double const cA = rec_c(A);
     f32x2 const y2 = pack2(C.y, C.y);
     f32x2 const a0 = pack2(D.x, D.x);
     f32x2 const d0 = pack2(D.y, D.y);
@@ -361,14 +498,14 @@ __device__ __forceinline__ void line_r1(double2 const A, float4 const B, float4 
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
-        accumulate2(acc[j], acc[j+1], A.y, region1_2(mul2_unfused(xi, xi), y2, a0, d0, d2));
+        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), rec_v(A), repwid);
+        accumulate2(acc[j], acc[j+1], cA, region1_2(mul2_unfused(xi, xi), y2, a0, d0, d2));
     }
 }
 
 // Pure-Lorentz lines (Y >= 70.55, RFM_voigt.c:97-106).  FULL: the window covers the tile.
 template <int PTS, bool TBL, int LN, bool FULL>
-__device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
+__device__ __forceinline__ void line_lorentz(RecA const A, float4 const B,
                                              TileCtx const &t, GridCache<PTS, TBL> &gc,
                                              double (&acc)[PTS])
 {
@@ -376,15 +513,16 @@ __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
-    double const repwid = widen_positive(B.x);
+    wn_t const repwid = rec_repwid(B);
+    double const cA = rec_c(A);
     int const f0 = t.warp_base + t.sub;
 #pragma unroll
     for (int j=0; j<PTS; ++j)
     {
         int const f = f0 + LN*j;
-        float const xi = abscissa_from(grid.t2(j), A.x, repwid);
+        float const xi = abscissa_from(grid.t2(j), rec_v(A), repwid);
         double const k = fast_rcp_of_float(xi*xi + B.y);
-        if (FULL || ((f >= s) && (f <= e))) acc[j] = fma(A.y, k, acc[j]);
+        if (FULL || ((f >= s) && (f <= e))) acc[j] = fma(cA, k, acc[j]);
     }
 }
 
@@ -392,14 +530,15 @@ __device__ __forceinline__ void line_lorentz(double2 const A, float4 const B,
 // kClsFarEdge: far wing only, but a window end falls inside the tile (kernels.c:435-437):
 // the far-wing arithmetic with a per-point window predicate.
 template <int PTS, bool TBL, int LN>
-__device__ __forceinline__ void line_far_edge(double2 const A, float4 const B, TileCtx const &t,
+__device__ __forceinline__ void line_far_edge(RecA const A, float4 const B, TileCtx const &t,
                                               GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
-    double const repwid = widen_positive(B.x);
+    wn_t const repwid = rec_repwid(B);
+    double const cA = rec_c(A);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
     int const f0 = t.warp_base + t.sub;
@@ -409,14 +548,14 @@ __device__ __forceinline__ void line_far_edge(double2 const A, float4 const B, T
         // a pair of chunks wholly beyond the window end: nothing to do (warp-uniform)
         int const cb = t.warp_base + LN*j;
         if (cb + 2*LN - 1 < s || cb > e) continue;
-        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), rec_v(A), repwid);
         f32x2 const k = far_wing2(mul2_unfused(xi, xi), yq2, yr2);
         float k0, k1;
         unpack2(k, k0, k1);
         int const fa = f0 + LN*j;
         int const fb = fa + LN;
-        if ((fa >= s) && (fa <= e)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
-        if ((fb >= s) && (fb <= e)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+        if ((fa >= s) && (fa <= e)) acc[j] = fma(cA, widen_positive(k0), acc[j]);
+        if ((fb >= s) && (fb <= e)) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
     }
 }
 
@@ -427,7 +566,7 @@ __device__ __forceinline__ void line_far_edge(double2 const A, float4 const B, T
 // Single-pair tiles (PTS = 2): far wing for both points, region 1 on top if the pair
 // reaches inside XLIM0 (warp-uniform test on the record's conservative half-width).
 template <int PTS, bool TBL, int LN>
-__device__ __forceinline__ void line_near_single(double2 const A, float4 const B, float4 const C,
+__device__ __forceinline__ void line_near_single(RecA const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
@@ -437,7 +576,8 @@ __device__ __forceinline__ void line_near_single(double2 const A, float4 const B
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
-    double const repwid = widen_positive(B.x);
+    wn_t const repwid = rec_repwid(B);
+    double const cA = rec_c(A);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
     int const f0 = t.warp_base + t.sub;
@@ -445,7 +585,7 @@ __device__ __forceinline__ void line_near_single(double2 const A, float4 const B
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        xi[j/2] = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        xi[j/2] = abscissa2(grid.t2(j), grid.t2(j + 1), rec_v(A), repwid);
         xq[j/2] = mul2_unfused(xi[j/2], xi[j/2]);
         k[j/2] = far_wing2(xq[j/2], yq2, yr2);
     }
@@ -478,8 +618,8 @@ __device__ __forceinline__ void line_near_single(double2 const A, float4 const B
             ina = ina && (far0 || (ax0 >= C.w));
             inb = inb && (far1 || (ax1 >= C.w));
         }
-        if (ina) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
-        if (inb) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+        if (ina) acc[j] = fma(cA, widen_positive(k0), acc[j]);
+        if (inb) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
     }
 }
 
@@ -488,7 +628,7 @@ __device__ __forceinline__ void line_near_single(double2 const A, float4 const B
 // warp-uniformly to far wing / region 1 / both (measured: -2.4 % on the config-2 step
 // against forming them inside the branches).
 template <int PTS, bool TBL, int LN>
-__device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B, float4 const C,
+__device__ __forceinline__ void line_near_pairs(RecA const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
@@ -498,7 +638,8 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
-    double const repwid = widen_positive(B.x);
+    wn_t const repwid = rec_repwid(B);
+    double const cA = rec_c(A);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
     f32x2 const y2 = pack2(C.y, C.y);
@@ -510,7 +651,7 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
 #pragma unroll
     for (int j=0; j<PTS; j+=2)
     {
-        xi[j/2] = abscissa2(grid.t2(j), grid.t2(j + 1), A.x, repwid);
+        xi[j/2] = abscissa2(grid.t2(j), grid.t2(j + 1), rec_v(A), repwid);
         xq[j/2] = mul2_unfused(xi[j/2], xi[j/2]);
     }
 #pragma unroll
@@ -529,15 +670,15 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
         {
             float k0, k1;
             unpack2(far_wing2(xq[j/2], yq2, yr2), k0, k1);
-            if (ina) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
-            if (inb) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+            if (ina) acc[j] = fma(cA, widen_positive(k0), acc[j]);
+            if (inb) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
         }
         else if (dhi < hw0in)
         {
             float k0, k1;
             unpack2(region1_2(xq[j/2], y2, a0, d0, d2), k0, k1);
-            if (ina && (fabsf(x0) >= C.w)) acc[j] = fma(A.y, widen_positive(k0), acc[j]);
-            if (inb && (fabsf(x1) >= C.w)) acc[j+1] = fma(A.y, widen_positive(k1), acc[j+1]);
+            if (ina && (fabsf(x0) >= C.w)) acc[j] = fma(cA, widen_positive(k0), acc[j]);
+            if (inb && (fabsf(x1) >= C.w)) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
         }
         else
         {
@@ -549,21 +690,21 @@ __device__ __forceinline__ void line_near_pairs(double2 const A, float4 const B,
                 bool const isfar = ax >= C.z;
                 bool const isr1 = !isfar && (ax >= C.w);
                 float const kf = isr1 ? kr0 : kf0;
-                if (ina && (isfar || isr1)) acc[j] = fma(A.y, widen_positive(kf), acc[j]);
+                if (ina && (isfar || isr1)) acc[j] = fma(cA, widen_positive(kf), acc[j]);
             }
             {
                 float const ax = fabsf(x1);
                 bool const isfar = ax >= C.z;
                 bool const isr1 = !isfar && (ax >= C.w);
                 float const kf = isr1 ? kr1 : kf1;
-                if (inb && (isfar || isr1)) acc[j+1] = fma(A.y, widen_positive(kf), acc[j+1]);
+                if (inb && (isfar || isr1)) acc[j+1] = fma(cA, widen_positive(kf), acc[j+1]);
             }
         }
     }
 }
 
 template <int PTS, bool TBL, int LN>
-__device__ __forceinline__ void line_near(double2 const A, float4 const B, float4 const C,
+__device__ __forceinline__ void line_near(RecA const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc, double (&acc)[PTS])
 {
@@ -572,17 +713,26 @@ __device__ __forceinline__ void line_near(double2 const A, float4 const B, float
 }
 
 
+__device__ __forceinline__ RecA lds_rec_a(uint32_t const addr)
+{
+#ifdef GRT_SINGLE
+    return lds_f32x4(addr);
+#else
+    return lds_f64x2(addr);
+#endif
+}
+
 // The four 16-byte vectors of a staged record.
 template <int NV>
 struct RecVec
 {
-    double2 A;         // v, c
+    RecA A;            // v, c (single build: v, c, c*Y/sqrt(pi))
     float4 B;          // repwid, yq, yrrtpi, fc
     float4 C;          // hw0, y, xlim0, xlim1
     float4 D;          // a0, d0, d2, hw1_hw0in
     __device__ __forceinline__ void load(uint32_t const addr)
     {
-        A = lds_f64x2(addr);
+        A = lds_rec_a(addr);
         B = lds_f32x4(addr + 16u);
         if (NV > 2)
         {
@@ -682,28 +832,48 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
     asm volatile("" : "+r"(sa));
     if (m)
     {
+#ifdef GRT_SINGLE
+        f32x2 facc[PTS/2];
+#pragma unroll
+        for (int j=0; j<PTS/2; ++j) facc[j] = 0ull;
+#define GRT_FAST_ACC facc
+#else
+#define GRT_FAST_ACC acc
+#endif
         int b = __ffs(m) - 1;
         m &= m - 1;
         // two records in flight, in alternating register sets (no copies between them)
-        double2 A0 = lds_f64x2(sa + 64u*(uint32_t)b);
+        RecA A0 = lds_rec_a(sa + 64u*(uint32_t)b);
         float4 B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
         for (;;)
         {
             bool more = m != 0;
             b = more ? __ffs(m) - 1 : b;
             m &= m - 1;
-            double2 const A1 = lds_f64x2(sa + 64u*(uint32_t)b);
+            RecA const A1 = lds_rec_a(sa + 64u*(uint32_t)b);
             float4 const B1 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
-            line_fast<PTS, TBL, LN>(A0, B0, t, gc, acc);
+            line_fast<PTS, TBL, LN>(A0, B0, t, gc, GRT_FAST_ACC);
             if (!more) break;
             more = m != 0;
             b = more ? __ffs(m) - 1 : b;
             m &= m - 1;
-            A0 = lds_f64x2(sa + 64u*(uint32_t)b);
+            A0 = lds_rec_a(sa + 64u*(uint32_t)b);
             B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
-            line_fast<PTS, TBL, LN>(A1, B1, t, gc, acc);
+            line_fast<PTS, TBL, LN>(A1, B1, t, gc, GRT_FAST_ACC);
             if (!more) break;
         }
+#undef GRT_FAST_ACC
+#ifdef GRT_SINGLE
+        // the batch's float partial sums (<= 32 lines) join the double accumulators
+#pragma unroll
+        for (int j=0; j<PTS; j+=2)
+        {
+            float f0, f1;
+            unpack2(facc[j/2], f0, f1);
+            acc[j] += (double)f0;
+            acc[j+1] += (double)f1;
+        }
+#endif
     }
     GRT_TM_END(kTmFast, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsR1) & t.gmask;
@@ -800,14 +970,14 @@ wing_sweep_kernel(SweepParams const p)
         for (int k=0; k<STG; ++k) mbar_init(mb0 + 8u*(uint32_t)k, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    double *iw = reinterpret_cast<double *>(smem_raw + Cfg::kRingBytes);
+    wn_t *iw = reinterpret_cast<wn_t *>(smem_raw + Cfg::kRingBytes);
     if (TBL)
     {
         // iw[k] = fl(k*wres): the product of RFM_voigt.c:165 for every sample index.
         int const entries = sweep_table_entries<PTS, LN>(p.fsteps);
         for (int k=threadIdx.x; k<entries; k+=kSweepThreads)
         {
-            iw[k] = __dmul_rn((double)k, p.wres);
+            iw[k] = wn_index_times(k, (wn_t)p.wres);
         }
         __syncthreads();
     }
@@ -854,10 +1024,10 @@ wing_sweep_kernel(SweepParams const p)
         tc.gmask = (LN == 32) ? 0xffffffffu : (((1u << (LN & 31)) - 1u) << ((lane/LN)*LN));
         tc.fsteps = p.fsteps;
         tc.nw = p.nw;
-        tc.w0 = p.w0;
-        tc.wres = p.wres;
+        tc.w0 = (wn_t)p.w0;
+        tc.wres = (wn_t)p.wres;
         tc.lane_pt = (double)(warp_base + tc.sub);
-        tc.iw_lane = smem_u32(iw) + 8u*(uint32_t)(warp_base + tc.sub);
+        tc.iw_lane = smem_u32(iw) + (uint32_t)sizeof(wn_t)*(uint32_t)(warp_base + tc.sub);
         GridCache<PTS, TBL> gc;
         reset_cache(gc);
 
@@ -973,7 +1143,7 @@ wing_sweep_kernel(SweepParams const p)
                 {
                     t += p.lay.cia[c*L + layer]*p.tab.cia[c][f];
                 }
-                p.tau[(size_t)layer*p.nw + f] = t;
+                p.tau[(size_t)layer*p.nw + f] = (real_t)t;
             }
         }
 #if GRT_DBG_TIMERS
@@ -1051,16 +1221,26 @@ core_sweep_kernel(SweepParams const p)
     float const xlim1 = C.w;
     bool const flagged = hw0 == kHwCoreOnly;
     if (!flagged && xlim1 <= 0.f) return;
+#ifdef GRT_SINGLE
+    float4 const A = *reinterpret_cast<float4 const *>(&rp->v);
+    wn_t const vline = A.x;
+    double const cline = (double)A.y;
+    wn_t const repwid = B.x;
+#else
     double2 const vc = *reinterpret_cast<double2 const *>(&rp->v);
-    double const repwid = (double)B.x;
+    wn_t const vline = vc.x;
+    double const cline = vc.y;
+    wn_t const repwid = (double)B.x;
+#endif
     int const F = p.fsteps;
     int const s = max(fc - F, 0);
     int const e = min(fc + F, p.nw - 1);
     // Half-width of the |x| < xlim1 window in grid points, rounded up generously.
-    double const hd = flagged ? (double)(2*F + 2) : (double)xlim1/(repwid*p.wres) + 2.;
+    double const hd = flagged ? (double)(2*F + 2) : (double)xlim1/((double)B.x*p.wres) + 2.;
     int const h = hd < (double)(2*F + 2) ? (int)hd : 2*F + 2;
-    double const dwno = __dadd_rn(__dmul_rn((double)s, p.wres), p.w0);
-    double *tau = p.tau + (size_t)layer*p.nw;
+    wn_t const wres = (wn_t)p.wres;
+    wn_t const dwno = wn_add(wn_index_times(s, wres), (wn_t)p.w0);
+    real_t *tau = p.tau + (size_t)layer*p.nw;
     VoigtLine line;
     voigt_line_init(line, y, xlim0, xlim1);
     for (int d=0; d<=h; ++d)
@@ -1070,11 +1250,11 @@ core_sweep_kernel(SweepParams const p)
         {
             int const f = side ? fc + d : fc - d;
             if ((side == 1 && d == 0) || f < s || f > e) continue;
-            float const xi = abscissa(dwno, (double)(f - s), p.wres, vc.x, repwid);
+            float const xi = abscissa_from(wn_add(dwno, wn_index_times(f - s, wres)), vline, repwid);
             if (flagged || fabsf(xi) < xlim1)
             {
                 double const k = voigt_line_eval(line, xi);
-                atomicAdd(&tau[f], vc.y*k);
+                atomicAdd(&tau[f], (real_t)(cline*k));
             }
         }
     }

@@ -23,6 +23,15 @@
 extern "C" {
 #endif
 
+/* Working precision of every data array below (fp_t of the host library:
+ * utilities/src/floating_point_type.h:23-29): double, or float when the stack is built
+ * with -DSINGLE_PRECISION (libgrtcode_sp.so + libgrt_sm100_sp.so).  Scalars stay double. */
+#ifdef SINGLE_PRECISION
+typedef float grt_real;
+#else
+typedef double grt_real;
+#endif
+
 #define GRT_SM100_ERR 12
 #define GRT_MAX_LAYERS 200   /* utilities/src/grtcode_config.h:52 */
 #define GRT_MAX_MOLS 53      /* gas-optics/src/molecules.h:86 */
@@ -64,27 +73,27 @@ int grt_gas_destroy(grt_gas *gas);
  * its partition-sum table q_table[num_iso][nt] on temperatures tmin + k [K]
  * (replaces inittips_d, gas-optics/src/tips2017.h:29). */
 int grt_gas_add_molecule(grt_gas *gas, int mol_id, double mass_g, int num_iso,
-                         uint64_t num_lines, int const *iso, double const *vnn,
-                         double const *snn, double const *yair, double const *yself,
-                         double const *en, double const *n_air, double const *delta,
+                         uint64_t num_lines, int const *iso, grt_real const *vnn,
+                         grt_real const *snn, grt_real const *yair, grt_real const *yself,
+                         grt_real const *en, grt_real const *n_air, grt_real const *delta,
                          double const *q_table, int tmin, int nt);
 /* Continuum / cross-section tables already resampled to the spectral grid
  * (water_vapor_continuum.c:32-122, ozone_continuum.c:31, cfcs.c:30,
  * collision_induced_absorption.c:29); each array has num_wpoints entries. */
-int grt_gas_set_h2o_continuum(grt_gas *gas, double const *s296, double const *ckds,
-                              double const *f296, double const *ckdf);
-int grt_gas_set_o3_continuum(grt_gas *gas, double const *cross_section);
-int grt_gas_add_cfc(grt_gas *gas, int cfc_id, double const *cross_section);
-int grt_gas_add_cia(grt_gas *gas, int species0, int species1, double const *cross_section);
+int grt_gas_set_h2o_continuum(grt_gas *gas, grt_real const *s296, grt_real const *ckds,
+                              grt_real const *f296, grt_real const *ckdf);
+int grt_gas_set_o3_continuum(grt_gas *gas, grt_real const *cross_section);
+int grt_gas_add_cfc(grt_gas *gas, int cfc_id, grt_real const *cross_section);
+int grt_gas_add_cia(grt_gas *gas, int species0, int species1, grt_real const *cross_section);
 
 /* One column: level pressure [atm] and temperature [K], mole fractions
  * x_mol[GRT_MAX_MOLS][num_levels] (row = HITRAN id - 1), x_cfc[GRT_MAX_CFCS][num_levels]
  * (row = cfc id), x_cia[GRT_NUM_CIA_SPECIES][num_levels]; writes (overwrites)
  * tau_dev[num_layers][num_wpoints].  method follows enum OpticalDepthMethod
  * (gas-optics/src/gas_optics.h:88-93): wavenumber_sweep (0), line_sweep (1), line_sample (2). */
-int grt_gas_optical_depth(grt_gas *gas, double const *p_atm, double const *t,
-                          double const *x_mol, double const *x_cfc, double const *x_cia,
-                          int method, double *tau_dev);
+int grt_gas_optical_depth(grt_gas *gas, grt_real const *p_atm, grt_real const *t,
+                          grt_real const *x_mol, grt_real const *x_cfc, grt_real const *x_cia,
+                          int method, grt_real *tau_dev);
 
 /* Counters of the last grt_gas_optical_depth call (bench/roofline bookkeeping):
  * out[0] = (line,layer) records inside the grid, out[1] = Voigt samples the
@@ -118,30 +127,30 @@ int grt_gas_class_histogram(grt_gas *gas, uint64_t out[8]);
 /* ---- Rayleigh + optics mixing: replaces rayleigh_scattering
  * (shortwave/src/rayleigh.c:100-144) and add_optics (utilities/src/optics.c:84-148). */
 int grt_rayleigh(int device, int num_layers, double w0, double dw, uint64_t num_wpoints,
-                 double const *p_atm, double *omega_dev, double *g_dev, double *tau_dev);
+                 grt_real const *p_atm, grt_real *omega_dev, grt_real *g_dev, grt_real *tau_dev);
 int grt_add_optics(int device, uint64_t num_values, int num_optics,
-                   double const *const *g_dev, double const *const *omega_dev,
-                   double const *const *tau_dev, double *g_out_dev, double *omega_out_dev,
-                   double *tau_out_dev);
+                   grt_real const *const *g_dev, grt_real const *const *omega_dev,
+                   grt_real const *const *tau_dev, grt_real *g_out_dev, grt_real *omega_out_dev,
+                   grt_real *tau_out_dev);
 
 /* ---- solvers: replace calculate_lw_fluxes (longwave/src/longwave.c:312-353) and
  * calculate_sw_fluxes (shortwave/src/shortwave.c:506-547).  Spectral fluxes are
  * written to device buffers [num_levels][num_wpoints]; the host library copies
  * them out. */
 int grt_lw_fluxes(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
-                  double t_surf, double const *t_layers, double const *t_levels,
-                  double const *tau_dev, double const *omega_dev, double const *emis_dev,
-                  double *flux_up_dev, double *flux_down_dev);
-int grt_sw_fluxes(int device, int num_levels, uint64_t num_wpoints, double const *omega_dev,
-                  double const *g_dev, double const *tau_dev, double mu_dir, double mu_dif,
-                  double const *alb_dir_dev, double const *alb_dif_dev, double tsi,
-                  double const *solar_dev, double *flux_up_dev, double *flux_down_dev);
+                  double t_surf, grt_real const *t_layers, grt_real const *t_levels,
+                  grt_real const *tau_dev, grt_real const *omega_dev, grt_real const *emis_dev,
+                  grt_real *flux_up_dev, grt_real *flux_down_dev);
+int grt_sw_fluxes(int device, int num_levels, uint64_t num_wpoints, grt_real const *omega_dev,
+                  grt_real const *g_dev, grt_real const *tau_dev, double mu_dir, double mu_dif,
+                  grt_real const *alb_dir_dev, grt_real const *alb_dif_dev, double tsi,
+                  grt_real const *solar_dev, grt_real *flux_up_dev, grt_real *flux_down_dev);
 
 /* ---- broadband integration: replaces the serial trapezoid loop of
  * output_fluxes (framework/src/driver.c:302-319), for every level at once:
  * out[level] = sum_{i<n-1} 0.5*(f[level][i] + f[level][i+1])*dw. */
 int grt_integrate_flux(int device, int num_levels, uint64_t num_wpoints, double dw,
-                       double const *flux_dev, double *out);
+                       grt_real const *flux_dev, grt_real *out);
 
 /* ---- fused column solvers for the drivers (no spectral arrays leave the GPU):
  * Rayleigh + optics mixing + solver + broadband integration in one kernel each;
@@ -150,14 +159,15 @@ int grt_integrate_flux(int device, int num_levels, uint64_t num_wpoints, double 
  * [first, last] is the index range of the trapezoid integration (0, num_wpoints - 1 for
  * the whole grid; a sub-range when the grid carries halo points of a spectral split). */
 int grt_lw_column(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
-                  double const *p_atm, double t_surf, double const *t_layers,
-                  double const *t_levels, double const *tau_gas_dev, double const *emis_dev,
-                  uint64_t first, uint64_t last, double *up, double *down);
+                  grt_real const *p_atm, double t_surf, grt_real const *t_layers,
+                  grt_real const *t_levels, grt_real const *tau_gas_dev,
+                  grt_real const *emis_dev, uint64_t first, uint64_t last, grt_real *up,
+                  grt_real *down);
 int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t num_wpoints,
-                  double const *p_atm, double const *tau_gas_dev, double mu_dir,
-                  double mu_dif, double const *alb_dir_dev, double const *alb_dif_dev,
-                  double tsi, double const *solar_dev, uint64_t first, uint64_t last,
-                  double *up, double *down);
+                  grt_real const *p_atm, grt_real const *tau_gas_dev, double mu_dir,
+                  double mu_dif, grt_real const *alb_dir_dev, grt_real const *alb_dif_dev,
+                  double tsi, grt_real const *solar_dev, uint64_t first, uint64_t last,
+                  grt_real *up, grt_real *down);
 
 /* ---- measurement helper: sustained FP64 / FP32 FMA throughput of this GPU
  * [TFLOP/s, FMA = 2 flop], the roofline denominator of the Voigt sweep. */
