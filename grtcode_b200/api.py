@@ -14,8 +14,17 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_HOST = os.path.join(HERE, "libgrtcode.so")
-LIB_CUDA = os.path.join(HERE, "libgrt_sm100.so")
+# Working precision of this PROCESS: GRT_PRECISION=single selects the libraries built with the
+# reference's -DSINGLE_PRECISION (fp_t = float, configure.ac:25-32): libgrtcode_sp.so +
+# libgrt_sm100_sp.so.  Every array that crosses the API then is float32.
+PRECISION = os.environ.get("GRT_PRECISION", "double")
+if PRECISION not in ("double", "single"):
+    raise ValueError(f"GRT_PRECISION={PRECISION!r}: expected 'double' or 'single'")
+SINGLE = PRECISION == "single"
+REAL = C.c_float if SINGLE else C.c_double
+DTYPE = np.float32 if SINGLE else np.float64
+LIB_HOST = os.path.join(HERE, "libgrtcode_sp.so" if SINGLE else "libgrtcode.so")
+LIB_CUDA = os.path.join(HERE, "libgrt_sm100_sp.so" if SINGLE else "libgrt_sm100.so")
 
 WAVENUMBER_SWEEP, LINE_SWEEP, LINE_SAMPLE = 0, 1, 2   # include/gas_optics.h
 NUM_MOLS, NUM_CFCS, NUM_CIAS, MAX_NUM_CIAS, DIR_PATH_LEN = 53, 21, 2, 3, 1024
@@ -49,7 +58,7 @@ class Shortwave(C.Structure):
 
 
 class SolarFlux(C.Structure):
-    _fields_ = [("grid", SpectralGrid), ("incident_flux", C.POINTER(C.c_double)),
+    _fields_ = [("grid", SpectralGrid), ("incident_flux", C.POINTER(REAL)),
                 ("n", C.c_uint64)]
 
 
@@ -67,7 +76,7 @@ class GasOpticsStruct(C.Structure):
                 ("sm100", C.c_void_p)]
 
 
-_dbl_p = C.POINTER(C.c_double)
+_dbl_p = C.POINTER(REAL)          # fp_t * of the loaded build
 _lib = None
 _cuda = None
 
@@ -117,31 +126,31 @@ def load():
     L.gas_optics_class_histogram.argtypes = [C.POINTER(GasOpticsStruct), C.POINTER(C.c_uint64)]
     L.gas_optics_debug_records.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, C.c_uint64,
                                            C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float),
-                                           _dbl_p]
+                                           C.POINTER(C.c_double)]
     L.gas_optics_debug_line_order.argtypes = [C.POINTER(GasOpticsStruct), C.c_uint64,
                                               C.POINTER(C.c_uint64)]
     L.rayleigh_scattering.argtypes = [C.POINTER(Optics), _dbl_p]
     L.create_longwave.argtypes = [C.POINTER(Longwave), C.c_int, C.POINTER(SpectralGrid),
                                   C.POINTER(C.c_int)]
     L.destroy_longwave.argtypes = [C.POINTER(Longwave)]
-    L.calculate_lw_fluxes.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), C.c_double, _dbl_p,
+    L.calculate_lw_fluxes.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), REAL, _dbl_p,
                                       _dbl_p, _dbl_p, _dbl_p, _dbl_p]
-    L.calculate_lw_column.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), _dbl_p, C.c_double,
+    L.calculate_lw_column.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), _dbl_p, REAL,
                                       _dbl_p, _dbl_p, _dbl_p, _dbl_p, _dbl_p]
     L.calculate_lw_column_window.argtypes = [C.POINTER(Longwave), C.POINTER(Optics), _dbl_p,
-                                             C.c_double, _dbl_p, _dbl_p, _dbl_p, C.c_uint64,
+                                             REAL, _dbl_p, _dbl_p, _dbl_p, C.c_uint64,
                                              C.c_uint64, _dbl_p, _dbl_p]
     L.calculate_sw_column_window.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), _dbl_p,
-                                             C.c_double, C.c_double, _dbl_p, _dbl_p, C.c_double,
+                                             REAL, REAL, _dbl_p, _dbl_p, REAL,
                                              _dbl_p, C.c_uint64, C.c_uint64, _dbl_p, _dbl_p]
     L.create_shortwave.argtypes = [C.POINTER(Shortwave), C.c_int, C.POINTER(SpectralGrid),
                                    C.POINTER(C.c_int)]
     L.destroy_shortwave.argtypes = [C.POINTER(Shortwave)]
-    L.calculate_sw_fluxes.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), C.c_double,
-                                      C.c_double, _dbl_p, _dbl_p, C.c_double, _dbl_p, _dbl_p,
+    L.calculate_sw_fluxes.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), REAL,
+                                      REAL, _dbl_p, _dbl_p, REAL, _dbl_p, _dbl_p,
                                       _dbl_p]
-    L.calculate_sw_column.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), _dbl_p, C.c_double,
-                                      C.c_double, _dbl_p, _dbl_p, C.c_double, _dbl_p, _dbl_p,
+    L.calculate_sw_column.argtypes = [C.POINTER(Shortwave), C.POINTER(Optics), _dbl_p, REAL,
+                                      REAL, _dbl_p, _dbl_p, REAL, _dbl_p, _dbl_p,
                                       _dbl_p]
     L.create_solar_flux.argtypes = [C.POINTER(SolarFlux), C.POINTER(SpectralGrid), C.c_char_p]
     L.destroy_solar_flux.argtypes = [C.POINTER(SolarFlux)]
@@ -177,12 +186,12 @@ def _check(rc: int, what: str):
 
 
 def _dp(a: np.ndarray):
-    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    assert a.dtype == DTYPE and a.flags["C_CONTIGUOUS"]
     return a.ctypes.data_as(_dbl_p)
 
 
 def _f64(a) -> np.ndarray:
-    return np.ascontiguousarray(a, dtype=np.float64)
+    return np.ascontiguousarray(a, dtype=DTYPE)
 
 
 def num_gpus() -> int:
@@ -248,7 +257,7 @@ class OpticsObject:
         out = []
         bufs = []
         for want in (tau, omega, g):
-            bufs.append(np.empty(self.shape) if want else None)
+            bufs.append(np.empty(self.shape, dtype=DTYPE) if want else None)
         _check(self.L.optical_properties(
             C.byref(self.o), *[(_dp(b) if b is not None else None) for b in bufs]),
             "optical_properties")
@@ -367,7 +376,8 @@ class GasOptics:
         v = np.empty(count, dtype=np.float64)
         _check(self.L.gas_optics_debug_records(
             C.byref(self.s), layer, first, count, rep.ctypes.data_as(C.POINTER(C.c_float)),
-            y.ctypes.data_as(C.POINTER(C.c_float)), _dp(v)), "gas_optics_debug_records")
+            y.ctypes.data_as(C.POINTER(C.c_float)), v.ctypes.data_as(C.POINTER(C.c_double))),
+            "gas_optics_debug_records")
         return rep, y, v
 
     def debug_line_order(self, count: int) -> np.ndarray:
@@ -403,8 +413,8 @@ class LongwaveSolver:
 
     def fluxes(self, optics: OpticsObject, t_surf, t_layers, t_levels, emis, out=None):
         """calculate_lw_fluxes; out = (up, down) preallocated float64[levels, n] arrays."""
-        up, dn = out if out is not None else (np.empty((self.num_levels, self.n)),
-                                              np.empty((self.num_levels, self.n)))
+        up, dn = out if out is not None else (np.empty((self.num_levels, self.n), dtype=DTYPE),
+                                              np.empty((self.num_levels, self.n), dtype=DTYPE))
         _check(self.L.calculate_lw_fluxes(C.byref(self.s), C.byref(optics.o), float(t_surf),
                                           _dp(_f64(t_layers)), _dp(_f64(t_levels)),
                                           _dp(_f64(emis)), _dp(up), _dp(dn)),
@@ -414,8 +424,8 @@ class LongwaveSolver:
     def column(self, gas: OpticsObject, p_mb, t_surf, t_layers, t_levels, emis, window=None):
         """Broadband fluxes of one column; window = (first, last) grid indices restricts
         the integration (spectral split with halo points)."""
-        up = np.empty(self.num_levels)
-        dn = np.empty(self.num_levels)
+        up = np.empty(self.num_levels, dtype=DTYPE)
+        dn = np.empty(self.num_levels, dtype=DTYPE)
         first, last = window if window is not None else (0, self.n - 1)
         _check(self.L.calculate_lw_column_window(
             C.byref(self.s), C.byref(gas.o), _dp(_f64(p_mb)), float(t_surf), _dp(_f64(t_layers)),
@@ -450,8 +460,8 @@ class ShortwaveSolver:
     def fluxes(self, optics: OpticsObject, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar,
                out=None):
         """calculate_sw_fluxes; out = (up, down) preallocated float64[levels, n] arrays."""
-        up, dn = out if out is not None else (np.empty((self.num_levels, self.n)),
-                                              np.empty((self.num_levels, self.n)))
+        up, dn = out if out is not None else (np.empty((self.num_levels, self.n), dtype=DTYPE),
+                                              np.empty((self.num_levels, self.n), dtype=DTYPE))
         _check(self.L.calculate_sw_fluxes(C.byref(self.s), C.byref(optics.o), float(mu_dir),
                                           float(mu_dif), _dp(_f64(alb_dir)), _dp(_f64(alb_dif)),
                                           float(tsi), _dp(_f64(solar)), _dp(up), _dp(dn)),
@@ -460,8 +470,8 @@ class ShortwaveSolver:
 
     def column(self, gas: OpticsObject, p_mb, mu_dir, mu_dif, alb_dir, alb_dif, tsi, solar,
                window=None):
-        up = np.empty(self.num_levels)
-        dn = np.empty(self.num_levels)
+        up = np.empty(self.num_levels, dtype=DTYPE)
+        dn = np.empty(self.num_levels, dtype=DTYPE)
         if alb_dir is None:
             p1 = p2 = p3 = None
         else:
@@ -496,7 +506,7 @@ def solar_flux(grid: SpectralGrid, path: str) -> np.ndarray:
 
 
 def integrate_fluxes(device: int, num_levels: int, grid: SpectralGrid, flux_dev_ptr: int):
-    out = np.empty(num_levels)
+    out = np.empty(num_levels, dtype=DTYPE)
     _check(load().integrate_fluxes(device, num_levels, C.byref(grid), C.c_void_p(flux_dev_ptr),
                                    _dp(out)), "integrate_fluxes")
     return out
@@ -504,7 +514,7 @@ def integrate_fluxes(device: int, num_levels: int, grid: SpectralGrid, flux_dev_
 
 def heating_rates(p_mb, up, down) -> np.ndarray:
     p = _f64(p_mb)
-    rate = np.empty(len(p) - 1)
+    rate = np.empty(len(p) - 1, dtype=DTYPE)
     _check(load().heating_rates(len(p), _dp(p), _dp(_f64(up)), _dp(_f64(down)), _dp(rate)),
            "heating_rates")
     return rate

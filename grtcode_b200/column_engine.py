@@ -20,11 +20,12 @@ from . import api as _api
 
 
 def pinned(n: int, fill: float) -> np.ndarray:
-    """float64[n] in page-locked host memory (cudaMallocHost through the C ABI)."""
+    """fp_t[n] (float64, or float32 in the single-precision build) in page-locked host memory
+    (cudaMallocHost through the C ABI)."""
     ptr = C.c_void_p()
-    if _api.cuda_layer().grt_host_alloc(C.byref(ptr), 8*n) != 0:
+    if _api.cuda_layer().grt_host_alloc(C.byref(ptr), C.sizeof(_api.REAL)*n) != 0:
         raise RuntimeError("grt_host_alloc failed")
-    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,))
+    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(_api.REAL)), shape=(n,))
     arr[:] = fill
     return arr
 
@@ -44,6 +45,7 @@ class ColumnEngine:
         api = _api
         api.load()
         self.device = device
+        self.real_bytes = C.sizeof(api.REAL)
         self.levels = len(column.p)
         self.parts = []
         for band in bands:
@@ -102,7 +104,7 @@ class ColumnEngine:
         for part in self.parts:
             self._set_abundances(part, col)
             part["go"].optical_depth(col.p, col.t, part["gas"])
-            h2d += 8*self.levels*(2 + 53 + 21 + 2)
+            h2d += self.real_bytes*self.levels*(2 + 53 + 21 + 2)
             n = part["n"]
             if "ray" not in part:
                 part["ray"] = api.OpticsObject(self.levels - 1, part["grid"], self.device)
@@ -114,13 +116,13 @@ class ColumnEngine:
             if part["band"].name.startswith("lw"):
                 part["emis"][:] = col.emissivity
                 part["solver"].fluxes(tot, col.t_surf, col.t_layer, col.t, part["emis"], out=dst)
-                h2d += 8*n
+                h2d += self.real_bytes*n
             else:
                 part["alb"][:] = col.albedo
                 part["solver"].fluxes(tot, col.mu0, 0.5, part["alb"], part["alb"], col.tsi,
                                       part["solar"], out=dst)
-                h2d += 3*8*n
-            d2h += 2*8*self.levels*n
+                h2d += 3*self.real_bytes*n
+            d2h += 2*self.real_bytes*self.levels*n
             tot.close()
             out[part["band"].name[:2]] = dst
         self.h2d_ref, self.d2h_ref = h2d, d2h
@@ -140,7 +142,7 @@ class ColumnEngine:
             go = part["go"]
             self._set_abundances(part, col)
             go.optical_depth(col.p, col.t, part["gas"])
-            h2d += 8*self.levels*(2 + 53 + 21 + 2)
+            h2d += self.real_bytes*self.levels*(2 + 53 + 21 + 2)
             name = part["band"].name[:2]
             if name == "lw":
                 send = upload_surface
@@ -150,7 +152,7 @@ class ColumnEngine:
                 up, dn = part["solver"].column(part["gas"], col.p, col.t_surf, col.t_layer,
                                                col.t, part["emis"] if send else None,
                                                window=part["window"])
-                h2d += 8*part["n"] if send else 0
+                h2d += self.real_bytes*part["n"] if send else 0
             else:
                 send = upload_surface
                 if part["alb"][0] != col.albedo:
@@ -160,7 +162,7 @@ class ColumnEngine:
                 up, dn = part["solver"].column(part["gas"], col.p, col.mu0, 0.5, alb, alb,
                                                col.tsi, part["solar"] if send else None,
                                                window=part["window"])
-                h2d += 2*8*part["n"] if send else 0
+                h2d += 2*self.real_bytes*part["n"] if send else 0
             # the sweep kernels were only enqueued by calculate_optical_depth: their event
             # times are read after the solver call, which synchronised the stream
             st = go.stats()
@@ -168,7 +170,7 @@ class ColumnEngine:
             out[name] = (up, dn, st)
         self.launches = launches
         self.h2d = h2d
-        self.d2h = 2*2*8*self.levels + 2*32
+        self.d2h = 2*2*self.real_bytes*self.levels + 2*32
         self.last = out
         return out
 

@@ -11,6 +11,21 @@
 #include "return_codes.h"
 #include "verbosity.h"
 
+/* Math functions of the working precision (utilities/src/grtcode_config.h:25-47). */
+#ifdef SINGLE_PRECISION
+#define GRT_EXP expf
+#define GRT_POW powf
+#define GRT_SQRT sqrtf
+#define GRT_ABS fabsf
+#define GRT_LOG logf
+#else
+#define GRT_EXP exp
+#define GRT_POW pow
+#define GRT_SQRT sqrt
+#define GRT_ABS fabs
+#define GRT_LOG log
+#endif
+
 void grt_error_reset(void);
 void grt_error_append(char const *text);
 void grt_error_frame(char const *file, int line);

@@ -109,8 +109,12 @@ static int parse_record(char const *rec, int *iso, fp_t *vnn, fp_t *snn, fp_t *y
                         fp_t *yself, fp_t *en, fp_t *n, fp_t *d)
 {
     int rc = parse_iso(rec[2], iso);
-    if (rc == GRTCODE_SUCCESS) rc = field_double(rec, 3, 12, vnn);
-    if (rc == GRTCODE_SUCCESS) rc = field_double(rec, 15, 10, snn);
+    /* v and S: lp.vnn[n] = (fp_t)(val.d) (parse_HITRAN_file.c:319-324) */
+    double dv = 0., ds = 0.;
+    if (rc == GRTCODE_SUCCESS) rc = field_double(rec, 3, 12, &dv);
+    if (rc == GRTCODE_SUCCESS) rc = field_double(rec, 15, 10, &ds);
+    *vnn = (fp_t)dv;
+    *snn = (fp_t)ds;
     if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 35, 5, 5, yair);
     if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 40, 5, 6, yself);
     if (rc == GRTCODE_SUCCESS) rc = field_float(rec, 45, 10, 7, en);
@@ -443,8 +447,8 @@ int parse_hitran_file(LineParams_t * const out, char const * const filepath, int
         lp.n[k] = t->n[i];
         lp.d[k] = t->d[i];
         /* Scale the raw intensity (parse_HITRAN_file.c:372-384). */
-        lp.snn[k] = t->snn[i]*(grt_tips_q(mol_id, tref, lp.iso[k])/(exp(c2*lp.en[k]/tref)*
-                    (1.f - exp(c2*lp.vnn[k]/tref))));
+        lp.snn[k] = t->snn[i]*((fp_t)grt_tips_q(mol_id, tref, lp.iso[k])/
+                    (GRT_EXP(c2*lp.en[k]/tref)*(1.f - GRT_EXP(c2*lp.vnn[k]/tref))));
         ++k;
     }
     lp.num_lines = n;

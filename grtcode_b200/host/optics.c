@@ -59,9 +59,9 @@ int add_optics(Optics_t const * const * const optics, int const num_optics,
     }
     Optics_t const *first = optics[0];
     REQUIRE_PTR(first);
-    double const *g[8];
-    double const *omega[8];
-    double const *tau[8];
+    fp_t const *g[8];
+    fp_t const *omega[8];
+    fp_t const *tau[8];
     int j;
     for (j=0; j<num_optics; ++j)
     {

@@ -22,9 +22,16 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 HOST_ONLY = -1
 LINE_SAMPLE = 2  # gas_optics.h:88-93
+# Working precision of this process (see grtcode_b200/api.py): GRT_PRECISION=single loads the
+# reference compiled with its own -DSINGLE_PRECISION (fp_t = float, configure.ac:25-32).
+SINGLE = os.environ.get("GRT_PRECISION", "double") == "single"
+REAL = C.c_float if SINGLE else C.c_double
+DTYPE = np.float32 if SINGLE else np.float64
 
 
 def lib_path(fast: bool = False) -> str:
+    if SINGLE:
+        return os.path.join(HERE, "_ref", "libgrtcode_ref_sp.so")
     return os.path.join(HERE, "_ref", "libgrtcode_ref_fast.so" if fast else "libgrtcode_ref.so")
 
 
@@ -37,9 +44,9 @@ class SpectralGrid(C.Structure):
 
 
 class Optics(C.Structure):
-    _fields_ = [("device", C.c_int), ("g", C.POINTER(C.c_double)), ("grid", SpectralGrid),
-                ("num_layers", C.c_int), ("omega", C.POINTER(C.c_double)),
-                ("tau", C.POINTER(C.c_double))]
+    _fields_ = [("device", C.c_int), ("g", C.POINTER(REAL)), ("grid", SpectralGrid),
+                ("num_layers", C.c_int), ("omega", C.POINTER(REAL)),
+                ("tau", C.POINTER(REAL))]
 
 
 class Longwave(C.Structure):
@@ -55,27 +62,27 @@ class Shortwave(C.Structure):
 
 
 class SolarFlux(C.Structure):
-    _fields_ = [("grid", SpectralGrid), ("incident_flux", C.POINTER(C.c_double)),
+    _fields_ = [("grid", SpectralGrid), ("incident_flux", C.POINTER(REAL)),
                 ("n", C.c_uint64)]
 
 
 class LineShapeInputs(C.Structure):
-    _fields_ = [("w", C.c_double), ("num_wpoints", C.c_uint64), ("wres", C.c_double),
-                ("line_center", C.c_double), ("lorentz_hwhm", C.c_double),
-                ("doppler_hwhm", C.c_double), ("eta", C.c_double)]
+    _fields_ = [("w", REAL), ("num_wpoints", C.c_uint64), ("wres", REAL),
+                ("line_center", REAL), ("lorentz_hwhm", REAL),
+                ("doppler_hwhm", REAL), ("eta", REAL)]
 
 
 class SpectralBins(C.Structure):
-    _fields_ = [("num_layers", C.c_int), ("w0", C.c_double), ("wres", C.c_double),
-                ("num_wpoints", C.c_uint64), ("n", C.c_uint64), ("width", C.c_double),
+    _fields_ = [("num_layers", C.c_int), ("w0", REAL), ("wres", REAL),
+                ("num_wpoints", C.c_uint64), ("n", C.c_uint64), ("width", REAL),
                 ("isize", C.c_uint64), ("ppb", C.c_int), ("do_interp", C.c_int),
                 ("last_ppb", C.c_int), ("do_last_interp", C.c_int), ("w", C.c_void_p),
                 ("tau", C.c_void_p), ("l", C.c_void_p), ("r", C.c_void_p), ("device", C.c_int)]
 
 
 def _dp(a: np.ndarray):
-    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
-    return a.ctypes.data_as(C.POINTER(C.c_double))
+    assert a.dtype == DTYPE and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.POINTER(REAL))
 
 
 class RefError(RuntimeError):
@@ -97,21 +104,21 @@ class Ref:
         except OSError:
             pass
         L = self.lib
-        L.Q.restype = C.c_double
-        L.Q.argtypes = [C.c_int, C.c_double, C.c_int]
-        L.rfm_voigt_line_shape.argtypes = [LineShapeInputs, C.POINTER(C.c_double)]
+        L.Q.restype = REAL
+        L.Q.argtypes = [C.c_int, REAL, C.c_int]
+        L.rfm_voigt_line_shape.argtypes = [LineShapeInputs, C.POINTER(REAL)]
         L.calc_optical_depth_line_sample.argtypes = [
-            C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
-            C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), SpectralBins,
-            C.POINTER(C.c_double), C.c_void_p, C.c_void_p]
+            C.c_uint64, C.c_int, C.POINTER(REAL), C.POINTER(REAL),
+            C.POINTER(REAL), C.POINTER(REAL), C.POINTER(REAL), SpectralBins,
+            C.POINTER(REAL), C.c_void_p, C.c_void_p]
         L.calculate_lw_fluxes.argtypes = [
-            C.POINTER(Longwave), C.POINTER(Optics), C.c_double, C.POINTER(C.c_double),
-            C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
-            C.POINTER(C.c_double)]
+            C.POINTER(Longwave), C.POINTER(Optics), REAL, C.POINTER(REAL),
+            C.POINTER(REAL), C.POINTER(REAL), C.POINTER(REAL),
+            C.POINTER(REAL)]
         L.calculate_sw_fluxes.argtypes = [
-            C.POINTER(Shortwave), C.POINTER(Optics), C.c_double, C.c_double,
-            C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double),
-            C.POINTER(C.c_double), C.POINTER(C.c_double)]
+            C.POINTER(Shortwave), C.POINTER(Optics), REAL, REAL,
+            C.POINTER(REAL), C.POINTER(REAL), REAL, C.POINTER(REAL),
+            C.POINTER(REAL), C.POINTER(REAL)]
         L.create_spectral_grid.argtypes = [C.POINTER(SpectralGrid), C.c_double, C.c_double,
                                            C.c_double]
         L.add_molecule.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
@@ -142,7 +149,7 @@ class Ref:
 
     def voigt(self, w: float, n: int, wres: float, center: float, gamma: float,
               alpha: float) -> np.ndarray:
-        k = np.zeros(n)
+        k = np.zeros(n, dtype=DTYPE)
         v = LineShapeInputs(w, n, wres, center, gamma, alpha, 0.)
         self.check(self.lib.rfm_voigt_line_shape(v, _dp(k)), "rfm_voigt_line_shape")
         return k
@@ -153,7 +160,7 @@ class Ref:
     def line_sample(self, v, s, gamma, alpha, ns, w0, wres, n) -> np.ndarray:
         """calc_optical_depth_line_sample (kernels.c:410) on [layers, lines] arrays."""
         layers, lines = v.shape
-        tau = np.zeros((layers, n))
+        tau = np.zeros((layers, n), dtype=DTYPE)
         bins = SpectralBins()
         bins.num_layers = layers
         bins.w0 = w0
@@ -229,14 +236,14 @@ class RefGasOptics:
         self.ref.check(self.ref.lib.add_cia(self.buf, a, b, path.encode()), "add_cia")
 
     def set_ppmv(self, kind: str, ident: int, ppmv: np.ndarray):
-        ppmv = np.ascontiguousarray(ppmv, dtype=np.float64)
+        ppmv = np.ascontiguousarray(ppmv, dtype=DTYPE)
         fn = getattr(self.ref.lib, {"mol": "set_molecule_ppmv", "cfc": "set_cfc_ppmv",
                                     "cia": "set_cia_ppmv"}[kind])
         self.ref.check(fn(self.buf, C.c_int(ident), _dp(ppmv)), f"set_{kind}_ppmv")
 
     def optical_depth(self, p_mb: np.ndarray, t: np.ndarray, optics: RefOptics):
-        p = np.ascontiguousarray(p_mb, dtype=np.float64)
-        tt = np.ascontiguousarray(t, dtype=np.float64)
+        p = np.ascontiguousarray(p_mb, dtype=DTYPE)
+        tt = np.ascontiguousarray(t, dtype=DTYPE)
         self.ref.check(self.ref.lib.calculate_optical_depth(
             self.buf, _dp(p), _dp(tt), C.byref(optics.o)), "calculate_optical_depth")
 
@@ -247,7 +254,7 @@ class RefGasOptics:
 
 
 def rayleigh(ref: Ref, optics: RefOptics, p_mb: np.ndarray):
-    p = np.ascontiguousarray(p_mb, dtype=np.float64)
+    p = np.ascontiguousarray(p_mb, dtype=DTYPE)
     ref.check(ref.lib.rayleigh_scattering(C.byref(optics.o), _dp(p)), "rayleigh_scattering")
 
 
@@ -269,11 +276,11 @@ def lw_fluxes(ref: Ref, optics: RefOptics, t_surf, t_layers, t_levels, emis):
     dev = C.c_int(HOST_ONLY)
     ref.check(ref.lib.create_longwave(C.byref(lw), levels, C.byref(optics.o.grid),
                                       C.byref(dev)), "create_longwave")
-    up = np.zeros((levels, n))
-    dn = np.zeros((levels, n))
-    tl = np.ascontiguousarray(t_layers, dtype=np.float64)
-    tv = np.ascontiguousarray(t_levels, dtype=np.float64)
-    em = np.ascontiguousarray(emis, dtype=np.float64)
+    up = np.zeros((levels, n), dtype=DTYPE)
+    dn = np.zeros((levels, n), dtype=DTYPE)
+    tl = np.ascontiguousarray(t_layers, dtype=DTYPE)
+    tv = np.ascontiguousarray(t_levels, dtype=DTYPE)
+    em = np.ascontiguousarray(emis, dtype=DTYPE)
     ref.check(ref.lib.calculate_lw_fluxes(C.byref(lw), C.byref(optics.o), float(t_surf),
                                           _dp(tl), _dp(tv), _dp(em), _dp(up), _dp(dn)),
               "calculate_lw_fluxes")
@@ -287,11 +294,11 @@ def sw_fluxes(ref: Ref, optics: RefOptics, mu_dir, mu_dif, alb_dir, alb_dif, tsi
     dev = C.c_int(HOST_ONLY)
     ref.check(ref.lib.create_shortwave(C.byref(sw), levels, C.byref(optics.o.grid),
                                        C.byref(dev)), "create_shortwave")
-    up = np.zeros((levels, n))
-    dn = np.zeros((levels, n))
-    a1 = np.ascontiguousarray(alb_dir, dtype=np.float64)
-    a2 = np.ascontiguousarray(alb_dif, dtype=np.float64)
-    so = np.ascontiguousarray(solar, dtype=np.float64)
+    up = np.zeros((levels, n), dtype=DTYPE)
+    dn = np.zeros((levels, n), dtype=DTYPE)
+    a1 = np.ascontiguousarray(alb_dir, dtype=DTYPE)
+    a2 = np.ascontiguousarray(alb_dif, dtype=DTYPE)
+    so = np.ascontiguousarray(solar, dtype=DTYPE)
     ref.check(ref.lib.calculate_sw_fluxes(C.byref(sw), C.byref(optics.o), float(mu_dir),
                                           float(mu_dif), _dp(a1), _dp(a2), float(tsi), _dp(so),
                                           _dp(up), _dp(dn)), "calculate_sw_fluxes")
@@ -309,4 +316,5 @@ def solar_flux(ref: Ref, grid: SpectralGrid, path: str) -> np.ndarray:
 
 def broadband(flux: np.ndarray, dw: float) -> np.ndarray:
     """Trapezoid of framework/src/driver.c:302-319, per level (numpy pairwise sum)."""
+    flux = np.asarray(flux, dtype=np.float64)
     return np.sum(0.5*(flux[:, :-1] + flux[:, 1:])*dw, axis=1)
