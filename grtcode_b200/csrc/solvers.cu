@@ -14,6 +14,7 @@
 // Rayleigh/total optics or spectral fluxes: they mix on the fly and reduce the
 // fluxes to broadband values inside the kernel.
 #include <cmath>
+#include <cstdint>
 #include <cstdlib>
 #include "common.cuh"
 
@@ -519,6 +520,78 @@ integrate_kernel(uint64_t const nw, double const dw, real_t const *flux, double 
 }
 
 
+// ---- allocation-free broadband integration (grt_integrate_flux_noalloc) -----------------
+// The same trapezoid sums as integrate_kernel for callers that must not allocate (CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc): a two-stage reduction whose
+// per-block partial sums live in a file-scope device array instead of a cudaMalloc'ed
+// buffer.  Every GPU that loads the library holds the array until the process exits
+// (GRT_NOALLOC_SCRATCH_BYTES, about 100 KB).  All calls on a device share it: calls that
+// overlap on the GPU (different streams, concurrent graphs) race.  Nothing has to start at
+// zero: the first stage overwrites every slot the second stage reads, so the previous call's
+// contents are never seen.
+constexpr int kNoAllocBlocks = GRT_NOALLOC_BLOCKS;
+constexpr int kNoAllocMaxLevels = GRT_NOALLOC_MAX_LEVELS;
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocMaxLevels*kNoAllocBlocks];
+static_assert(sizeof(double)*kNoAllocMaxLevels*kNoAllocBlocks == GRT_NOALLOC_SCRATCH_BYTES,
+              "scratch size stated in grt_sm100.h");
+
+// Stage 1: block (b, level) sums its grid-stride share of the level's trapezoid intervals in a
+// fixed order (no atomics) and writes partial[level*gridDim.x + b].
+__global__ void __launch_bounds__(256)
+integrate_partial_kernel(uint64_t const nw, double const dw, real_t const *flux, double *partial)
+{
+    __shared__ double warp_sums[8];
+    int const level = blockIdx.y;
+    real_t const *f = flux + (size_t)level*nw;
+    double acc = 0.;
+    for (uint64_t i=(uint64_t)blockIdx.x*blockDim.x + threadIdx.x; i + 1 < nw;
+         i += (uint64_t)gridDim.x*blockDim.x)
+    {
+        acc += 0.5*((double)f[i] + (double)f[i+1])*dw;
+    }
+    for (int o=16; o>0; o>>=1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double s = 0.;
+        for (int k=0; k<(int)(blockDim.x >> 5); ++k) s += warp_sums[k];
+        partial[(size_t)level*gridDim.x + blockIdx.x] = s;
+    }
+}
+
+// Stage 2: one warp per level adds the level's partial sums and stores the result in the
+// caller's output array.
+__global__ void __launch_bounds__(32)
+integrate_finish_kernel(int const num_blocks, double const *partial, real_t *out)
+{
+    int const level = blockIdx.x;
+    double acc = 0.;
+    for (int k=threadIdx.x; k<num_blocks; k+=32) acc += partial[(size_t)level*num_blocks + k];
+    for (int o=16; o>0; o>>=1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if (threadIdx.x == 0) out[level] = (real_t)acc;
+}
+
+// Device address of g_noalloc_scratch on each device: in host code the array's name is only
+// a stand-in for the symbol, so the address is looked up once per device, with that device
+// current (stream_of() has made it so), and passed to the kernels as an ordinary pointer.
+static double *g_noalloc_ptr[64];
+
+static int noalloc_scratch(int device, double **ptr)
+{
+    if (device < 0 || device >= 64) return fail("device id %d out of range", device);
+    if (g_noalloc_ptr[device] == nullptr)
+    {
+        double *p = nullptr;
+        GRT_CUDA(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch));
+        if (p == nullptr) return fail("cudaGetSymbolAddress returned a null scratch address");
+        g_noalloc_ptr[device] = p;
+    }
+    *ptr = g_noalloc_ptr[device];
+    return 0;
+}
+
+
 // Per-device scratch for broadband results.
 static double *g_out_buf[64];
 
@@ -695,6 +768,32 @@ int grt_integrate_flux(int device, int num_levels, uint64_t nw, double dw,
     GRT_CUDA(cudaMemcpyAsync(host, buf, sizeof(double)*num_levels, cudaMemcpyDeviceToHost, st));
     GRT_CUDA(cudaStreamSynchronize(st));
     for (int i=0; i<num_levels; ++i) out[i] = (real_t)host[i];
+    return 0;
+}
+
+int grt_integrate_flux_noalloc(int device, int num_levels, uint64_t nw, double dw,
+                               real_t const *flux_dev, real_t *out_dev)
+{
+    if (flux_dev == nullptr || out_dev == nullptr) return fail("null device pointer");
+    if (num_levels < 1) return fail("bad level count %d", num_levels);
+    if (num_levels > kNoAllocMaxLevels)
+    {
+        return fail("grt_integrate_flux_noalloc: %d levels exceed the static scratch array "
+                    "(GRT_NOALLOC_MAX_LEVELS = %d); use grt_integrate_flux", num_levels,
+                    kNoAllocMaxLevels);
+    }
+    if (nw < 1 || nw > (uint64_t)INT32_MAX) return fail("spectral grid size unsupported");
+    cudaStream_t st;
+    GRT_TRY(stream_of(device, &st));          // makes `device` current
+    double *scratch;
+    GRT_TRY(noalloc_scratch(device, &scratch));
+    unsigned bx = (unsigned)((nw + 255)/256);
+    if (bx > (unsigned)kNoAllocBlocks) bx = (unsigned)kNoAllocBlocks;
+    if (bx < 1) bx = 1;
+    integrate_partial_kernel<<<dim3(bx, (unsigned)num_levels), 256, 0, st>>>(nw, dw, flux_dev,
+                                                                             scratch);
+    integrate_finish_kernel<<<(unsigned)num_levels, 32, 0, st>>>((int)bx, scratch, out_dev);
+    GRT_CUDA(cudaGetLastError());
     return 0;
 }
 

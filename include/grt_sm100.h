@@ -152,6 +152,26 @@ int grt_sw_fluxes(int device, int num_levels, uint64_t num_wpoints, grt_real con
 int grt_integrate_flux(int device, int num_levels, uint64_t num_wpoints, double dw,
                        grt_real const *flux_dev, grt_real *out);
 
+/* ---- allocation-free broadband integration.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  The same sums as
+ * grt_integrate_flux, out_dev[level] = sum_{i<n-1} 0.5*(f[level][i] + f[level][i+1])*dw, as a
+ * two-stage reduction whose scratch (per-block partial sums) is a file-scope
+ * `static __device__` array of GRT_NOALLOC_SCRATCH_BYTES that every GPU loading the library
+ * holds until exit.  The call allocates and frees nothing and does not synchronise: it
+ * enqueues two kernels on the library stream of `device`; out_dev (DEVICE memory,
+ * num_levels values, caller-owned like flux_dev) is complete for any later work on that
+ * stream (grt_copy_to_host synchronises).  num_levels > GRT_NOALLOC_MAX_LEVELS is rejected
+ * with GRT_SM100_ERR and a message (use grt_integrate_flux).  All calls on a device share
+ * the one scratch array: calls that overlap on the GPU race; calls ordered on the library
+ * stream do not.  The first call per device looks up the array's device address
+ * (cudaGetSymbolAddress) and, if no other call has yet, creates the library stream. */
+#define GRT_NOALLOC_MAX_LEVELS (GRT_MAX_LAYERS + 1)
+#define GRT_NOALLOC_BLOCKS 64
+#define GRT_NOALLOC_SCRATCH_BYTES (8*GRT_NOALLOC_MAX_LEVELS*GRT_NOALLOC_BLOCKS)   /* 102912 */
+int grt_integrate_flux_noalloc(int device, int num_levels, uint64_t num_wpoints, double dw,
+                               grt_real const *flux_dev, grt_real *out_dev);
+
 /* ---- fused column solvers for the drivers (no spectral arrays leave the GPU):
  * Rayleigh + optics mixing + solver + broadband integration in one kernel each;
  * replaces the chain column_calculation -> add_optics -> calculate_*_fluxes ->
