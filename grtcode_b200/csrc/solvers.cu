@@ -40,10 +40,32 @@ struct LayerDensity
 };
 
 
+// ---- working precision of the solver arithmetic ----------------------------------------
+// `fp` is the reference's fp_t.  Every local the reference declares fp_t is an `fp` here and
+// every expression is written as the reference writes it, so that C's usual arithmetic
+// conversions round at the same places in both builds: in the single build an expression with
+// a double literal (1., 0.25, ...) or a double variable (k, alpha1, alpha2, gamma4) is
+// evaluated in double and rounded to float when it is stored in an fp, a product of two fp
+// values is a float product (this TU is compiled -fmad=false: nothing is contracted).  The
+// Meador-Weaver formulas are ill-conditioned where the single-scattering albedo is tiny, so
+// the float roundings of gamma1..3 are visible in the fluxes: the single build has to make
+// them exactly where the reference's single build does.  With fp = double nothing changes.
+typedef real_t fp;
+#ifdef GRT_SINGLE
+#define GRT_MAX_EXP_ARG 80.f                     /* grtcode_config.h:29 */
+__device__ __forceinline__ float fp_exp(float const x) { return expf(x); }     // EXP
+#else
+#define GRT_MAX_EXP_ARG 700.                     /* grtcode_config.h:41 */
+__device__ __forceinline__ double fp_exp(double const x) { return exp(x); }
+#endif
+// the reference's plain exp() / sqrt(): double functions in both builds
+__device__ __forceinline__ double d_exp(double const x) { return exp(x); }
+__device__ __forceinline__ double d_sqrt(double const x) { return sqrt(x); }
+
 // ---- Rayleigh (rayleigh.c:29-41) -------------------------------------------------
-__device__ __forceinline__ double rayleigh_tau(double const w, double const n)
+__device__ __forceinline__ fp rayleigh_tau(double const w, fp const n)
 {
-    double const W = w*1.e-4;
+    fp const W = w*1.e-4;
     return (n*1.e-20*W*W*W*W)/(0.268675*1.e5*(9.38076E2 - 10.8426*W*W));
 }
 
@@ -59,7 +81,7 @@ __global__ void rayleigh_kernel(int const num_layers, double const w0, double co
         size_t const o = (size_t)j*nw + i;
         omega[o] = (real_t)1.;
         g[o] = (real_t)0.;
-        tau[o] = (real_t)rayleigh_tau(w, dens.n[j]);
+        tau[o] = rayleigh_tau(w, (fp)dens.n[j]);
     }
 }
 
@@ -77,40 +99,39 @@ __global__ void add_optics_kernel(uint64_t const n, int const num_optics, Optics
 {
     uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     if (i >= n) return;
-    double g = 0., omega = 0., tau = 0.;
+    fp g = 0., omega = 0., tau = 0.;
     for (int j=0; j<num_optics; ++j)
     {
-        double const gi = (double)in.g[j][i];
-        double const oi = (double)in.omega[j][i];
-        double const ti = (double)in.tau[j][i];
+        fp const gi = in.g[j][i];
+        fp const oi = in.omega[j][i];
+        fp const ti = in.tau[j][i];
         g += gi*oi*ti;
         omega += oi*ti;
         tau += ti;
     }
-    g_out[i] = (real_t)(g/omega);
-    omega_out[i] = (real_t)(omega/tau);
-    tau_out[i] = (real_t)tau;
+    g_out[i] = g/omega;
+    omega_out[i] = omega/tau;
+    tau_out[i] = tau;
 }
 
 
 // ---- longwave ----------------------------------------------------------------------
-__device__ __forceinline__ double planck(double const T, double const w)
+__device__ __forceinline__ fp planck(fp const T, fp const w)
 {
-    double const c1 = 1.1910429526245744e-8;
-    double const c2 = 1.4387773538277202;
-    double e = c2*w/T;
-    if (e > 700.) e = 700.;
-    e = exp(e);
+    fp const c1 = 1.1910429526245744e-8;
+    fp const c2 = 1.4387773538277202;
+    fp e = c2*w/T;
+    if (e > GRT_MAX_EXP_ARG) e = GRT_MAX_EXP_ARG;
+    e = fp_exp(e);
     return (c1*w*w*w)/(e - 1.);
 }
 
-__device__ __forceinline__ double effective_planck(double const Tc, double const Te,
-                                                   double const w, double const tau)
+__device__ __forceinline__ fp effective_planck(fp const Tc, fp const Te, fp const w, fp const tau)
 {
-    double const a = 0.193;
-    double const b = 0.013;
-    double const pc = planck(Tc, w);
-    double const pe = planck(Te, w);
+    fp const a = 0.193;
+    fp const b = 0.013;
+    fp const pc = planck(Tc, w);
+    fp const pe = planck(Te, w);
     return (pc + (a*tau + b*tau*tau)*pe)/(1. + a*tau + b*tau*tau);
 }
 
@@ -188,11 +209,11 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     bool const live = i < nw;
     uint64_t const ii = live ? i : nw - 1;
     int const L = num_levels - 1;
-    double const w = w0 + (double)ii*dw;
-    double const c1[4] = {-14.402613260847248, -3.0302159969901132, -1.4925584280108841,
-                          -1.0746123148178333};
-    double const c2[4] = {0.07587638482015649, 0.676114979733751, 1.3726594476601073,
-                          1.0169418413757783};
+    fp const w = w0 + (double)ii*dw;                 // longwave.c:238
+    fp const c1[4] = {-14.402613260847248, -3.0302159969901132, -1.4925584280108841,
+                      -1.0746123148178333};
+    fp const c2[4] = {0.07587638482015649, 0.676114979733751, 1.3726594476601073,
+                      1.0169418413757783};
     double weight = 0.;
     if (FUSED)
     {
@@ -202,21 +223,23 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         if (first == last) weight = 0.;
     }
 
-    auto layer_tau = [&](int const j) -> double
+    // tau_buf[j] = tau*(1. - omega) (longwave.c:253)
+    auto layer_tau = [&](int const j) -> fp
     {
         size_t const o = (size_t)j*nw + ii;
         if (FUSED)
         {
-            double const tg = (double)tau[o];
-            double const tr = rayleigh_tau(w, dens.n[j]);
-            double const tt = tg + tr;
-            double const om = tr/tt;
+            // add_optics of [gas, rayleigh] (optics.c:134-146)
+            fp const tg = tau[o];
+            fp const tr = rayleigh_tau(w0 + (double)ii*dw, (fp)dens.n[j]);
+            fp const tt = tg + tr;
+            fp const om = tr/tt;
             return tt*(1. - om);
         }
-        return (double)tau[o]*(1. - (double)omega[o]);
+        return tau[o]*(1. - omega[o]);
     };
 
-    double I[4] = {0., 0., 0., 0.};
+    fp I[4] = {0., 0., 0., 0.};
     if (FUSED)
     {
         // flux_down at the top of the atmosphere is zero: nothing to add.
@@ -227,38 +250,39 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     }
     for (int j=0; j<L; ++j)
     {
-        double const t = layer_tau(j);
-        double const b = effective_planck(temps.t_layers[j], temps.t_levels[j+1], w, t);
-        double f = 0.;
+        fp const t = layer_tau(j);
+        fp const b = effective_planck((fp)temps.t_layers[j], (fp)temps.t_levels[j+1], w, t);
+        fp f = 0.;
 #pragma unroll
         for (int s=0; s<4; ++s)
         {
-            double const ext = exp(c1[s]*t);
-            double const pp = (1. - ext)*b;
+            fp const e = c1[s]*t;
+            fp const ext = d_exp(e);
+            fp const pp = (1. - ext)*b;
             I[s] = pp + I[s]*ext;
             f += c2[s]*I[s];
         }
         if (FUSED)
         {
-            warp_accumulate(f*weight, sums, 1, j + 1);
+            warp_accumulate((double)f*weight, sums, 1, j + 1);
         }
         else if (live)
         {
             flux_down[(size_t)(j+1)*nw + ii] = (flux_t)f;
         }
     }
-    double const bs = planck(t_surf, w);
-    double const em = (double)emis[ii];
-    double f = 0.;
+    fp const bs = planck((fp)t_surf, w);
+    fp const em = emis[ii];
+    fp f = 0.;
 #pragma unroll
     for (int s=0; s<4; ++s)
     {
-        I[s] = em*bs + (1. - em)*I[s];
+        I[s] = em*bs + (1 - em)*I[s];
         f += c2[s]*I[s];
     }
     if (FUSED)
     {
-        warp_accumulate(f*weight, sums, 0, L);
+        warp_accumulate((double)f*weight, sums, 0, L);
     }
     else if (live)
     {
@@ -266,20 +290,21 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     }
     for (int j=L-1; j>=0; --j)
     {
-        double const t = layer_tau(j);
-        double const b = effective_planck(temps.t_layers[j], temps.t_levels[j], w, t);
+        fp const t = layer_tau(j);
+        fp const b = effective_planck((fp)temps.t_layers[j], (fp)temps.t_levels[j], w, t);
         f = 0.;
 #pragma unroll
         for (int s=0; s<4; ++s)
         {
-            double const ext = exp(c1[s]*t);
-            double const pp = (1. - ext)*b;
+            fp const e = c1[s]*t;
+            fp const ext = d_exp(e);
+            fp const pp = (1. - ext)*b;
             I[s] = pp + I[s]*ext;
             f += c2[s]*I[s];
         }
         if (FUSED)
         {
-            warp_accumulate(f*weight, sums, 0, j);
+            warp_accumulate((double)f*weight, sums, 0, j);
         }
         else if (live)
         {
@@ -293,16 +318,16 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
 // ---- shortwave ---------------------------------------------------------------------
 // meador_weaver_1980 (shortwave.c:97-209) with the Eddington gammas of
 // eddington_mw1980 (shortwave.c:214-236).  t_pure == nullptr for the diffuse beam.
-__device__ void eddington(double const omega, double const tau, double const mu,
-                          double const g, double *R, double *T, double *T_pure)
+__device__ void eddington(fp const omega, fp const tau, fp const mu, fp const g, fp *R, fp *T,
+                          fp *T_pure)
 {
-    double const gamma1 = 0.25*(7. - omega*(4. + 3.*g));
-    double const gamma2 = -0.25*(1. - omega*(4. - 3.*g));
-    double const gamma3 = 0.25*(2. - 3.*g*mu);
+    fp const gamma1 = 0.25*(7. - omega*(4. + 3.*g));
+    fp const gamma2 = -0.25*(1. - omega*(4. - 3.*g));
+    fp const gamma3 = 0.25*(2. - 3.*g*mu);
     if (omega <= 0.0)
     {
         *R = 0.;
-        *T = exp(-tau/mu);
+        *T = d_exp(-tau/mu);
         if (T_pure != nullptr) *T_pure = *T;
     }
     else
@@ -310,17 +335,17 @@ __device__ void eddington(double const omega, double const tau, double const mu,
         double const gamma4 = 1. - gamma3;
         double const alpha1 = gamma1*gamma4 + gamma2*gamma3;
         double const alpha2 = gamma1*gamma3 + gamma2*gamma4;
-        double const k = sqrt(gamma1*gamma1 - gamma2*gamma2);
-        double t = tau;
-        if (1./mu > k && tau/mu > 700.)
+        double const k = d_sqrt(gamma1*gamma1 - gamma2*gamma2);
+        fp t = tau;
+        if (1./mu > k && tau/mu > GRT_MAX_EXP_ARG)
         {
-            t = 700.*mu;
+            t = GRT_MAX_EXP_ARG*mu;
         }
-        else if (tau*k > 700.)
+        else if (tau*k > GRT_MAX_EXP_ARG)
         {
-            t = 700./k;
+            t = GRT_MAX_EXP_ARG/k;
         }
-        double const tp = exp(t/mu);
+        fp const tp = d_exp(t/mu);
         if (tp <= 1.0)
         {
             *R = 0.;
@@ -329,9 +354,9 @@ __device__ void eddington(double const omega, double const tau, double const mu,
         }
         else
         {
-            double const tm = exp(-t/mu);
-            double const tkm = exp(-t*k);
-            double const tkp = exp(t*k);
+            fp const tm = d_exp(-t/mu);
+            fp const tkm = d_exp(-t*k);
+            fp const tkp = d_exp(t*k);
             if (T_pure != nullptr) *T_pure = tm;
             if (omega >= 1.)
             {
@@ -380,56 +405,59 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     uint64_t const ii = live ? i : nw - 1;
     int const L = num_levels - 1;
     double const w = w0 + (double)ii*dw;
+    fp const mu_d = mu_dir;                          // fp_t arguments of sw_flux
+    fp const mu_f = mu_dif;
+    fp const tsi_fp = tsi;
 
     // Layer reflectivities / transmittances and, in the same bottom-up loop, the adding
     // recursions from the surface (shortwave.c:242-260): a layer's five values are in
     // registers when Rdd / Rfd need them, so the per-thread arrays (local memory, the traffic
     // that bounds this kernel) are written once here and read once by the level loop below.
     // The layers are independent, so their order does not change any value.
-    double R_dir[MAXL], R_dif[MAXL], T_dir[MAXL], T_dif[MAXL], T_pure[MAXL];
-    double Rdd[MAXL + 1], Rfd[MAXL + 1];
-    double rdd_below = (double)alb_dir[ii];
-    double rfd_below = (double)alb_dif[ii];
+    fp R_dir[MAXL], R_dif[MAXL], T_dir[MAXL], T_dif[MAXL], T_pure[MAXL];
+    fp Rdd[MAXL + 1], Rfd[MAXL + 1];
+    fp rdd_below = alb_dir[ii];
+    fp rfd_below = alb_dif[ii];
     Rdd[L] = rdd_below;
     Rfd[L] = rfd_below;
     for (int j=L-1; j>=0; --j)
     {
         size_t const o = (size_t)j*nw + ii;
-        double omega, g, tau;
+        fp omega, g, tau;
         if (FUSED)
         {
             // add_optics of [gas, rayleigh] (optics.c:134-146): g = 0*tau_R/tau_R,
             // omega = tau_R/(tau_gas + tau_R).
-            double const tg = (double)tau_in[o];
-            double const tr = rayleigh_tau(w, dens.n[j]);
+            fp const tg = tau_in[o];
+            fp const tr = rayleigh_tau(w, (fp)dens.n[j]);
             tau = tg + tr;
             g = 0./tr;
             omega = tr/tau;
         }
         else
         {
-            omega = (double)omega_in[o];
-            g = (double)g_in[o];
-            tau = (double)tau_in[o];
+            omega = omega_in[o];
+            g = g_in[o];
+            tau = tau_in[o];
         }
         // delta-Eddington scaling (shortwave.c:86-89).
-        double const gs = g/(g + 1.);
-        double const f = g*g;
-        double const os = (1. - f)*omega/(1. - omega*f);
-        double const ts = tau*(1. - omega*f);
-        double r_dir, t_dir, t_pure, r_dif, t_dif;
-        eddington(os, ts, mu_dir, gs, &r_dir, &t_dir, &t_pure);
-        eddington(os, ts, mu_dif, gs, &r_dif, &t_dif, nullptr);
+        fp const gs = g/(g + 1.);
+        fp const f = g*g;
+        fp const os = (1. - f)*omega/(1. - omega*f);
+        fp const ts = tau*(1. - omega*f);
+        fp r_dir, t_dir, t_pure, r_dif, t_dif;
+        eddington(os, ts, mu_d, gs, &r_dir, &t_dir, &t_pure);
+        eddington(os, ts, mu_f, gs, &r_dif, &t_dif, nullptr);
         R_dir[j] = r_dir;
         T_dir[j] = t_dir;
         T_pure[j] = t_pure;
         R_dif[j] = r_dif;
         T_dif[j] = t_dif;
         // Adding (shortwave.c:242-260).
-        double const A = t_pure;
-        double const B = 1./(1. - r_dif*rfd_below);
-        double const rdd = r_dir + (A*rdd_below + (t_dir - A)*rfd_below)*t_dif*B;
-        double const rfd = r_dif + t_dif*t_dif*rfd_below*B;
+        fp const A = t_pure;
+        fp const B = 1./(1. - r_dif*rfd_below);
+        fp const rdd = r_dir + (A*rdd_below + (t_dir - A)*rfd_below)*t_dif*B;
+        fp const rfd = r_dif + t_dif*t_dif*rfd_below*B;
         Rdd[j] = rdd;
         Rfd[j] = rfd;
         rdd_below = rdd;
@@ -438,7 +466,7 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
     // Rfu (reflectivity of the layers above a level to diffuse light from below,
     // shortwave.c:262-268) is a top-down recursion: it is advanced inside the level loop
     // below (the same operations in the same order) instead of being stored per layer.
-    double const scale = (double)solar[ii]*mu_dir;
+    fp const scale = solar[ii]*mu_d;                 // flux *= solar_flux*mu_dir (shortwave.c:402)
     double weight = 0.;
     if (FUSED)
     {
@@ -447,15 +475,17 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
                                                      : 0.;
         if (first == last) weight = 0.;
     }
-    double dir_beam = 1.;
-    double dif_beam = 0.;
+    fp dir_beam = 1.;
+    fp dif_beam = 0.;
     {
-        double const up = tsi*((dir_beam*Rdd[0])*scale);
-        double const down = tsi*(dir_beam*scale);
+        fp const r0 = dir_beam*Rdd[0];
+        fp const t0 = dir_beam;
+        fp const up = tsi_fp*(r0*scale);             // shortwave.c:448
+        fp const down = tsi_fp*(t0*scale);
         if (FUSED)
         {
-            warp_accumulate(up*weight, sums, 0, 0);
-            warp_accumulate(down*weight, sums, 1, 0);
+            warp_accumulate((double)up*weight, sums, 0, 0);
+            warp_accumulate((double)down*weight, sums, 1, 0);
         }
         else
         {
@@ -463,18 +493,18 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
             flux_down[ii] = (flux_t)down;
         }
     }
-    double rfu_above = 0.;          // Rfu[j-2]
-    double rfu = R_dif[0];          // Rfu[j-1]
+    fp rfu_above = 0.;          // Rfu[j-2]
+    fp rfu = R_dif[0];          // Rfu[j-1]
     for (int j=1; j<num_levels; ++j)
     {
         if (j > 1)
         {
             // Rfu[j-1] from Rfu[j-2]
-            double const Bu = 1./(1. - R_dif[j-1]*rfu);
-            double const next = R_dif[j-1] + T_dif[j-1]*T_dif[j-1]*rfu*Bu;
+            fp const Bu = 1./(1. - R_dif[j-1]*rfu);
+            fp const next = R_dif[j-1] + T_dif[j-1]*T_dif[j-1]*rfu*Bu;
             rfu_above = rfu;
             rfu = next;
-            double const C = 1./(1. - R_dif[j-1]*rfu_above);
+            fp const C = 1./(1. - R_dif[j-1]*rfu_above);
             dif_beam = (dir_beam*R_dir[j-1]*rfu_above + dif_beam)*T_dif[j-1]*C +
                        dir_beam*(T_dir[j-1] - T_pure[j-1]);
         }
@@ -483,15 +513,15 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
             dif_beam = dir_beam*(T_dir[j-1] - T_pure[j-1]);
         }
         dir_beam *= T_pure[j-1];
-        double const B = 1./(1. - Rfd[j]*rfu);
-        double const R = (dir_beam*Rdd[j] + dif_beam*Rfd[j])*B;
-        double const T = dir_beam*(1. + Rdd[j]*rfu*B) + dif_beam*B;
-        double const up = tsi*(R*scale);
-        double const down = tsi*(T*scale);
+        fp const B = 1./(1. - Rfd[j]*rfu);
+        fp const R = (dir_beam*Rdd[j] + dif_beam*Rfd[j])*B;
+        fp const T = dir_beam*(1. + Rdd[j]*rfu*B) + dif_beam*B;
+        fp const up = tsi_fp*(R*scale);
+        fp const down = tsi_fp*(T*scale);
         if (FUSED)
         {
-            warp_accumulate(up*weight, sums, 0, j);
-            warp_accumulate(down*weight, sums, 1, j);
+            warp_accumulate((double)up*weight, sums, 0, j);
+            warp_accumulate((double)down*weight, sums, 1, j);
         }
         else
         {

@@ -31,7 +31,8 @@ DTYPE = np.float32 if SINGLE else np.float64
 
 def lib_path(fast: bool = False) -> str:
     if SINGLE:
-        return os.path.join(HERE, "_ref", "libgrtcode_ref_sp.so")
+        return os.path.join(HERE, "_ref", "libgrtcode_ref_sp_fast.so" if fast else
+                            "libgrtcode_ref_sp.so")
     return os.path.join(HERE, "_ref", "libgrtcode_ref_fast.so" if fast else "libgrtcode_ref.so")
 
 

@@ -30,9 +30,10 @@ def build_dataset(root, w0, wn, lines, seed, cfcs=(), cias=()):
 
 
 def oracle_column(ds, w0, wn, dw, col, molecules, use_ctm=True, threads=None, solvers=True,
-                  line_window=(None, None), method=R.LINE_SAMPLE):
-    """Reference pipeline on the host: tau_gas, then (optionally) LW + SW fluxes."""
-    r = R.Ref(threads=threads)
+                  line_window=(None, None), method=R.LINE_SAMPLE, fast=False):
+    """Reference pipeline on the host: tau_gas, then (optionally) LW + SW fluxes.
+    fast: the reference's own -DFAST build (no range checks / trapped exceptions)."""
+    r = R.Ref(fast=fast, threads=threads)
     g = r.grid(w0, wn, dw)
     levels = len(col.p)
     go = R.RefGasOptics(r, levels, g, ds.hitran, ds.h2o_ctm_dir if use_ctm else None,
@@ -126,13 +127,14 @@ def gpu_column(ds, w0, wn, dw, col, molecules, use_ctm=True, solvers=True, devic
     return out
 
 
-def run_column_pair(root, w0, wn, dw, num_levels, lines, seed, cfcs=(), cias=(), use_ctm=True):
+def run_column_pair(root, w0, wn, dw, num_levels, lines, seed, cfcs=(), cias=(), use_ctm=True,
+                    oracle_fast=False):
     """One synthetic column through both implementations; returns error metrics."""
     ds = build_dataset(root, w0, wn, lines, seed, cfcs, cias)
     rng = np.random.default_rng(seed)
     mols = tuple(lines.keys())
     col = synth.make_column(num_levels, rng, molecules=mols, cfcs=tuple(ds.cfc.keys()))
-    want = oracle_column(ds, w0, wn, dw, col, mols, use_ctm)
+    want = oracle_column(ds, w0, wn, dw, col, mols, use_ctm, fast=oracle_fast)
     got = gpu_column(ds, w0, wn, dw, col, mols, use_ctm)
     rel = relative_error(got["tau"], want["tau"])
     bb = lambda f: R.broadband(f, dw)
