@@ -39,7 +39,12 @@ if ROOT not in sys.path:
 
 METRIC = "spectral pts x layers / s (line-by-line tau, LW+SW column incl. solvers)"
 UNIT = "pts*layers/s"
-FLOP_PER_SAMPLE = 9.0        # 6 FP64 + 3 FP32 per far-wing Voigt sample
+# Algorithmic flops per far-wing Voigt sample.  Double build: 6 FP64 + 3 FP32.
+# Single build (GRT_PRECISION=single, the reference's --enable-single-precision): the float
+# chain t2 - v, *REPWID, x*x + Y*Y, reciprocal, c*K + acc = 7 FP32.
+SINGLE = os.environ.get("GRT_PRECISION", "double") == "single"
+FLOP_PER_SAMPLE = 7.0 if SINGLE else 9.0
+DTYPE = "f32" if SINGLE else "f64"
 
 
 def parse_args():
@@ -308,7 +313,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3*mean_est, "ms_per_step_note": "extrapolated full-column time",
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE,
             "data": "synthetic HITRAN-format line lists + CIRC-1 profile",
             "config": workload_config(args, lw, sw, layers),
             "cpu_baseline": info,
@@ -320,6 +325,7 @@ def run_reference(args):
 def workload_config(args, lw, sw, layers):
     return {"workload": "BASELINE config 2: CIRC case 1 clear-sky LW+SW, 7 HITRAN molecules + "
                         "H2O/O3 continua + 3 CIA pairs + 3 CFCs, one column per step per GPU",
+            "precision": "single (fp_t = float, --enable-single-precision)" if SINGLE else "double",
             "layers": layers, "dw_cm-1": args.dw, "lw_points": lw.n, "sw_points": sw.n,
             "lw_lines": lw.num_lines, "sw_lines": sw.num_lines, "line_scale": args.scale,
             "method": args.method, "columns_per_step_per_gpu": 1,
@@ -670,13 +676,14 @@ def run_ours(args):
     achieved = wing_flop/(wing_ns*1e-9)/1e12 if wing_ns else None
     samples_step = sum(out[n][2]["samples"] for n in ("lw", "sw"))
     roofline = {
-        "bound": "fp64",
+        "bound": "fp32" if SINGLE else "fp64",
         "kernel": "wing_sweep_kernel" if args.method == "line_sample" else "bin_gather_kernel",
-        "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
-        "frac": achieved/fp64_peak if achieved else None,
+        "achieved": achieved, "peak": fp32_peak if SINGLE else fp64_peak, "unit": "TFLOP/s",
+        "frac": achieved/(fp32_peak if SINGLE else fp64_peak) if achieved else None,
         "traffic": recorded_wing_traffic(args),
-        "peak_source": "measured here: dependent-free DFMA chains, all SMs (grt_measure_fma_peak); "
-                       "MEASURED_PEAKS.json has no FP64 figure",
+        "peak_source": "measured here: dependent-free " + ("FFMA" if SINGLE else "DFMA") +
+                       " chains, all SMs (grt_measure_fma_peak); MEASURED_PEAKS.json has no "
+                       "non-tensor FP64 / FP32 figure",
         "flop_per_sample": FLOP_PER_SAMPLE,
         "avg_launch_ms": wing_ns*1e-6/launches_wing if wing_ns else None,
         "samples_per_s": (wing_flop/FLOP_PER_SAMPLE)/(wing_ns*1e-9) if wing_ns else None,
@@ -691,15 +698,18 @@ def run_ours(args):
     sm_mhz = clk.get("sm_mhz") or clk.get("sm_max_mhz")
     if roofline["samples_per_s"] and sm_mhz:
         xu_peak = torch.cuda.get_device_properties(device).multi_processor_count*16.*sm_mhz*1e6
-        roofline["xu_pipe"] = {"ops_per_sample": 2, "achieved_lane_ops_per_s": 2.*roofline["samples_per_s"],
+        # single build: no F2F, and half of the point pairs take the MUFU-free reciprocal
+        xu_ops = 0.5 if SINGLE else 2.
+        roofline["xu_pipe"] = {"ops_per_sample": xu_ops,
+                               "achieved_lane_ops_per_s": xu_ops*roofline["samples_per_s"],
                                "peak_lane_ops_per_s": xu_peak,
-                               "frac": 2.*roofline["samples_per_s"]/xu_peak}
+                               "frac": xu_ops*roofline["samples_per_s"]/xu_peak}
     if args.method != "line_sample":
         # the flop bookkeeping above is the wing sweep's: no roofline line for the binned methods
         roofline = None
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3*secs/args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "scaling": "weak", "vs_baseline": None, "dtype": DTYPE,
             "data": "synthetic HITRAN-format line lists + CIRC-1 profile",
             "config": workload_config(args, lw, sw, layers),
             "clocks": clk,

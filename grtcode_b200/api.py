@@ -159,7 +159,7 @@ def load():
     L.grtcode_errstr.argtypes = [C.c_int, C.c_char_p, C.c_int]
     L.grt_tips_q.restype = C.c_double
     L.grt_tips_q.argtypes = [C.c_int, C.c_double, C.c_int]
-    _cuda.grt_measure_fma_peak.argtypes = [C.c_int, _dbl_p, _dbl_p]
+    _cuda.grt_measure_fma_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     _cuda.grt_synchronize.argtypes = [C.c_int]
     _cuda.grt_selftest_arithmetic.argtypes = [C.c_int, C.c_ulonglong, C.c_ulonglong,
                                               C.POINTER(C.c_ulonglong)]
