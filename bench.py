@@ -476,28 +476,50 @@ def spectral_split_leg(args, bands2, device, rank, world, barrier, torch, dist, 
         return None
     col = W.circ1_column()
     sw = bands2[1]
+
+    def measure(part):
+        """Per-rank [compute s, all-reduce s, total s, points, samples] of one split column."""
+        part.run(W.perturbed(col, 0, 0))                   # warm-up (allocations, tile lists)
+        comp, red, tot = [], [], []
+        for k in range(3):
+            barrier()
+            t0 = time.perf_counter()
+            part.run(W.perturbed(col, 0, 300 + k))
+            torch.cuda.synchronize(device)
+            t1 = time.perf_counter()
+            comp.append(part.compute_seconds)
+            red.append(part.reduce_seconds)
+            tot.append(t1 - t0)
+        mine = torch.tensor([min(comp), float(np.median(red)), min(tot),
+                             float(part.chunks["sw"].n),
+                             float(part.engine.parts[0]["go"].stats()["samples"])],
+                            device=f"cuda:{device}", dtype=torch.float64)
+        allv = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allv, mine)
+        return [[float(x) for x in v.tolist()] for v in allv]
+
     t_setup = time.perf_counter()
     part = P.SpectralSplitColumn([sw], col, device, W.MOLECULES, world, rank)
     t_setup = time.perf_counter() - t_setup
-    part.run(W.perturbed(col, 0, 0))                   # warm-up (allocations, tile lists)
-    reps = 3
-    comp, red, tot = [], [], []
-    for k in range(reps):
-        barrier()
-        t0 = time.perf_counter()
-        part.run(W.perturbed(col, 0, 300 + k))
-        torch.cuda.synchronize(device)
-        t1 = time.perf_counter()
-        comp.append(part.compute_seconds)
-        red.append(part.reduce_seconds)
-        tot.append(t1 - t0)
-    mine = torch.tensor([min(comp), float(np.median(red)), min(tot),
-                         float(part.chunks["sw"].n), float(part.engine.parts[0]["go"].stats()["samples"])],
-                        device=f"cuda:{device}", dtype=torch.float64)
-    allv = [torch.zeros_like(mine) for _ in range(world)]
-    dist.all_gather(allv, mine)
+    cur = measure(part)
+    rows = cur                                             # the best cuts' measurements
+    passes = [{"cuts": "line-density model (parallel.interval_cost)",
+               "seconds_split": max(r[2] for r in cur),
+               "compute_seconds_per_rank": [round(r[0], 5) for r in cur]}]
+    # cuts moved by the measured per-rank times (parallel.measured_costs); every rank takes
+    # the same decisions because all of them see the same gathered numbers
+    for it in range(int(os.environ.get("GRT_SPLIT_REBALANCE", "2"))):
+        cost = P.measured_costs(part.costs["sw"], part.all_chunks["sw"], [r[0] for r in cur])
+        part.close()
+        part = P.SpectralSplitColumn([sw], col, device, W.MOLECULES, world, rank,
+                                     cost_override={"sw": cost})
+        cur = measure(part)
+        passes.append({"cuts": f"measured per-rank times, pass {it + 1}",
+                       "seconds_split": max(r[2] for r in cur),
+                       "compute_seconds_per_rank": [round(r[0], 5) for r in cur]})
+        if max(r[2] for r in cur) < max(r[2] for r in rows):
+            rows = cur
     part.close()
-    rows = [[float(x) for x in v.tolist()] for v in allv]
     slowest = max(r[2] for r in rows)
     one = sw_ms_one_gpu*1e-3
     return {"workload": "BASELINE config 4: one CIRC-1 column, 1-50000 cm-1 at 0.01 cm-1 "
@@ -510,7 +532,7 @@ def spectral_split_leg(args, bands2, device, rank, world, barrier, torch, dist, 
             "allreduce_seconds_per_rank": [round(r[1], 6) for r in rows],
             "points_per_rank": [int(r[3]) for r in rows],
             "voigt_samples_per_rank": [int(r[4]) for r in rows],
-            "allreduce_bytes": 2*8*len(col.p), "setup_s": t_setup,
+            "allreduce_bytes": 2*8*len(col.p), "setup_s": t_setup, "passes": passes,
             "limiter": "the slowest rank's compute time (chunk cost imbalance + the halo and "
                        "fixed per-launch costs every rank repeats); the all-reduce is "
                        f"{1e6*float(np.median([r[1] for r in rows])):.0f} us"}

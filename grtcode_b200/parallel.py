@@ -214,6 +214,22 @@ def gather_columns(local: np.ndarray, num_columns: int, group=None) -> np.ndarra
     return np.concatenate([recv[r][:sizes[r]].cpu().numpy() for r in range(world)], axis=0)
 
 
+def measured_costs(cost: np.ndarray | None, chunks: list, seconds_per_rank) -> np.ndarray:
+    """Per-interval costs rescaled so that every chunk's summed cost equals the compute time
+    its rank MEASURED with the current cuts: inside a chunk the model's shape is kept, between
+    chunks the measurement decides.  Cutting by the result (``split_spectral_range``) moves
+    points from slow ranks to fast ones; the estimate includes each rank's halo and fixed
+    per-launch work, which is what one more pass corrects."""
+    n_int = chunks[-1].last
+    c = np.ones(n_int) if cost is None else np.asarray(cost, dtype=np.float64).copy()
+    for ch, secs in zip(chunks, seconds_per_rank):
+        seg = slice(ch.first, ch.last)
+        total = float(c[seg].sum())
+        if total > 0.:
+            c[seg] *= float(secs)/total
+    return c
+
+
 class SpectralSplitColumn:
     """One column whose spectral range is split over the ranks of the process group
     (config 4).  Every rank builds the engine for its own chunk (+ halo) of every band;
@@ -223,11 +239,15 @@ class SpectralSplitColumn:
     work (``interval_cost`` of the band's line list) instead of by point count."""
 
     def __init__(self, bands, column, device: int, molecules, world: int, rank: int,
-                 balance: bool = True):
+                 balance: bool = True, cost_override: dict | None = None):
+        """cost_override: {band name: float[n-1]} per-interval costs to cut by instead of the
+        line-density model (see ``measured_costs``)."""
         from . import api
         from . import workloads as W
         from .column_engine import ColumnEngine
         self.chunks = {}
+        self.all_chunks = {}
+        self.costs = {}
         sub = []
         windows = {}
         solar = {}
@@ -237,8 +257,13 @@ class SpectralSplitColumn:
                 # every rank derives the same cuts from the same line list
                 cost = interval_cost(band.w0, band.wn, band.dw,
                                      line_centres(band.dataset.hitran, molecules))
-            ch = split_spectral_range(band.w0, band.wn, band.dw, world, cost)[rank]
+            if cost_override is not None and band.name in cost_override:
+                cost = np.asarray(cost_override[band.name], dtype=np.float64)
+            every = split_spectral_range(band.w0, band.wn, band.dw, world, cost)
+            ch = every[rank]
             self.chunks[band.name] = ch
+            self.all_chunks[band.name] = every
+            self.costs[band.name] = cost
             sub.append(W.Band(band.name, ch.w_lo, ch.wn_arg, band.dw, band.lines, band.dataset))
             windows[band.name] = ch.window
             if not band.name.startswith("lw"):

@@ -160,3 +160,28 @@ def test_single_process_reduce_is_the_identity():
     up, dn = P.reduce_broadband(np.arange(4.), np.arange(4.) + 1.)
     np.testing.assert_array_equal(up, np.arange(4.))
     np.testing.assert_array_equal(dn, np.arange(4.) + 1.)
+
+
+def test_measured_costs_move_the_cuts_towards_the_slow_ranks():
+    """parallel.measured_costs: chunk sums equal the measured seconds, and cutting by the
+    result gives the slow rank fewer intervals."""
+    from grtcode_b200 import parallel as P
+    w0, wn, dw, world = 1., 1001., 0.5, 4
+    chunks = P.split_spectral_range(w0, wn, dw, world)
+    n_int = P.grid_size(w0, wn, dw) - 1
+    secs = [1., 1., 3., 1.]
+    cost = P.measured_costs(None, chunks, secs)
+    assert cost.shape == (n_int,)
+    for ch, t in zip(chunks, secs):
+        assert abs(cost[ch.first:ch.last].sum() - t) < 1e-12
+    again = P.split_spectral_range(w0, wn, dw, world, cost)
+    width = lambda c: c.last - c.first
+    assert sum(width(c) for c in again) == n_int
+    # every rank now carries the same measured cost: 6/4 s
+    for c in again:
+        assert abs(cost[c.first:c.last].sum() - 1.5) < 2.*cost.max()
+    # the slow interval range [chunks[2].first, chunks[2].last) is shared by more ranks
+    assert sum(1 for c in again if c.first < chunks[2].last and c.last > chunks[2].first) >= 2
+    shaped = P.measured_costs(np.linspace(1., 2., n_int), chunks, secs)
+    seg = shaped[chunks[0].first:chunks[0].last]
+    assert seg[-1] > seg[0]            # the model's shape is kept inside a chunk
