@@ -23,8 +23,11 @@ if PRECISION not in ("double", "single"):
 SINGLE = PRECISION == "single"
 REAL = C.c_float if SINGLE else C.c_double
 DTYPE = np.float32 if SINGLE else np.float64
-LIB_HOST = os.path.join(HERE, "libgrtcode_sp.so" if SINGLE else "libgrtcode.so")
-LIB_CUDA = os.path.join(HERE, "libgrt_sm100_sp.so" if SINGLE else "libgrt_sm100.so")
+# GRT_LIB_DIR: directory of an alternative build of the two libraries (kernel variants made
+# by tools/build_variant.sh for A/B measurements); default: the in-tree build.
+LIB_DIR = os.environ.get("GRT_LIB_DIR") or HERE
+LIB_HOST = os.path.join(LIB_DIR, "libgrtcode_sp.so" if SINGLE else "libgrtcode.so")
+LIB_CUDA = os.path.join(LIB_DIR, "libgrt_sm100_sp.so" if SINGLE else "libgrt_sm100.so")
 
 WAVENUMBER_SWEEP, LINE_SWEEP, LINE_SAMPLE = 0, 1, 2   # include/gas_optics.h
 NUM_MOLS, NUM_CFCS, NUM_CIAS, MAX_NUM_CIAS, DIR_PATH_LEN = 53, 21, 2, 3, 1024

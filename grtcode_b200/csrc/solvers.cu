@@ -318,66 +318,99 @@ lw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
 // ---- shortwave ---------------------------------------------------------------------
 // meador_weaver_1980 (shortwave.c:97-209) with the Eddington gammas of
 // eddington_mw1980 (shortwave.c:214-236).  t_pure == nullptr for the diffuse beam.
-__device__ void eddington(fp const omega, fp const tau, fp const mu, fp const g, fp *R, fp *T,
-                          fp *T_pure)
+// The optical depth the exponentials see (shortwave.c:137-145).
+__device__ __forceinline__ fp edd_clamped_tau(fp const tau, fp const mu, double const k)
 {
-    fp const gamma1 = 0.25*(7. - omega*(4. + 3.*g));
-    fp const gamma2 = -0.25*(1. - omega*(4. - 3.*g));
+    fp t = tau;
+    if (1./mu > k && tau/mu > GRT_MAX_EXP_ARG)
+    {
+        t = GRT_MAX_EXP_ARG*mu;
+    }
+    else if (tau*k > GRT_MAX_EXP_ARG)
+    {
+        t = GRT_MAX_EXP_ARG/k;
+    }
+    return t;
+}
+
+// One beam of meador_weaver_1980 for omega > 0, given the quantities that do not depend on
+// the beam's zenith angle (gamma1, gamma2, k) and exp(-t*k), exp(t*k).
+__device__ __forceinline__ void edd_beam(fp const omega, fp const mu, fp const g,
+                                         fp const gamma1, fp const gamma2, double const k,
+                                         fp const t, fp const tkm, fp const tkp, fp *R, fp *T,
+                                         fp *T_pure)
+{
     fp const gamma3 = 0.25*(2. - 3.*g*mu);
-    if (omega <= 0.0)
+    double const gamma4 = 1. - gamma3;
+    double const alpha1 = gamma1*gamma4 + gamma2*gamma3;
+    double const alpha2 = gamma1*gamma3 + gamma2*gamma4;
+    fp const tp = d_exp(t/mu);
+    if (tp <= 1.0)
     {
         *R = 0.;
-        *T = d_exp(-tau/mu);
-        if (T_pure != nullptr) *T_pure = *T;
+        *T = 1.;
+        if (T_pure != nullptr) *T_pure = 1.;
     }
     else
     {
-        double const gamma4 = 1. - gamma3;
-        double const alpha1 = gamma1*gamma4 + gamma2*gamma3;
-        double const alpha2 = gamma1*gamma3 + gamma2*gamma4;
-        double const k = d_sqrt(gamma1*gamma1 - gamma2*gamma2);
-        fp t = tau;
-        if (1./mu > k && tau/mu > GRT_MAX_EXP_ARG)
+        fp const tm = d_exp(-t/mu);
+        if (T_pure != nullptr) *T_pure = tm;
+        if (omega >= 1.)
         {
-            t = GRT_MAX_EXP_ARG*mu;
-        }
-        else if (tau*k > GRT_MAX_EXP_ARG)
-        {
-            t = GRT_MAX_EXP_ARG/k;
-        }
-        fp const tp = d_exp(t/mu);
-        if (tp <= 1.0)
-        {
-            *R = 0.;
-            *T = 1.;
-            if (T_pure != nullptr) *T_pure = 1.;
+            *R = (1./(1. + gamma1*t))*(gamma1*t + (gamma3 - gamma1*mu)*(1. - tm));
+            *T = 1. - *R;
         }
         else
         {
-            fp const tm = d_exp(-t/mu);
-            fp const tkm = d_exp(-t*k);
-            fp const tkp = d_exp(t*k);
-            if (T_pure != nullptr) *T_pure = tm;
-            if (omega >= 1.)
-            {
-                *R = (1./(1. + gamma1*t))*(gamma1*t + (gamma3 - gamma1*mu)*(1. - tm));
-                *T = 1. - *R;
-            }
-            else
-            {
-                *R = (omega/((1. - k*k*mu*mu)*((k + gamma1)*tkp + (k - gamma1)*tkm)))*
-                     ((1. - k*mu)*(alpha2 + k*gamma3)*tkp - (1. + k*mu)*(alpha2 - k*gamma3)*tkm -
-                      2.*k*(gamma3 - alpha2*mu)*tm);
-                *T = tm*(1. - (omega/((1. - k*k*mu*mu)*((k + gamma1)*tkp + (k - gamma1)*tkm)))*
-                     ((1. + k*mu)*(alpha1 + k*gamma4)*tkp - (1. - k*mu)*(alpha1 - k*gamma4)*tkm -
-                      2.*k*(gamma4 + alpha1*mu)*tp));
-            }
+            *R = (omega/((1. - k*k*mu*mu)*((k + gamma1)*tkp + (k - gamma1)*tkm)))*
+                 ((1. - k*mu)*(alpha2 + k*gamma3)*tkp - (1. + k*mu)*(alpha2 - k*gamma3)*tkm -
+                  2.*k*(gamma3 - alpha2*mu)*tm);
+            *T = tm*(1. - (omega/((1. - k*k*mu*mu)*((k + gamma1)*tkp + (k - gamma1)*tkm)))*
+                 ((1. + k*mu)*(alpha1 + k*gamma4)*tkp - (1. - k*mu)*(alpha1 - k*gamma4)*tkm -
+                  2.*k*(gamma4 + alpha1*mu)*tp));
         }
     }
     if (T_pure != nullptr)
     {
         if (*T_pure > *T) *T = *T_pure;
     }
+}
+
+// eddington_mw1980 + meador_weaver_1980 (shortwave.c:97-236) for the direct (mu_d) and the
+// diffuse (mu_f) beam of one layer.  The reference evaluates the two beams independently; the
+// Eddington gammas 1 and 2, k and -- unless one of the two optical-depth clamps fires for one
+// beam only -- exp(-t*k) and exp(t*k) do not depend on the beam, so they are computed once
+// (2 of the 8 double exp and 1 of the 2 sqrt per layer): the same expressions on the same
+// operands, hence the same bits.
+__device__ void eddington_pair(fp const omega, fp const tau, fp const mu_d, fp const mu_f,
+                               fp const g, fp *R_dir, fp *T_dir, fp *T_pure, fp *R_dif,
+                               fp *T_dif)
+{
+    if (omega <= 0.0)
+    {
+        *R_dir = 0.;
+        *T_dir = d_exp(-tau/mu_d);
+        *T_pure = *T_dir;
+        *R_dif = 0.;
+        *T_dif = d_exp(-tau/mu_f);
+        return;
+    }
+    fp const gamma1 = 0.25*(7. - omega*(4. + 3.*g));
+    fp const gamma2 = -0.25*(1. - omega*(4. - 3.*g));
+    double const k = d_sqrt(gamma1*gamma1 - gamma2*gamma2);
+    fp const td = edd_clamped_tau(tau, mu_d, k);
+    fp const tf = edd_clamped_tau(tau, mu_f, k);
+    fp const tkm_d = d_exp(-td*k);
+    fp const tkp_d = d_exp(td*k);
+    fp tkm_f = tkm_d;
+    fp tkp_f = tkp_d;
+    if (tf != td)
+    {
+        tkm_f = d_exp(-tf*k);
+        tkp_f = d_exp(tf*k);
+    }
+    edd_beam(omega, mu_d, g, gamma1, gamma2, k, td, tkm_d, tkp_d, R_dir, T_dir, T_pure);
+    edd_beam(omega, mu_f, g, gamma1, gamma2, k, tf, tkm_f, tkp_f, R_dif, T_dif, nullptr);
 }
 
 // Resident blocks per SM the compiler must allow.  The solver is latency-bound on its
@@ -446,8 +479,7 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
         fp const os = (1. - f)*omega/(1. - omega*f);
         fp const ts = tau*(1. - omega*f);
         fp r_dir, t_dir, t_pure, r_dif, t_dif;
-        eddington(os, ts, mu_d, gs, &r_dir, &t_dir, &t_pure);
-        eddington(os, ts, mu_f, gs, &r_dif, &t_dif, nullptr);
+        eddington_pair(os, ts, mu_d, mu_f, gs, &r_dir, &t_dir, &t_pure, &r_dif, &t_dif);
         R_dir[j] = r_dir;
         T_dir[j] = t_dir;
         T_pure[j] = t_pure;

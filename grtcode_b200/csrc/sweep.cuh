@@ -395,6 +395,11 @@ __device__ __forceinline__ void accumulate2(double &a0, double &a1, double const
 #define GRT_SEED_MIX 0
 #endif
 
+// Far-edge records share the fast class's pipelined loop (see process_batch).
+#ifndef GRT_MERGE_EDGE
+#define GRT_MERGE_EDGE 0
+#endif
+
 // kClsFast: the tile lies wholly inside the line's window and wholly in its far wing:
 // no predicates, PTS independent dependency chains in flight, two samples per packed op.
 #ifdef GRT_SINGLE
@@ -823,6 +828,21 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
                             t.warp_base, t.warp_last, t.fsteps, t.nw);
     }
     unsigned m = __ballot_sync(0xffffffffu, cls == kClsFast) & t.gmask;
+#if GRT_MERGE_EDGE
+    // Far-edge records ride in the software-pipelined loop of the fast class (the next
+    // record's vectors are loaded while the current one computes) behind a warp-uniform
+    // branch: on coarse grids a visit is only a few samples per lane, so the load latency a
+    // plain class walk exposes per record is a large share of its cost.
+    unsigned const medge = __ballot_sync(0xffffffffu, cls == kClsFarEdge) & t.gmask;
+    m |= medge;
+#define GRT_LINE_BODY(A, B, b_)                                                      \
+    do {                                                                             \
+        if ((medge >> (b_)) & 1u) line_far_edge<PTS, TBL, LN>(A, B, t, gc, acc);     \
+        else line_fast<PTS, TBL, LN>(A, B, t, gc, GRT_FAST_ACC);                     \
+    } while (0)
+#else
+#define GRT_LINE_BODY(A, B, b_) line_fast<PTS, TBL, LN>(A, B, t, gc, GRT_FAST_ACC)
+#endif
     GRT_TM_END(kTmClassify, 1);
 #if GRT_DBG_TIMERS
     int tm_n = __popc(m);
@@ -845,6 +865,7 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
         // two records in flight, in alternating register sets (no copies between them)
         RecA A0 = lds_rec_a(sa + 64u*(uint32_t)b);
         float4 B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
+        int b0 = b;
         for (;;)
         {
             bool more = m != 0;
@@ -852,16 +873,19 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
             m &= m - 1;
             RecA const A1 = lds_rec_a(sa + 64u*(uint32_t)b);
             float4 const B1 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
-            line_fast<PTS, TBL, LN>(A0, B0, t, gc, GRT_FAST_ACC);
+            int const b1 = b;
+            GRT_LINE_BODY(A0, B0, b0);
             if (!more) break;
             more = m != 0;
             b = more ? __ffs(m) - 1 : b;
             m &= m - 1;
             A0 = lds_rec_a(sa + 64u*(uint32_t)b);
             B0 = lds_f32x4(sa + 64u*(uint32_t)b + 16u);
-            line_fast<PTS, TBL, LN>(A1, B1, t, gc, GRT_FAST_ACC);
+            b0 = b;
+            GRT_LINE_BODY(A1, B1, b1);
             if (!more) break;
         }
+#undef GRT_LINE_BODY
 #undef GRT_FAST_ACC
 #ifdef GRT_SINGLE
         // the batch's float partial sums (<= 32 lines) join the double accumulators
@@ -882,12 +906,14 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
 #endif
     walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_r1<PTS, TBL, LN>(r.A, r.B, r.C, r.D, t, gc, acc); });
     GRT_TM_END(kTmR1, tm_n);
+#if !GRT_MERGE_EDGE
     m = __ballot_sync(0xffffffffu, cls == kClsFarEdge) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
     walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_far_edge<PTS, TBL, LN>(r.A, r.B, t, gc, acc); });
     GRT_TM_END(kTmFarEdge, tm_n);
+#endif
     m = __ballot_sync(0xffffffffu, cls == kClsNear) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
