@@ -256,3 +256,27 @@ def test_synthetic_hitran_records_are_160_chars(tmp_path):
     lines = open(ds.hitran).read().split("\n")
     assert lines[-1] == ""
     assert all(len(l) == 160 for l in lines[:-1]) and len(lines) == 71
+
+
+def test_fortran_bound_interfaces_match_the_headers():
+    """Every C symbol the reference's Fortran module binds (fortran-bindings/
+    grtcode_fortran.F90:127-554; fixture tests/golden/fortran_interfaces.json made by
+    tools/fortran_interfaces.py) has a prototype in include/*.h with the same number of
+    arguments and, position by position, the same class (by value / by reference, integer /
+    real / pointer / character).  No Fortran compiler exists here, so this is the check that
+    can be made; symbol export is covered by test_host_library_exports_reference_api."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "fortran_interfaces", os.path.join(ROOT, "tools", "fortran_interfaces.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    import json
+    fx = json.load(open(os.path.join(ROOT, "tests", "golden", "fortran_interfaces.json")))["interfaces"]
+    assert len(fx) >= 26
+    protos = mod.parse_headers(os.path.join(ROOT, "include"))
+    problems = mod.check(fx, protos)
+    assert not problems, problems
+    # the checker does notice a wrong argument list
+    broken = dict(protos)
+    broken["add_molecule"] = dict(protos["add_molecule"], args=protos["add_molecule"]["args"][:-1])
+    assert mod.check(fx, broken)
