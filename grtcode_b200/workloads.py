@@ -3,7 +3,7 @@
 Config 2 (the one the headline metric is quoted on): CIRC case 1, clear sky,
 longwave 1-3250 cm-1 and shortwave 1-50000 cm-1 at 0.01 cm-1, seven HITRAN
 molecules + H2O/O3 continua + three CIA pairs + the three CFCs of the case.
-The column itself is the real CIRC-1 profile (tests/golden/circ1_profile.json,
+The column itself is the real CIRC-1 profile (grtcode_b200/data/circ1_profile.json,
 copied from testing_harness/src/circ1.h by tools/make_golden.py); line lists
 and tables are synthetic (no HITRAN data in the mount).
 """
@@ -18,7 +18,7 @@ import numpy as np
 from . import synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CIRC1 = os.path.join(ROOT, "tests", "golden", "circ1_profile.json")
+CIRC1 = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "circ1_profile.json")
 
 LW_RANGE = (1., 3250.)
 SW_RANGE = (1., 50000.)

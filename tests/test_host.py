@@ -280,3 +280,14 @@ def test_fortran_bound_interfaces_match_the_headers():
     broken = dict(protos)
     broken["add_molecule"] = dict(protos["add_molecule"], args=protos["add_molecule"]["args"][:-1])
     assert mod.check(fx, broken)
+
+
+def test_package_data_is_self_contained():
+    """The product package reads its CIRC-1 input from its own data directory, not from
+    tests/ (the two copies are the same file, both written by tools/make_golden.py)."""
+    import filecmp
+    from grtcode_b200 import workloads
+    assert os.path.dirname(workloads.CIRC1).endswith(os.path.join("grtcode_b200", "data"))
+    assert filecmp.cmp(workloads.CIRC1, os.path.join(ROOT, "tests", "golden", "circ1_profile.json"),
+                       shallow=False)
+    assert len(workloads.circ1_column().p) == 55

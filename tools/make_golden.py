@@ -90,6 +90,10 @@ def main():
     for k in ("solar_zenith_angle", "surface_temperature", "toa_solar_irradiance"):
         prof[k] = c_scalar(c1, k)
     json.dump(prof, open(os.path.join(OUT, "circ1_profile.json"), "w"), indent=0)
+    # the product's copy (input data of BASELINE config 2): the package must not read tests/
+    data = os.path.join(os.path.dirname(OUT.rstrip("/")), "..", "grtcode_b200", "data")
+    os.makedirs(data, exist_ok=True)
+    json.dump(prof, open(os.path.join(data, "circ1_profile.json"), "w"), indent=0)
     print({k: len(v) for k, v in prof.items() if isinstance(v, list)})
     print({k: len(v) for k, v in pins["kernels"].items() if isinstance(v, list)})
     print(pins["tips"])
