@@ -159,6 +159,20 @@ int add_molecule(GasOptics_t * const gas_optics, int const molecule_id,
              (double)(MAX_NUM_LINES - 1));
     }
 
+    /* tips2017.c is absent from the reference mount: unless an external table supplied this
+       molecule's partition sums (GRT_TIPS_TABLE, host/tips.c) they are a substitute that only
+       reproduces the reference's test pins.  Say so once per molecule and process. */
+    {
+        static unsigned char warned[64];
+        if (grt_tips_is_substitute(molecule_id) && molecule_id < 64 && !warned[molecule_id])
+        {
+            warned[molecule_id] = 1;
+            LOG_WARN("partition sums Q(T) of %s are a SUBSTITUTE for TIPS-2017 (its source is "
+                     "not part of this build): line strengths are not HITRAN-accurate; set "
+                     "GRT_TIPS_TABLE=<file of 'mol iso T Q' rows> to supply real values.", name);
+        }
+    }
+
     /* Partition-sum tables of every isotopologue, shared verbatim with the device. */
     double *q = (double *)malloc(sizeof(double)*(size_t)(num_iso > 0 ? num_iso : 1)*GRT_TIPS_NT);
     if (q == NULL)

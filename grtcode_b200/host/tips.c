@@ -15,6 +15,9 @@
 #include <math.h>
 #include <pthread.h>
 #include <stddef.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 #include "molecule_table.h"
 #include "tips.h"
 
@@ -69,6 +72,18 @@ static MolInfo_t const mols[GRT_TIPS_NUM_MOLS + 1] = {
 
 static double table[GRT_TIPS_NUM_MOLS + 1][GRT_TIPS_MAX_ISO][GRT_TIPS_NT];
 static pthread_once_t once = PTHREAD_ONCE_INIT;
+
+/* The interpolant of one table row at T (inside the table range), for the loader. */
+static double grt_tips_q_unlocked(double const *tab, double T)
+{
+    double const tmax = (double)(GRT_TIPS_TMIN + GRT_TIPS_NT - 1);
+    if (T < (double)GRT_TIPS_TMIN) T = (double)GRT_TIPS_TMIN;
+    if (T >= tmax) return tab[GRT_TIPS_NT-1];
+    int const it = (int)T;
+    double const f = T - (double)it;
+    int const idx = it - GRT_TIPS_TMIN;
+    return tab[idx] + f*(tab[idx+1] - tab[idx]);
+}
 
 
 /* Synthetic ratio Q_iso/Q_main for isotopologues that have no anchors. */
@@ -165,9 +180,152 @@ static void build(void)
 }
 
 
+/* ---- external partition sums ---------------------------------------------------------
+ * GRT_TIPS_TABLE=<file> in the environment replaces the substitute for every (molecule,
+ * isotopologue) the file lists: text rows "mol iso T Q" (blank- or comma-separated, '#'
+ * starts a comment), T ascending within a (mol, iso) group, at least two rows per group.
+ * The 1 K table is filled by linear interpolation between the given points; outside the
+ * given range the substitute continues, scaled to meet the table at its ends.  The file is
+ * read once per process, inside the same table build the oracle's shim uses
+ * (oracle/tips_shim.c links this file), so both sides keep evaluating one function. */
+static int external_groups[GRT_TIPS_NUM_MOLS + 1];
+static char external_path[1024];
+static int external_rows = -1;        /* -1: no file; >= 0: rows used */
+
+typedef struct TipsRow
+{
+    int mol;
+    int iso;
+    double t;
+    double q;
+} TipsRow_t;
+
+static void apply_group(TipsRow_t const *r, int const n)
+{
+    if (n < 2)
+    {
+        return;
+    }
+    int const mol = r[0].mol;
+    int const iso = r[0].iso;
+    double *tab = table[mol][iso-1];
+    double const lo_ratio = r[0].q/grt_tips_q_unlocked(tab, r[0].t);
+    double const hi_ratio = r[n-1].q/grt_tips_q_unlocked(tab, r[n-1].t);
+    int i;
+    int k = 0;
+    for (i=0; i<GRT_TIPS_NT; ++i)
+    {
+        double const t = (double)(GRT_TIPS_TMIN + i);
+        if (t <= r[0].t)
+        {
+            tab[i] *= lo_ratio;
+        }
+        else if (t >= r[n-1].t)
+        {
+            tab[i] *= hi_ratio;
+        }
+        else
+        {
+            while (k + 2 < n && r[k+1].t < t)
+            {
+                ++k;
+            }
+            double const f = (t - r[k].t)/(r[k+1].t - r[k].t);
+            tab[i] = r[k].q + f*(r[k+1].q - r[k].q);
+        }
+    }
+    external_groups[mol] += 1;
+}
+
+static void load_external(char const *path)
+{
+    FILE *f = fopen(path, "r");
+    external_rows = 0;
+    snprintf(external_path, sizeof(external_path), "%s", path);
+    if (f == NULL)
+    {
+        fprintf(stderr, "[grtcode] GRT_TIPS_TABLE=%s cannot be opened: keeping the substitute "
+                "partition sums.\n", path);
+        return;
+    }
+    size_t cap = 4096, n = 0;
+    TipsRow_t *rows = (TipsRow_t *)malloc(sizeof(TipsRow_t)*cap);
+    char line[512];
+    while (rows != NULL && fgets(line, sizeof(line), f) != NULL)
+    {
+        char *c;
+        for (c=line; *c; ++c)
+        {
+            if (*c == ',' || *c == ';' || *c == '\t') *c = ' ';
+            if (*c == '#') { *c = '\0'; break; }
+        }
+        TipsRow_t r;
+        if (sscanf(line, "%d %d %lf %lf", &r.mol, &r.iso, &r.t, &r.q) != 4)
+        {
+            continue;
+        }
+        if (r.mol < 1 || r.mol > GRT_TIPS_NUM_MOLS || r.iso < 1 || r.iso > GRT_TIPS_MAX_ISO ||
+            !(r.q > 0.) || !(r.t > 0.))
+        {
+            continue;
+        }
+        if (n == cap)
+        {
+            cap *= 2;
+            TipsRow_t *grown = (TipsRow_t *)realloc(rows, sizeof(TipsRow_t)*cap);
+            if (grown == NULL) break;
+            rows = grown;
+        }
+        rows[n++] = r;
+    }
+    fclose(f);
+    size_t start = 0, i;
+    for (i=1; i<=n; ++i)
+    {
+        int const boundary = i == n || rows[i].mol != rows[start].mol ||
+                             rows[i].iso != rows[start].iso || !(rows[i].t > rows[i-1].t);
+        if (boundary)
+        {
+            apply_group(rows + start, (int)(i - start));
+            if (i - start >= 2) external_rows += (int)(i - start);
+            start = i;
+        }
+    }
+    free(rows);
+}
+
+static void build_all(void)
+{
+    build();
+    char const *path = getenv("GRT_TIPS_TABLE");
+    if (path != NULL && path[0] != '\0')
+    {
+        load_external(path);
+    }
+}
+
+/* 1 if Q of this molecule is the built-in substitute (no external group was loaded). */
+int grt_tips_is_substitute(int const mol)
+{
+    pthread_once(&once, build_all);
+    if (mol < 1 || mol > GRT_TIPS_NUM_MOLS)
+    {
+        return 1;
+    }
+    return external_groups[mol] == 0;
+}
+
+/* Path of the external table in use (empty string if none) and the rows taken from it. */
+char const *grt_tips_external(int * const rows)
+{
+    pthread_once(&once, build_all);
+    if (rows != NULL) *rows = external_rows < 0 ? 0 : external_rows;
+    return external_rows < 0 ? "" : external_path;
+}
+
 double const *grt_tips_table(int const mol, int const iso)
 {
-    pthread_once(&once, build);
+    pthread_once(&once, build_all);
     if (mol < 1 || mol > GRT_TIPS_NUM_MOLS || iso < 1 || iso > GRT_TIPS_MAX_ISO)
     {
         return NULL;

@@ -28,6 +28,12 @@ double grt_tips_q(int mol, double T, int iso);
 /* Pointer to the GRT_TIPS_NT-entry table of (mol, iso) (for the device upload). */
 double const *grt_tips_table(int mol, int iso);
 
+/* 1 if the molecule's Q is the built-in substitute, 0 if an external table supplied it
+ * (GRT_TIPS_TABLE=<file> with rows "mol iso T Q", read once per process; see tips.c). */
+int grt_tips_is_substitute(int mol);
+/* Path of the external table in use ("" if none); *rows = rows taken from it. */
+char const *grt_tips_external(int *rows);
+
 /* Number of isotopologues the molecule table lists (molecules.c:36-306). */
 int grt_tips_num_iso(int mol);
 

@@ -49,7 +49,8 @@ def grid_size(w0: float, wn: float, dw: float) -> int:
 class SpectralChunk:
     """Rank `rank` OWNS global grid points [first, last] (its share of the trapezoid
     intervals; `last` is the next chunk's `first`) and COMPUTES on [lo, hi] = the owned
-    points plus a halo of ceil(25/dw) + 1 points on either side, clipped to the global grid:
+    points plus a halo of ceil(25/dw) + 1 + ceil(max|delta| p/dw) points on either side, clipped
+    to the global grid:
     the reference only lets lines centred inside the grid contribute (kernels.c:431-433),
     so lines centred within the cut-off of an owned point must lie on the rank's grid."""
     rank: int
@@ -79,7 +80,7 @@ class SpectralChunk:
 
 
 def split_spectral_range(w0: float, wn: float, dw: float, world: int,
-                         cost: np.ndarray | None = None) -> list[SpectralChunk]:
+                         cost: np.ndarray | None = None, shift: float = 0.) -> list[SpectralChunk]:
     """Cut the grid [w0, wn] @ dw into `world` chunks.  Neighbouring chunks share one grid
     point; every chunk keeps the global spacing and starts on a global grid point,
     w(i) = w0 + i*dw (spectral_grid.c:94).  Without `cost` the chunks hold (almost) equal
@@ -93,7 +94,10 @@ def split_spectral_range(w0: float, wn: float, dw: float, world: int,
     # F of kernels.c:417, plus one point: lines in the half interval beyond a grid end are
     # dropped by the parser (parse_HITRAN_file.c:349), so their reach must end short of
     # the owned points
-    halo = int(math.ceil(float(np.float32(LINE_CUTOFF))/dw)) + 1
+    # `shift` [cm-1] = max |delta|*p over the line list and column: a rank's parser keeps lines
+    # by UNSHIFTED centre while the kernel windows a line around its pressure-SHIFTED centre
+    # (kernels.c:44,431), so the halo has to cover the cut-off plus the largest shift
+    halo = int(math.ceil(float(np.float32(LINE_CUTOFF))/dw)) + 1 + int(math.ceil(abs(shift)/dw))
     if cost is None:
         cuts = [(r*intervals)//world for r in range(world + 1)]
     else:
@@ -118,6 +122,24 @@ def split_spectral_range(w0: float, wn: float, dw: float, world: int,
         hi = min(b + halo, n - 1)
         chunks.append(SpectralChunk(r, a, b, lo, hi, w0 + lo*dw, w0 + hi*dw, dw))
     return chunks
+
+
+def max_pressure_shift(hitran_path: str, molecules=None) -> float:
+    """Largest |delta| [cm-1 atm-1] of a HITRAN .par file (field 9 = columns 60-67,
+    parse_HITRAN_file.c:79-100), optionally over the given molecule ids only."""
+    raw = np.fromfile(hitran_path, dtype=np.uint8)
+    if raw.size == 0:
+        return 0.
+    nl = int(np.argmax(raw == 10))
+    rec = nl + 1
+    if raw[nl] != 10 or nl < 160 or raw.size % rec:
+        raise ValueError(f"{hitran_path}: not fixed-length HITRAN records")
+    tab = raw.reshape(-1, rec)
+    d = np.ascontiguousarray(tab[:, 59:67]).view("S8").ravel().astype(np.float64)
+    if molecules is not None:
+        mol = np.ascontiguousarray(tab[:, 0:2]).view("S2").ravel().astype(np.int64)
+        d = d[np.isin(mol, np.asarray(list(molecules), dtype=np.int64))]
+    return float(np.abs(d).max()) if d.size else 0.
 
 
 def line_centres(hitran_path: str, molecules=None) -> np.ndarray:
@@ -259,7 +281,11 @@ class SpectralSplitColumn:
                                      line_centres(band.dataset.hitran, molecules))
             if cost_override is not None and band.name in cost_override:
                 cost = np.asarray(cost_override[band.name], dtype=np.float64)
-            every = split_spectral_range(band.w0, band.wn, band.dw, world, cost)
+            # largest pressure shift of any line in this column [cm-1]: mb -> atm as the
+            # library does (gas_optics.c:445)
+            shift = max_pressure_shift(band.dataset.hitran, molecules) * \
+                float(np.max(np.abs(column.p)))*0.000986923
+            every = split_spectral_range(band.w0, band.wn, band.dw, world, cost, shift=shift)
             ch = every[rank]
             self.chunks[band.name] = ch
             self.all_chunks[band.name] = every

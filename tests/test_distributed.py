@@ -185,3 +185,22 @@ def test_measured_costs_move_the_cuts_towards_the_slow_ranks():
     shaped = P.measured_costs(np.linspace(1., 2., n_int), chunks, secs)
     seg = shaped[chunks[0].first:chunks[0].last]
     assert seg[-1] > seg[0]            # the model's shape is kept inside a chunk
+
+
+def test_halo_covers_the_pressure_shift(tmp_path):
+    """A line whose unshifted centre lies just outside a rank's cut-off halo but whose shifted
+    centre reaches an owned point must be on the rank's grid: the halo grows by
+    ceil(max|delta| p/dw) points."""
+    from grtcode_b200 import parallel as P, synth
+    plain = P.split_spectral_range(1., 1001., 0.01, 4)
+    wide = P.split_spectral_range(1., 1001., 0.01, 4, shift=0.031)
+    for a, b in zip(plain, wide):
+        assert (a.first, a.last) == (b.first, b.last)
+        if a.lo > 0:
+            assert a.lo - b.lo == 4
+        if a.hi < 100000:
+            assert b.hi - a.hi == 4
+    ds = synth.make_dataset(str(tmp_path), 100., 200., {1: 50, 2: 50}, seed=1)
+    d = P.max_pressure_shift(ds.hitran)
+    assert 0.01 < d <= 0.02        # synth draws delta from U(-0.02, 0.015)
+    assert P.max_pressure_shift(ds.hitran, molecules=(7,)) == 0.

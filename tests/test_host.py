@@ -291,3 +291,41 @@ def test_package_data_is_self_contained():
     assert filecmp.cmp(workloads.CIRC1, os.path.join(ROOT, "tests", "golden", "circ1_profile.json"),
                        shallow=False)
     assert len(workloads.circ1_column().p) == 55
+
+
+def test_external_partition_sums_replace_the_substitute(built, tmp_path):
+    """GRT_TIPS_TABLE=<file of 'mol iso T Q' rows>: read once per process, so checked in a
+    subprocess.  Listed (molecule, isotopologue) groups follow the file (linear between its
+    points), other molecules keep the substitute, and add_molecule warns only for those."""
+    import subprocess, sys, textwrap
+    table = tmp_path/"tips.txt"
+    rows = ["# mol iso T Q"] + [f"2 1 {t} {2.*t + 5.}" for t in range(100, 501, 50)]
+    table.write_text("\n".join(rows) + "\n")
+    ds = synth.make_dataset(str(tmp_path/"d"), 600., 650., {1: 5, 2: 5}, seed=2)
+    code = textwrap.dedent(f"""
+        import ctypes as C, sys
+        sys.path.insert(0, {ROOT!r})
+        from grtcode_b200 import api
+        L = api.load()
+        L.grt_tips_is_substitute.argtypes = [C.c_int]
+        print("Q", api.tips_q(2, 225., 1), api.tips_q(2, 100., 1), api.tips_q(2, 500., 1))
+        print("SUB", L.grt_tips_is_substitute(1), L.grt_tips_is_substitute(2))
+        L.grtcode_set_verbosity(2)
+        try:
+            g = api.spectral_grid(600., 650., 0.1)
+            go = api.GasOptics(5, g, {ds.hitran!r}, None, None)
+            go.add_molecule(1); go.add_molecule(2)
+        except Exception as e:          # no GPU here: the warning is printed before the upload
+            print("EXC", type(e).__name__)
+    """)
+    env = dict(os.environ, GRT_TIPS_TABLE=str(table))
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True)
+    text = out.stdout + out.stderr
+    assert "Q 455.0 205.0 1005.0" in text, text[-2000:]
+    assert "SUB 1 0" in text
+    # without the variable both are substitutes and the values are the built-in ones
+    out2 = subprocess.run([sys.executable, "-c", code], env={k: v for k, v in os.environ.items()
+                                                             if k != "GRT_TIPS_TABLE"},
+                          capture_output=True, text=True)
+    assert "SUB 1 1" in out2.stdout
+    assert "Q 455.0" not in out2.stdout
