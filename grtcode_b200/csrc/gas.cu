@@ -1050,7 +1050,30 @@ static int binned_optical_depth(grt_gas *g, int const method, LayerView const &l
     bp.evals = g->d_evals;
     if (bp.bins.n > 0x7fffffffull) return fail("too many spectral bins");
     size_t const smem = sizeof(double)*(size_t)bp.bins.ppb*kBinGroup*(bp.bins.ppb <= kBinLanePerLine ? 33 : 1);
-    if (smem > 40*1024) return fail("spectral resolution too fine for the binned methods");
+    // Up to 48 KB is available by default; beyond that the kernel opts in to the large dynamic
+    // shared memory of sm_100 (per device, as the attribute is): 200 KB holds the sums of
+    // eight bins down to a resolution of 0.00032 cm-1, finer than the reference's own lower
+    // limit (MIN_RESOLUTION 0.001, grtcode_config.h:58).
+    constexpr size_t kBinSmemMax = 200*1024;
+    if (smem > kBinSmemMax)
+    {
+        return fail("spectral resolution %g cm-1 too fine for the binned methods (%zu bytes of "
+                    "shared memory per block, limit %zu): use line_sample", g->dw, smem,
+                    kBinSmemMax);
+    }
+    if (smem > 40*1024)
+    {
+        static bool configured[64] = {};
+        int dev = 0;
+        GRT_CUDA(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !configured[dev])
+        {
+            GRT_CUDA(cudaFuncSetAttribute(bin_gather_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)kBinSmemMax));
+            if (dev >= 0 && dev < 64) configured[dev] = true;
+        }
+    }
     size_t const nranges = (size_t)L*bp.bins.n*(size_t)std::max(bp.num_slots, 1);
     if (nranges > g->ranges_capacity)
     {

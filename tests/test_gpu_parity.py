@@ -150,6 +150,26 @@ def test_binned_methods(built, tmp_path, method, case):
     assert rel.max() <= TAU_RTOL
 
 
+@pytest.mark.parametrize("method", [0, 1], ids=["wavenumber_sweep", "line_sweep"])
+def test_binned_methods_at_the_finest_resolution_the_reference_allows(built, tmp_path, method):
+    """0.001 cm-1 (MIN_RESOLUTION, grtcode_config.h:58): 1001 points per bin, 64 KB of
+    shared memory per block -- beyond the 48 KB default, the gather kernel opts in to the
+    large dynamic shared memory instead of refusing (wavenumber_sweep is the library default
+    method, so a caller that passes no method must not fail here)."""
+    # at least 26 bins: on a narrower grid the reference itself indexes bins.w out of bounds
+    # ((bins.n-1)-nbin wraps as unsigned, kernels.c:199,238) and its result is undefined
+    lines = {synth.H2O: 60, synth.CO2: 80}
+    w0, wn, dw, levels = 1000., 1030., 0.001, 4
+    ds = parity.build_dataset(str(tmp_path), w0, wn, lines, 41)
+    mols = tuple(lines)
+    col = synth.make_column(levels, np.random.default_rng(41), molecules=mols)
+    want = parity.oracle_column(ds, w0, wn, dw, col, mols, solvers=False, method=method)
+    got = parity.gpu_column(ds, w0, wn, dw, col, mols, solvers=False, method=method)
+    rel = parity.relative_error(got["tau"], want["tau"])
+    print(f"method {method} @ {dw}: tau max rel {rel.max():.3e}")
+    assert rel.max() <= TAU_RTOL
+
+
 # ---- BASELINE full sizes: size-independent properties (no oracle: it would take hours) ----
 
 def _full_size_tau(ds, w0, wn, dw, col, mols, method=2, use_ctm=False):
