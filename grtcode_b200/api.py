@@ -132,6 +132,10 @@ def load():
                                            C.POINTER(C.c_double)]
     L.gas_optics_debug_line_order.argtypes = [C.POINTER(GasOpticsStruct), C.c_uint64,
                                               C.POINTER(C.c_uint64)]
+    L.gas_optics_debug_table.argtypes = [C.POINTER(GasOpticsStruct), C.c_int, C.c_int,
+                                         C.POINTER(C.c_double)]
+    L.grt_table_on_grid.argtypes = [C.c_char_p, C.c_int, C.c_double, C.c_double, C.c_ulonglong,
+                                    C.POINTER(_dbl_p)]
     L.rayleigh_scattering.argtypes = [C.POINTER(Optics), _dbl_p]
     L.create_longwave.argtypes = [C.POINTER(Longwave), C.c_int, C.POINTER(SpectralGrid),
                                   C.POINTER(C.c_int)]
@@ -383,6 +387,15 @@ class GasOptics:
             "gas_optics_debug_records")
         return rep, y, v
 
+    def debug_table(self, kind: int, index: int = 0) -> np.ndarray:
+        """A continuum / cross-section table as it lives on the device (float64[n]): kind
+        0-3 = H2O S296 / CKDS / F296 / CKDF, 4 = O3, 5 = CFC `index`, 6 = CIA pair `index`."""
+        out = np.empty(int(self.grid.n), dtype=np.float64)
+        _check(self.L.gas_optics_debug_table(C.byref(self.s), kind, index,
+                                             out.ctypes.data_as(C.POINTER(C.c_double))),
+               "gas_optics_debug_table")
+        return out
+
     def debug_line_order(self, count: int) -> np.ndarray:
         order = np.empty(count, dtype=np.uint64)
         _check(self.L.gas_optics_debug_line_order(
@@ -505,6 +518,20 @@ def solar_flux(grid: SpectralGrid, path: str) -> np.ndarray:
     _check(L.create_solar_flux(C.byref(s), C.byref(grid), path.encode()), "create_solar_flux")
     out = np.ctypeslib.as_array(s.incident_flux, shape=(int(s.n),)).copy()
     _check(L.destroy_solar_flux(C.byref(s)), "destroy_solar_flux")
+    return out
+
+
+def table_on_grid_host(path: str, cols: int, grid: SpectralGrid) -> np.ndarray:
+    """The HOST resampling of a CSV table to the grid (host/parse_csv.c: grt_table_on_grid,
+    the reference's interpolate_to_grid rule) -- what the device resampler must reproduce."""
+    L = load()
+    p = _dbl_p()
+    _check(L.grt_table_on_grid(path.encode(), cols, grid.w0, grid.dw, int(grid.n), C.byref(p)),
+           "grt_table_on_grid")
+    out = np.ctypeslib.as_array(p, shape=(int(grid.n),)).astype(np.float64)
+    libc = C.CDLL(None)
+    libc.free.argtypes = [C.c_void_p]
+    libc.free(C.cast(p, C.c_void_p))
     return out
 
 

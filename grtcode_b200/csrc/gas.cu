@@ -501,6 +501,37 @@ __global__ void patch_records_kernel(RecordPatch const *patch, unsigned const co
     if (k < count) recs[patch[k].idx] = patch[k].rec;
 }
 
+// Setup on the device: a continuum / cross-section table given by its m samples (x, y) is
+// resampled to the spectral grid by one thread per grid point -- the reference's
+// interpolate_to_grid / interpolate2 / linear_sample (spectral_grid.c:87-112,
+// utilities.c:149-246): grid wavenumber w_i = w0 + i*dw; a point in (x_j, x_{j+1}] gets
+// slope*w + intercept with slope = (y_{j+1} - y_j)/(x_{j+1} - x_j), intercept = y_j -
+// slope*x_j; points at or below x_0 or beyond x_{m-1} stay 0 (no extrapolation).  The same
+// expressions in the same order and type (fp_t) as the host code, so the same bits.
+__global__ void __launch_bounds__(256)
+resample_table_kernel(real_t const *x, real_t const *y, unsigned const m, double const w0,
+                      double const dw, uint64_t const n, double *out)
+{
+    uint64_t const i = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typedef real_t T;
+    T const w = (T)(w0 + (double)i*dw);
+    T v = (T)0;
+    if (w > x[0] && w <= x[m-1])
+    {
+        unsigned lo = 0, hi = m - 1;             // x[lo] < w <= x[hi]
+        while (hi - lo > 1)
+        {
+            unsigned const mid = (lo + hi)/2;
+            if (x[mid] < w) lo = mid; else hi = mid;
+        }
+        T const slope = (y[lo+1] - y[lo])/(x[lo+1] - x[lo]);
+        T const intercept = y[lo] - slope*x[lo];
+        v = slope*w + intercept;
+    }
+    out[i] = (double)v;
+}
+
 
 }  // namespace grt
 
@@ -605,6 +636,30 @@ static int upload_table(grt_gas *g, real_t const *host_in, double const **dev_ou
     GRT_CUDA(cudaMalloc(&d, sizeof(double)*g->nw));
     GRT_CUDA(cudaMemcpyAsync(d, host, sizeof(double)*g->nw, cudaMemcpyHostToDevice, g->stream));
     GRT_CUDA(cudaStreamSynchronize(g->stream));
+    g->owned_tables.push_back(d);
+    *dev_out = d;
+    return 0;
+}
+
+
+// A table from its samples, resampled on the device (no n-point host array, no n-point copy).
+static int resample_table(grt_gas *g, real_t const *x, real_t const *y, uint64_t m,
+                          double const **dev_out)
+{
+    if (x == nullptr || y == nullptr) return fail("null table samples");
+    if (m < 2 || m > 0x7fffffffull) return fail("a table needs at least two samples (%llu given)",
+                                                 (unsigned long long)m);
+    real_t *xy = nullptr;
+    double *d = nullptr;
+    GRT_CUDA(cudaMalloc(&xy, sizeof(real_t)*2*m));
+    GRT_CUDA(cudaMalloc(&d, sizeof(double)*g->nw));
+    GRT_CUDA(cudaMemcpyAsync(xy, x, sizeof(real_t)*m, cudaMemcpyHostToDevice, g->stream));
+    GRT_CUDA(cudaMemcpyAsync(xy + m, y, sizeof(real_t)*m, cudaMemcpyHostToDevice, g->stream));
+    resample_table_kernel<<<(unsigned)((g->nw + 255)/256), 256, 0, g->stream>>>(
+        xy, xy + m, (unsigned)m, g->w0, g->dw, g->nw, d);
+    GRT_CUDA(cudaGetLastError());
+    GRT_CUDA(cudaStreamSynchronize(g->stream));
+    GRT_CUDA(cudaFree(xy));
     g->owned_tables.push_back(d);
     *dev_out = d;
     return 0;
@@ -1278,6 +1333,74 @@ int grt_gas_add_cia(grt_gas *g, int species0, int species1, real_t const *cross_
     g->meta.cia_id[k][0] = species0;
     g->meta.cia_id[k][1] = species1;
     g->tab.num_cias = g->meta.num_cias = k + 1;
+    return 0;
+}
+
+int grt_gas_set_h2o_continuum_samples(grt_gas *g, real_t const *const x[4],
+                                      real_t const *const y[4], uint64_t const m[4])
+{
+    if (g == nullptr || x == nullptr || y == nullptr || m == nullptr) return fail("null argument");
+    GRT_CUDA(cudaSetDevice(g->device));
+    for (int k=0; k<4; ++k) GRT_TRY(resample_table(g, x[k], y[k], m[k], &g->tab.h2o[k]));
+    g->tab.h2o_slot = find_slot(g, 1);
+    return 0;
+}
+
+int grt_gas_set_o3_continuum_samples(grt_gas *g, real_t const *x, real_t const *y, uint64_t m)
+{
+    if (g == nullptr) return fail("null gas handle");
+    GRT_CUDA(cudaSetDevice(g->device));
+    GRT_TRY(resample_table(g, x, y, m, &g->tab.o3));
+    g->tab.o3_slot = find_slot(g, 3);
+    return 0;
+}
+
+int grt_gas_add_cfc_samples(grt_gas *g, int cfc_id, real_t const *x, real_t const *y, uint64_t m)
+{
+    if (g == nullptr) return fail("null gas handle");
+    if (cfc_id < 0 || cfc_id >= GRT_MAX_CFCS) return fail("unrecognized CFC id %d", cfc_id);
+    if (g->tab.num_cfcs >= GRT_MAX_CFCS) return fail("too many CFCs");
+    GRT_CUDA(cudaSetDevice(g->device));
+    int const k = g->tab.num_cfcs;
+    GRT_TRY(resample_table(g, x, y, m, &g->tab.cfc[k]));
+    g->meta.cfc_id[k] = cfc_id;
+    g->tab.num_cfcs = g->meta.num_cfcs = k + 1;
+    return 0;
+}
+
+int grt_gas_add_cia_samples(grt_gas *g, int species0, int species1, real_t const *x,
+                            real_t const *y, uint64_t m)
+{
+    if (g == nullptr) return fail("null gas handle");
+    if (species0 < 0 || species0 >= GRT_NUM_CIA_SPECIES || species1 < 0 ||
+        species1 >= GRT_NUM_CIA_SPECIES)
+    {
+        return fail("unrecognized CIA species (%d, %d)", species0, species1);
+    }
+    if (g->tab.num_cias >= GRT_MAX_CIAS) return fail("too many CIA pairs");
+    GRT_CUDA(cudaSetDevice(g->device));
+    int const k = g->tab.num_cias;
+    GRT_TRY(resample_table(g, x, y, m, &g->tab.cia[k]));
+    g->meta.cia_id[k][0] = species0;
+    g->meta.cia_id[k][1] = species1;
+    g->tab.num_cias = g->meta.num_cias = k + 1;
+    return 0;
+}
+
+/* Diagnostic read-back of a device table (tests): kind 0-3 = H2O S296 / CKDS / F296 / CKDF,
+ * 4 = O3, 5 = CFC number `index` (in add order), 6 = CIA pair number `index`. */
+int grt_gas_debug_table(grt_gas *g, int kind, int index, double *out)
+{
+    if (g == nullptr || out == nullptr) return fail("null argument");
+    double const *src = nullptr;
+    if (kind >= 0 && kind < 4) src = g->tab.h2o[kind];
+    else if (kind == 4) src = g->tab.o3;
+    else if (kind == 5 && index >= 0 && index < g->tab.num_cfcs) src = g->tab.cfc[index];
+    else if (kind == 6 && index >= 0 && index < g->tab.num_cias) src = g->tab.cia[index];
+    if (src == nullptr) return fail("no such table (kind %d, index %d)", kind, index);
+    GRT_CUDA(cudaSetDevice(g->device));
+    GRT_CUDA(cudaStreamSynchronize(g->stream));
+    GRT_CUDA(cudaMemcpy(out, src, sizeof(double)*g->nw, cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -97,9 +97,29 @@ int destroy_gas_optics(GasOptics_t * const gas_optics)
     return GRTCODE_SUCCESS;
 }
 
-/* Reads <dir>/<name>, checks its column count and resamples column 1 to the grid. */
-static int continuum_table(GasOptics_t const *go, char const *dir, char const *name,
-                           int cols, fp_t **out)
+/* Reads <dir>/<name> and checks it; the samples go to the device, which resamples them to the
+ * grid (grt_sm100.h: grt_gas_*_samples). */
+static int table_samples(char const *dir, char const *name, int cols, fp_t **table, int *rows)
+{
+    char path[DIR_PATH_LEN + 64];
+    if (dir != NULL)
+    {
+        snprintf(path, sizeof(path), "%s/%s", dir, name);
+    }
+    else
+    {
+        snprintf(path, sizeof(path), "%s", name);
+    }
+    TRY(grt_table_samples(path, cols, table, rows));
+    return GRTCODE_SUCCESS;
+}
+
+/* Reads <dir>/<name>, checks its column count and resamples column 1 to the grid on the HOST
+ * (kept for the tests that compare the device resampler with it). */
+int grt_continuum_table_host(GasOptics_t const *go, char const *dir, char const *name,
+                             int cols, fp_t **out);
+int grt_continuum_table_host(GasOptics_t const *go, char const *dir, char const *name,
+                             int cols, fp_t **out)
 {
     char path[DIR_PATH_LEN + 64];
     if (dir != NULL)
@@ -205,15 +225,30 @@ int add_molecule(GasOptics_t * const gas_optics, int const molecule_id,
     {
         /* water_vapor_continuum.c:49-64: two 2-column and two 4-column tables. */
         LOG_MESG("Using the %s continuum.", name);
+        /* S296, CKDS, F296, CKDF: the argument order of launch.c:165-170 */
+        static char const * const files[4] = {"296MTCKD25_S.csv", "CKDS.csv", "296MTCKD25_F.csv",
+                                              "CKDF.csv"};
+        static int const cols[4] = {2, 4, 2, 4};
         fp_t *t[4] = {NULL, NULL, NULL, NULL};
-        int r = continuum_table(gas_optics, gas_optics->h2o_ctm_dir, "296MTCKD25_S.csv", 2, &t[0]);
-        if (r == GRTCODE_SUCCESS) r = continuum_table(gas_optics, gas_optics->h2o_ctm_dir, "CKDS.csv", 4, &t[1]);
-        if (r == GRTCODE_SUCCESS) r = continuum_table(gas_optics, gas_optics->h2o_ctm_dir, "296MTCKD25_F.csv", 2, &t[2]);
-        if (r == GRTCODE_SUCCESS) r = continuum_table(gas_optics, gas_optics->h2o_ctm_dir, "CKDF.csv", 4, &t[3]);
+        fp_t const *x[4];
+        fp_t const *y[4];
+        uint64_t m[4];
+        int r = GRTCODE_SUCCESS;
+        for (k=0; k<4 && r == GRTCODE_SUCCESS; ++k)
+        {
+            int rows = 0;
+            r = table_samples(gas_optics->h2o_ctm_dir, files[k], cols[k], &t[k], &rows);
+            if (r == GRTCODE_SUCCESS)
+            {
+                x[k] = t[k];
+                y[k] = t[k] + rows;        /* first value column only */
+                m[k] = (uint64_t)rows;
+            }
+        }
         int g = 0;
         if (r == GRTCODE_SUCCESS)
         {
-            g = grt_gas_set_h2o_continuum((grt_gas *)gas_optics->sm100, t[0], t[1], t[2], t[3]);
+            g = grt_gas_set_h2o_continuum_samples((grt_gas *)gas_optics->sm100, x, y, m);
         }
         for (k=0; k<4; ++k) free(t[k]);
         if (r != GRTCODE_SUCCESS)
@@ -227,8 +262,10 @@ int add_molecule(GasOptics_t * const gas_optics, int const molecule_id,
     {
         LOG_MESG("Using the %s continuum.", name);
         fp_t *t = NULL;
-        TRY(continuum_table(gas_optics, NULL, gas_optics->o3_ctm_file, 2, &t));
-        int const g = grt_gas_set_o3_continuum((grt_gas *)gas_optics->sm100, t);
+        int rows = 0;
+        TRY(table_samples(NULL, gas_optics->o3_ctm_file, 2, &t, &rows));
+        int const g = grt_gas_set_o3_continuum_samples((grt_gas *)gas_optics->sm100, t, t + rows,
+                                                       (uint64_t)rows);
         free(t);
         if (g != 0) return grt_gpu_failure(__FILE__, __LINE__);
     }
@@ -271,8 +308,10 @@ int add_cfc(GasOptics_t * const gas_optics, int const cfc_id, char const * const
         FAIL(GRTCODE_VALUE_ERR, "cfc %d has already been added.", cfc_id);
     }
     fp_t *t = NULL;
-    TRY(continuum_table(gas_optics, NULL, filepath, 2, &t));
-    int const g = grt_gas_add_cfc((grt_gas *)gas_optics->sm100, cfc_id, t);
+    int rows = 0;
+    TRY(table_samples(NULL, filepath, 2, &t, &rows));
+    int const g = grt_gas_add_cfc_samples((grt_gas *)gas_optics->sm100, cfc_id, t, t + rows,
+                                          (uint64_t)rows);
     free(t);
     if (g != 0) return grt_gpu_failure(__FILE__, __LINE__);
     gas_optics->num_cfcs++;
@@ -318,8 +357,10 @@ int add_cia(GasOptics_t * const gas_optics, int const species1, int const specie
         FAIL(GRTCODE_RANGE_ERR, "at most %d CIA pairs are supported.", MAX_NUM_CIAS);
     }
     fp_t *t = NULL;
-    TRY(continuum_table(gas_optics, NULL, filepath, 2, &t));
-    int const g = grt_gas_add_cia((grt_gas *)gas_optics->sm100, species1, species2, t);
+    int rows = 0;
+    TRY(table_samples(NULL, filepath, 2, &t, &rows));
+    int const g = grt_gas_add_cia_samples((grt_gas *)gas_optics->sm100, species1, species2, t,
+                                          t + rows, (uint64_t)rows);
     free(t);
     if (g != 0) return grt_gpu_failure(__FILE__, __LINE__);
     int const index = gas_optics->num_cias++;
@@ -419,5 +460,14 @@ int gas_optics_class_histogram(GasOptics_t const * const gas_optics, uint64_t ou
     REQUIRE_PTR(gas_optics);
     REQUIRE_PTR(out);
     GPU(grt_gas_class_histogram((grt_gas *)gas_optics->sm100, out));
+    return GRTCODE_SUCCESS;
+}
+
+int gas_optics_debug_table(GasOptics_t const * const gas_optics, int const kind, int const index,
+                           double * const out)
+{
+    REQUIRE_PTR(gas_optics);
+    REQUIRE_PTR(out);
+    GPU(grt_gas_debug_table((grt_gas *)gas_optics->sm100, kind, index, out));
     return GRTCODE_SUCCESS;
 }

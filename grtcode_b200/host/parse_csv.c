@@ -138,6 +138,35 @@ int grt_read_csv(char const *path, int *num_rows, int *num_cols, fp_t **values)
     return GRTCODE_SUCCESS;
 }
 
+/* The samples of a two-column table (column 0 = x, column 1 = y) for the device resampler:
+ * reads the file, checks its column count and the conditions interpolate2 checks
+ * (utilities.c:157-166: at least two points, x strictly increasing).  *table is the
+ * column-major buffer of grt_read_csv (free it); x = *table, y = *table + *rows. */
+int grt_table_samples(char const *path, int expected_cols, fp_t **table, int *rows)
+{
+    int cols;
+    fp_t *raw = NULL;
+    TRY(grt_read_csv(path, rows, &cols, &raw));
+    if (cols != expected_cols)
+    {
+        free(raw);
+        FAIL(GRTCODE_VALUE_ERR, "The number of columns (%d) in file %s does not match the"
+             " expected number (%d).", cols, path, expected_cols);
+    }
+    if (*rows < 2)
+    {
+        free(raw);
+        FAIL(GRTCODE_VALUE_ERR, "at least two x points required (%d given).", *rows);
+    }
+    if (!monotonically_increasing(raw, (size_t)*rows))
+    {
+        free(raw);
+        FAIL(GRTCODE_VALUE_ERR, "x (%p) must be monotonically increasing.", (void const *)raw);
+    }
+    *table = raw;
+    return GRTCODE_SUCCESS;
+}
+
 int grt_table_on_grid(char const *path, int expected_cols, double w0, double dw,
                       unsigned long long n, fp_t **on_grid)
 {

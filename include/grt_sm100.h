@@ -86,6 +86,26 @@ int grt_gas_set_o3_continuum(grt_gas *gas, grt_real const *cross_section);
 int grt_gas_add_cfc(grt_gas *gas, int cfc_id, grt_real const *cross_section);
 int grt_gas_add_cia(grt_gas *gas, int species0, int species1, grt_real const *cross_section);
 
+/* The same tables given by their SAMPLES (x ascending, at least two; as read from the CSV
+ * files) and resampled to the grid ON THE DEVICE by one thread per grid point with the
+ * reference's rule (interpolate_to_grid / interpolate2 / linear_sample,
+ * utilities/src/spectral_grid.c:87-112, utilities.c:149-246: linear inside (x_j, x_{j+1}],
+ * 0 at or below x_0 and beyond x_m-1): the setup path of SURVEY section 8 f.3 -- no
+ * num_wpoints-sized host array and no num_wpoints-sized copy per table.  h2o: the four
+ * tables in the order S296, CKDS, F296, CKDF. */
+int grt_gas_set_h2o_continuum_samples(grt_gas *gas, grt_real const *const x[4],
+                                      grt_real const *const y[4], uint64_t const m[4]);
+int grt_gas_set_o3_continuum_samples(grt_gas *gas, grt_real const *x, grt_real const *y,
+                                     uint64_t m);
+int grt_gas_add_cfc_samples(grt_gas *gas, int cfc_id, grt_real const *x, grt_real const *y,
+                            uint64_t m);
+int grt_gas_add_cia_samples(grt_gas *gas, int species0, int species1, grt_real const *x,
+                            grt_real const *y, uint64_t m);
+/* Diagnostic read-back of a device table (tests): kind 0-3 = H2O S296 / CKDS / F296 / CKDF,
+ * 4 = O3, 5 = CFC number `index` (add order), 6 = CIA pair number `index`; out has
+ * num_wpoints doubles. */
+int grt_gas_debug_table(grt_gas *gas, int kind, int index, double *out);
+
 /* One column: level pressure [atm] and temperature [K], mole fractions
  * x_mol[GRT_MAX_MOLS][num_levels] (row = HITRAN id - 1), x_cfc[GRT_MAX_CFCS][num_levels]
  * (row = cfc id), x_cia[GRT_NUM_CIA_SPECIES][num_levels]; writes (overwrites)

@@ -58,4 +58,6 @@ EXTERN int gas_optics_debug_records(GasOptics_t const * const gas_optics, int co
 EXTERN int gas_optics_debug_line_order(GasOptics_t const * const gas_optics,
                                        uint64_t const count, uint64_t * const order);
 EXTERN int gas_optics_class_histogram(GasOptics_t const * const gas_optics, uint64_t out[8]);
+EXTERN int gas_optics_debug_table(GasOptics_t const * const gas_optics, int const kind,
+                                  int const index, double * const out);
 #endif

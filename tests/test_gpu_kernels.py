@@ -74,3 +74,45 @@ def test_binned_sort_paths_agree(built, tmp_path, method):
     a, _ = _tau(tmp_path, 500., 900., 0.1, 20, lines, 43, method, {"GRT_BIN_SORT": "d"})
     b, _ = _tau(tmp_path, 500., 900., 0.1, 20, lines, 43, method, {"GRT_BIN_SORT": "s"})
     assert np.array_equal(a, b)
+
+
+def test_device_table_resampling_matches_the_host_rule(built, tmp_path):
+    """Setup on the device: continuum / CFC / CIA tables are resampled to the
+    spectral grid by a kernel; every table must equal, bit for bit, what the host's
+    interpolate_to_grid restatement (host/parse_csv.c: grt_table_on_grid, checked against the
+    reference in tests/test_host.py) gives for the same CSV: linear inside a source interval,
+    0 at or below the first abscissa and beyond the last."""
+    import numpy as np
+    from grtcode_b200 import api, synth
+    api.load()
+    # grid wider than the CFC table (500-1500.5 cm-1) and finer than any table's spacing
+    w0, wn, dw = 1., 3250., 0.01
+    ds = synth.make_dataset(str(tmp_path), w0, wn, {synth.H2O: 20, synth.O3: 20}, seed=3,
+                            cfcs=("CFC11", "CCl4"), cias=((0, 0), (1, 1)))
+    g = api.spectral_grid(w0, wn, dw)
+    go = api.GasOptics(4, g, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm)
+    go.add_molecule(synth.H2O)
+    go.add_molecule(synth.O3)
+    for c, path in ds.cfc.items():
+        go.add_cfc(c, path)
+    for (a, b), path in ds.cia.items():
+        go.add_cia(a, b, path)
+    import os
+    cases = [(0, 0, os.path.join(ds.h2o_ctm_dir, "296MTCKD25_S.csv"), 2),
+             (1, 0, os.path.join(ds.h2o_ctm_dir, "CKDS.csv"), 4),
+             (2, 0, os.path.join(ds.h2o_ctm_dir, "296MTCKD25_F.csv"), 2),
+             (3, 0, os.path.join(ds.h2o_ctm_dir, "CKDF.csv"), 4),
+             (4, 0, ds.o3_ctm, 2)]
+    cases += [(5, k, path, 2) for k, path in enumerate(ds.cfc.values())]
+    cases += [(6, k, path, 2) for k, path in enumerate(ds.cia.values())]
+    for kind, index, path, cols in cases:
+        got = go.debug_table(kind, index)
+        want = api.table_on_grid_host(path, cols, g)
+        assert got.shape == want.shape
+        assert np.array_equal(got, want), (kind, index, np.abs(got - want).max())
+        assert (got != 0).any()
+    # the CFC table is zero outside 500-1500.5 cm-1 (no extrapolation)
+    cfc = go.debug_table(5, 0)
+    w = w0 + np.arange(int(g.n))*dw
+    assert not cfc[w <= 500.].any() and not cfc[w > 1500.5].any()
+    go.close()
