@@ -45,6 +45,7 @@ int create_gas_optics(GasOptics_t * const gas_optics, int const num_levels,
     gas_optics->num_layers = num_levels - 1;
     gas_optics->grid = *grid;
     gas_optics->device = *device;
+    grt_hitran_use_device(*device);
     TRY(copy_str(gas_optics->hitran_path, hitran_path, DIR_PATH_LEN));
     LOG_INFO("Using HITRAN database file %s.", gas_optics->hitran_path);
     gas_optics->wcutoff = DEFAULT_CUTOFF;

@@ -18,6 +18,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 #include "errors.h"
+#include "grt_sm100.h"
 #include "hitran.h"
 #include "tips.h"
 #include "utilities.h"
@@ -128,7 +129,18 @@ static int parse_record(char const *rec, int *iso, fp_t *vnn, fp_t *snn, fp_t *y
  * all host cores, into a table of every record; parse_hitran_file() then filters that
  * table by molecule and wavenumber range.  The table is keyed by (path, size, mtime); the
  * two most recently used files are kept (one per spectral band). */
-enum { ROW_OK = 0, ROW_BAD_MOLECULE = 1, ROW_BAD_FIELD = 2 };
+enum { ROW_OK = 0, ROW_BAD_MOLECULE = 1, ROW_BAD_FIELD = 2, ROW_HOST = 3 };
+
+/* Where the records are converted: on the device a GasOptics_t was created on
+ * (grt_hitran_use_device, called by create_gas_optics; csrc/hitran_parse.cu), or -- for the
+ * host-only parse_hitran_file() of a process that has created none, and with GRT_PARSE=host --
+ * by the host threads below. */
+static int parse_device = -1;
+
+void grt_hitran_use_device(int const device)
+{
+    parse_device = device;
+}
 
 typedef struct HitranTable
 {
@@ -336,8 +348,29 @@ static int load_table(HitranTable_t *t, char const *filepath, struct stat const 
     {
         FAIL(GRTCODE_NULL_ERR, "out of memory for %llu spectral lines.", (unsigned long long)n);
     }
-    run_parallel(t, parse_rows);
-    run_parallel(t, convert_rows);
+    char const *where = getenv("GRT_PARSE");
+    if (parse_device < 0 || n == 0 || (where != NULL && strcmp(where, "host") == 0))
+    {
+        run_parallel(t, parse_rows);
+        run_parallel(t, convert_rows);
+        return GRTCODE_SUCCESS;
+    }
+    GPU(grt_hitran_convert(parse_device, t->text, size, t->start, n, t->mol, t->iso, t->vnn,
+                           t->snn, t->yair, t->yself, t->en, t->n, t->d, t->status));
+    /* Rows the device did not decide (unusual text, malformed fields): strtod, as above. */
+    uint64_t i;
+    for (i=0; i<n; ++i)
+    {
+        if (t->status[i] == ROW_HOST)
+        {
+            ParseJob_t one;
+            one.t = t;
+            one.first = i;
+            one.last = i + 1;
+            parse_rows(&one);
+            convert_rows(&one);
+        }
+    }
     return GRTCODE_SUCCESS;
 }
 

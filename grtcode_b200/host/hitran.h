@@ -24,5 +24,7 @@ int parse_hitran_file(LineParams_t * const line_params, char const * const filep
 void free_line_params(LineParams_t * const line_params);
 /* Drops the parsed-file tables kept between parse_hitran_file() calls (hitran.c). */
 void grt_hitran_cache_clear(void);
+/* The device that converts the records from now on (-1: the host threads). */
+void grt_hitran_use_device(int const device);
 
 #endif

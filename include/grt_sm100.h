@@ -106,6 +106,23 @@ int grt_gas_add_cia_samples(grt_gas *gas, int species0, int species1, grt_real c
  * num_wpoints doubles. */
 int grt_gas_debug_table(grt_gas *gas, int kind, int index, double *out);
 
+/* Setup on the device: the fixed-width HITRAN records of `text`
+ * (`size` bytes on the host; record k starts at start[k]) converted to numbers by one thread per
+ * record, into host arrays of num_records entries -- the conversions of
+ * gas-optics/src/parse_HITRAN_file.c:266-370 (strtod per field, float rounding of the widths,
+ * E'', n and delta).  status[k]: 0 = converted, 3 = not decided here (unusual text, a malformed
+ * field, a molecule id that is not two characters of digits): the caller converts that row
+ * with strtod itself.  No reference counterpart: the reference parses on the host only. */
+int grt_hitran_convert(int device, char const *text, uint64_t size, uint64_t const *start,
+                       uint64_t num_records, short *mol, int *iso, grt_real *vnn, grt_real *snn,
+                       grt_real *yair, grt_real *yself, grt_real *en, grt_real *n, grt_real *d,
+                       signed char *status);
+
+/* Test hook of the decimal conversion above: `count` fields of `width` (<= 31) characters,
+ * back to back in `text`; out[k] = the double, status[k] = 0 or 3 as above. */
+int grt_decimal_fields(int device, char const *text, int width, uint64_t count, double *out,
+                       signed char *status);
+
 /* One column: level pressure [atm] and temperature [K], mole fractions
  * x_mol[GRT_MAX_MOLS][num_levels] (row = HITRAN id - 1), x_cfc[GRT_MAX_CFCS][num_levels]
  * (row = cfc id), x_cia[GRT_NUM_CIA_SPECIES][num_levels]; writes (overwrites)

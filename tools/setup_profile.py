@@ -18,8 +18,11 @@ for band in (lw, sw):
     grid = api.spectral_grid(band.w0, band.wn, band.dw)
     go = api.GasOptics(len(col.p), grid, ds.hitran, ds.h2o_ctm_dir, ds.o3_ctm, device=0)
     mark()
+    per = []
     for m in W.MOLECULES:
+        t1 = time.perf_counter()
         go.add_molecule(m)
+        per.append(time.perf_counter() - t1)
     mark()
     for c, path in ds.cfc.items():
         go.add_cfc(c, path)
@@ -40,3 +43,24 @@ for band in (lw, sw):
     print(f"{band.name}: create (continua tables) {d[0]:.2f}  add_molecule x7 {d[1]:.2f}  "
           f"cfc+cia tables {d[2]:.2f}  first optical_depth (line upload) {d[3]:.2f}  "
           f"second {d[4]:.2f}  solar {d[5]:.2f}  [s]")
+    print("   add_molecule one by one: " + " ".join(f"{x:.3f}" for x in per))
+
+# the HITRAN conversion alone: parse_hitran_file for one molecule with the table cache dropped,
+# on the device and by the host threads
+import ctypes as C
+L = api.load()
+L.grt_hitran_use_device.argtypes = [C.c_int]
+L.parse_hitran_file.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_double, C.c_double]
+for band in (lw, sw):
+    for where in ("device", "host", "device", "host"):
+        L.grt_hitran_cache_clear()
+        if where == "host":
+            os.environ["GRT_PARSE"] = "host"
+        else:
+            os.environ.pop("GRT_PARSE", None)
+        L.grt_hitran_use_device(0)
+        buf = C.create_string_buffer(256)
+        t1 = time.perf_counter()
+        rc = L.parse_hitran_file(buf, band.dataset.hitran.encode(), 2, band.w0, band.wn)
+        print(f"{band.name}: parse_hitran_file (file read + conversion + one molecule's filter) "
+              f"{where}: {time.perf_counter() - t1:.3f} s  rc {rc}")
