@@ -368,10 +368,31 @@ __device__ __forceinline__ f32x2 abscissa2(wn_t const t2a, wn_t const t2b, wn_t 
     return pack2(abscissa_from(t2a, v, repwid), abscissa_from(t2b, v, repwid));
 }
 
+// a/b for two samples: the exact IEEE quotient in the double build (the reference's float
+// division, bit for bit); in the single build, whose tolerance on tau is 1e-4, the reciprocal
+// unit's 2^-22.
+__device__ __forceinline__ f32x2 rcp2_mufu(f32x2 const q)
+{
+    float qx, qy, rx, ry;
+    unpack2(q, qx, qy);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(qx));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(qy));
+    return pack2(rx, ry);
+}
+
+__device__ __forceinline__ f32x2 div2(f32x2 const a, f32x2 const b)
+{
+#ifdef GRT_SINGLE
+    return mul2(a, rcp2_mufu(b));
+#else
+    return div_exact2(a, b);
+#endif
+}
+
 // Far wing K = YRRTPI/(XQ + YQ) (RFM_voigt.c:168-171) for two samples.
 __device__ __forceinline__ f32x2 far_wing2(f32x2 const xq, f32x2 const yq2, f32x2 const yr2)
 {
-    return div_exact2(yr2, add2(xq, yq2));
+    return div2(yr2, add2(xq, yq2));
 }
 
 // Humlicek region 1 (RFM_voigt.c:172-183) for two samples, per-line constants hoisted.
@@ -379,17 +400,53 @@ __device__ __forceinline__ f32x2 region1_2(f32x2 const xq, f32x2 const y2, f32x2
                                            f32x2 const d0, f32x2 const d2)
 {
     f32x2 const den = add2(d0, mul2_unfused(xq, add2(d2, xq)));
-    f32x2 const D = div_exact2(pack2(kRsqrpi, kRsqrpi), den);
+    f32x2 const D = div2(pack2(kRsqrpi, kRsqrpi), den);
     return mul2(mul2(D, y2), add2(a0, xq));
 }
 
-__device__ __forceinline__ void accumulate2(double &a0, double &a1, double const c, f32x2 const k)
+// The sums a line class adds its samples to.  Double build: the tile's double accumulators,
+// one DFMA per sample.  Single build: packed float partial sums of the staged batch (<= 32
+// lines), flushed into the double accumulators by process_batch -- no FP64 and no conversion
+// per sample in any class.
+#ifdef GRT_SINGLE
+template <int PTS> struct BatchAcc { typedef f32x2 type[PTS/2]; };
+typedef float coef_t;
+__device__ __forceinline__ coef_t rec_coef(RecA const a) { return a.y; }
+#define GRT_ACC_PAIR(acc, j) acc[(j)/2]
+
+__device__ __forceinline__ void add_pair(f32x2 &a, float const c, f32x2 const k)
+{
+    a = fma2(pack2(c, c), k, a);
+}
+
+__device__ __forceinline__ void add_pair_if(f32x2 &a, float const c, float const k0,
+                                            float const k1, bool const p0, bool const p1)
+{
+    // a predicated-off sample may be any bit pattern (abscissae beyond a window end)
+    a = fma2(pack2(c, c), pack2(p0 ? k0 : 0.f, p1 ? k1 : 0.f), a);
+}
+#else
+template <int PTS> struct BatchAcc { typedef double type[PTS]; };
+typedef double coef_t;
+__device__ __forceinline__ coef_t rec_coef(RecA const a) { return a.y; }
+#define GRT_ACC_PAIR(acc, j) acc[j], acc[(j) + 1]
+
+__device__ __forceinline__ void add_pair(double &a0, double &a1, double const c, f32x2 const k)
 {
     float k0, k1;
     unpack2(k, k0, k1);
     a0 = fma(c, widen_positive(k0), a0);
     a1 = fma(c, widen_positive(k1), a1);
 }
+
+__device__ __forceinline__ void add_pair_if(double &a0, double &a1, double const c,
+                                            float const k0, float const k1, bool const p0,
+                                            bool const p1)
+{
+    if (p0) a0 = fma(c, widen_positive(k0), a0);
+    if (p1) a1 = fma(c, widen_positive(k1), a1);
+}
+#endif
 
 #ifndef GRT_SEED_MIX
 #define GRT_SEED_MIX 0
@@ -422,15 +479,6 @@ __device__ __forceinline__ f32x2 rcp2_seeded(f32x2 const q)
     r = fma2(r, e, r);
     e = fma2(nq, r, one);
     return fma2(r, e, r);
-}
-
-__device__ __forceinline__ f32x2 rcp2_mufu(f32x2 const q)
-{
-    float qx, qy, rx, ry;
-    unpack2(q, qx, qy);
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(qx));
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(qy));
-    return pack2(rx, ry);
 }
 
 #ifndef GRT_SP_SEED_PAIRS
@@ -479,7 +527,7 @@ __device__ __forceinline__ void line_fast(RecA const A, float4 const B, TileCtx 
         // GRT_SEED_MIX of every four pairs take the XU-free division (voigt.cuh)
         f32x2 const k = ((j/2) % 4 < GRT_SEED_MIX) ? div_exact2_seeded(yr2, add2(xq, yq2))
                                                    : far_wing2(xq, yq2, yr2);
-        accumulate2(acc[j], acc[j+1], A.y, k);
+        add_pair(acc[j], acc[j+1], A.y, k);
     }
 }
 
@@ -490,12 +538,13 @@ __device__ __forceinline__ void line_fast(RecA const A, float4 const B, TileCtx 
 template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_r1(RecA const A, float4 const B, float4 const C,
                                         float4 const D, TileCtx const &t,
-                                        GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+                                        GridCache<PTS, TBL> &gc,
+                                        typename BatchAcc<PTS>::type &acc)
 {
     // C = hw0, y, xlim0, xlim1;  D = a0, d0, d2, -
     LineGrid<PTS, TBL, LN> const grid(gc, t, __float_as_int(B.w));
     wn_t const repwid = rec_repwid(B);
-    double const cA = rec_c(A);
+    coef_t const cA = rec_coef(A);
     f32x2 const y2 = pack2(C.y, C.y);
     f32x2 const a0 = pack2(D.x, D.x);
     f32x2 const d0 = pack2(D.y, D.y);
@@ -504,7 +553,7 @@ __device__ __forceinline__ void line_r1(RecA const A, float4 const B, float4 con
     for (int j=0; j<PTS; j+=2)
     {
         f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), rec_v(A), repwid);
-        accumulate2(acc[j], acc[j+1], cA, region1_2(mul2_unfused(xi, xi), y2, a0, d0, d2));
+        add_pair(GRT_ACC_PAIR(acc, j), cA, region1_2(mul2_unfused(xi, xi), y2, a0, d0, d2));
     }
 }
 
@@ -512,15 +561,30 @@ __device__ __forceinline__ void line_r1(RecA const A, float4 const B, float4 con
 template <int PTS, bool TBL, int LN, bool FULL>
 __device__ __forceinline__ void line_lorentz(RecA const A, float4 const B,
                                              TileCtx const &t, GridCache<PTS, TBL> &gc,
-                                             double (&acc)[PTS])
+                                             typename BatchAcc<PTS>::type &acc)
 {
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     wn_t const repwid = rec_repwid(B);
-    double const cA = rec_c(A);
     int const f0 = t.warp_base + t.sub;
+#ifdef GRT_SINGLE
+    float const cA = rec_coef(A);
+    f32x2 const yq2 = pack2(B.y, B.y);
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        int const fa = f0 + LN*j;
+        int const fb = fa + LN;
+        f32x2 const xi = abscissa2(grid.t2(j), grid.t2(j + 1), rec_v(A), repwid);
+        float k0, k1;
+        unpack2(rcp2_mufu(fma2(xi, xi, yq2)), k0, k1);
+        add_pair_if(acc[j/2], cA, k0, k1, FULL || ((fa >= s) && (fa <= e)),
+                    FULL || ((fb >= s) && (fb <= e)));
+    }
+#else
+    double const cA = rec_c(A);
 #pragma unroll
     for (int j=0; j<PTS; ++j)
     {
@@ -529,6 +593,7 @@ __device__ __forceinline__ void line_lorentz(RecA const A, float4 const B,
         double const k = fast_rcp_of_float(xi*xi + B.y);
         if (FULL || ((f >= s) && (f <= e))) acc[j] = fma(cA, k, acc[j]);
     }
+#endif
 }
 
 
@@ -536,14 +601,15 @@ __device__ __forceinline__ void line_lorentz(RecA const A, float4 const B,
 // the far-wing arithmetic with a per-point window predicate.
 template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_far_edge(RecA const A, float4 const B, TileCtx const &t,
-                                              GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+                                              GridCache<PTS, TBL> &gc,
+                                              typename BatchAcc<PTS>::type &acc)
 {
     int const fc = __float_as_int(B.w);
     int const s = max(fc - t.fsteps, 0);
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     wn_t const repwid = rec_repwid(B);
-    double const cA = rec_c(A);
+    coef_t const cA = rec_coef(A);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
     int const f0 = t.warp_base + t.sub;
@@ -559,8 +625,8 @@ __device__ __forceinline__ void line_far_edge(RecA const A, float4 const B, Tile
         unpack2(k, k0, k1);
         int const fa = f0 + LN*j;
         int const fb = fa + LN;
-        if ((fa >= s) && (fa <= e)) acc[j] = fma(cA, widen_positive(k0), acc[j]);
-        if ((fb >= s) && (fb <= e)) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
+        add_pair_if(GRT_ACC_PAIR(acc, j), cA, k0, k1, (fa >= s) && (fa <= e),
+                    (fb >= s) && (fb <= e));
     }
 }
 
@@ -573,7 +639,8 @@ __device__ __forceinline__ void line_far_edge(RecA const A, float4 const B, Tile
 template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_near_single(RecA const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
-                                          GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+                                          GridCache<PTS, TBL> &gc,
+                                          typename BatchAcc<PTS>::type &acc)
 {
     // C = hw0, y, xlim0, xlim1;  D = a0, d0, d2, hw1_hw0in
     int const fc = __float_as_int(B.w);
@@ -582,7 +649,7 @@ __device__ __forceinline__ void line_near_single(RecA const A, float4 const B, f
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     wn_t const repwid = rec_repwid(B);
-    double const cA = rec_c(A);
+    coef_t const cA = rec_coef(A);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
     int const f0 = t.warp_base + t.sub;
@@ -623,8 +690,7 @@ __device__ __forceinline__ void line_near_single(RecA const A, float4 const B, f
             ina = ina && (far0 || (ax0 >= C.w));
             inb = inb && (far1 || (ax1 >= C.w));
         }
-        if (ina) acc[j] = fma(cA, widen_positive(k0), acc[j]);
-        if (inb) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
+        add_pair_if(GRT_ACC_PAIR(acc, j), cA, k0, k1, ina, inb);
     }
 }
 
@@ -635,7 +701,8 @@ __device__ __forceinline__ void line_near_single(RecA const A, float4 const B, f
 template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_near_pairs(RecA const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
-                                          GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+                                          GridCache<PTS, TBL> &gc,
+                                          typename BatchAcc<PTS>::type &acc)
 {
     int const fc = __float_as_int(B.w);
     int const hw0 = __float_as_int(C.x);
@@ -644,7 +711,7 @@ __device__ __forceinline__ void line_near_pairs(RecA const A, float4 const B, fl
     int const e = min(fc + t.fsteps, t.nw - 1);
     LineGrid<PTS, TBL, LN> const grid(gc, t, fc);
     wn_t const repwid = rec_repwid(B);
-    double const cA = rec_c(A);
+    coef_t const cA = rec_coef(A);
     f32x2 const yq2 = pack2(B.y, B.y);
     f32x2 const yr2 = pack2(B.z, B.z);
     f32x2 const y2 = pack2(C.y, C.y);
@@ -675,35 +742,28 @@ __device__ __forceinline__ void line_near_pairs(RecA const A, float4 const B, fl
         {
             float k0, k1;
             unpack2(far_wing2(xq[j/2], yq2, yr2), k0, k1);
-            if (ina) acc[j] = fma(cA, widen_positive(k0), acc[j]);
-            if (inb) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
+            add_pair_if(GRT_ACC_PAIR(acc, j), cA, k0, k1, ina, inb);
         }
         else if (dhi < hw0in)
         {
             float k0, k1;
             unpack2(region1_2(xq[j/2], y2, a0, d0, d2), k0, k1);
-            if (ina && (fabsf(x0) >= C.w)) acc[j] = fma(cA, widen_positive(k0), acc[j]);
-            if (inb && (fabsf(x1) >= C.w)) acc[j+1] = fma(cA, widen_positive(k1), acc[j+1]);
+            add_pair_if(GRT_ACC_PAIR(acc, j), cA, k0, k1, ina && (fabsf(x0) >= C.w),
+                        inb && (fabsf(x1) >= C.w));
         }
         else
         {
             float kf0, kf1, kr0, kr1;
             unpack2(far_wing2(xq[j/2], yq2, yr2), kf0, kf1);
             unpack2(region1_2(xq[j/2], y2, a0, d0, d2), kr0, kr1);
-            {
-                float const ax = fabsf(x0);
-                bool const isfar = ax >= C.z;
-                bool const isr1 = !isfar && (ax >= C.w);
-                float const kf = isr1 ? kr0 : kf0;
-                if (ina && (isfar || isr1)) acc[j] = fma(cA, widen_positive(kf), acc[j]);
-            }
-            {
-                float const ax = fabsf(x1);
-                bool const isfar = ax >= C.z;
-                bool const isr1 = !isfar && (ax >= C.w);
-                float const kf = isr1 ? kr1 : kf1;
-                if (inb && (isfar || isr1)) acc[j+1] = fma(cA, widen_positive(kf), acc[j+1]);
-            }
+            float const ax0 = fabsf(x0);
+            bool const isfar0 = ax0 >= C.z;
+            bool const isr10 = !isfar0 && (ax0 >= C.w);
+            float const ax1 = fabsf(x1);
+            bool const isfar1 = ax1 >= C.z;
+            bool const isr11 = !isfar1 && (ax1 >= C.w);
+            add_pair_if(GRT_ACC_PAIR(acc, j), cA, isr10 ? kr0 : kf0, isr11 ? kr1 : kf1,
+                        ina && (isfar0 || isr10), inb && (isfar1 || isr11));
         }
     }
 }
@@ -711,7 +771,8 @@ __device__ __forceinline__ void line_near_pairs(RecA const A, float4 const B, fl
 template <int PTS, bool TBL, int LN>
 __device__ __forceinline__ void line_near(RecA const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
-                                          GridCache<PTS, TBL> &gc, double (&acc)[PTS])
+                                          GridCache<PTS, TBL> &gc,
+                                          typename BatchAcc<PTS>::type &acc)
 {
     if (PTS <= 2) line_near_single<PTS, TBL, LN>(A, B, C, D, t, gc, acc);
     else line_near_pairs<PTS, TBL, LN>(A, B, C, D, t, gc, acc);
@@ -837,7 +898,7 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
     m |= medge;
 #define GRT_LINE_BODY(A, B, b_)                                                      \
     do {                                                                             \
-        if ((medge >> (b_)) & 1u) line_far_edge<PTS, TBL, LN>(A, B, t, gc, acc);     \
+        if ((medge >> (b_)) & 1u) line_far_edge<PTS, TBL, LN>(A, B, t, gc, GRT_FAST_ACC);     \
         else line_fast<PTS, TBL, LN>(A, B, t, gc, GRT_FAST_ACC);                     \
     } while (0)
 #else
@@ -850,16 +911,17 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
     // the stage address is kept opaque so that it stays in a register
     uint32_t sa = smem_u32(stage);
     asm volatile("" : "+r"(sa));
-    if (m)
-    {
 #ifdef GRT_SINGLE
-        f32x2 facc[PTS/2];
+    // float partial sums of this batch, every class (see BatchAcc)
+    f32x2 facc[PTS/2];
 #pragma unroll
-        for (int j=0; j<PTS/2; ++j) facc[j] = 0ull;
+    for (int j=0; j<PTS/2; ++j) facc[j] = 0ull;
 #define GRT_FAST_ACC facc
 #else
 #define GRT_FAST_ACC acc
 #endif
+    if (m)
+    {
         int b = __ffs(m) - 1;
         m &= m - 1;
         // two records in flight, in alternating register sets (no copies between them)
@@ -886,52 +948,52 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
             if (!more) break;
         }
 #undef GRT_LINE_BODY
-#undef GRT_FAST_ACC
-#ifdef GRT_SINGLE
-        // the batch's float partial sums (<= 32 lines) join the double accumulators
-#pragma unroll
-        for (int j=0; j<PTS; j+=2)
-        {
-            float f0, f1;
-            unpack2(facc[j/2], f0, f1);
-            acc[j] += (double)f0;
-            acc[j+1] += (double)f1;
-        }
-#endif
     }
     GRT_TM_END(kTmFast, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsR1) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_r1<PTS, TBL, LN>(r.A, r.B, r.C, r.D, t, gc, acc); });
+    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_r1<PTS, TBL, LN>(r.A, r.B, r.C, r.D, t, gc, GRT_FAST_ACC); });
     GRT_TM_END(kTmR1, tm_n);
 #if !GRT_MERGE_EDGE
     m = __ballot_sync(0xffffffffu, cls == kClsFarEdge) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_far_edge<PTS, TBL, LN>(r.A, r.B, t, gc, acc); });
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_far_edge<PTS, TBL, LN>(r.A, r.B, t, gc, GRT_FAST_ACC); });
     GRT_TM_END(kTmFarEdge, tm_n);
 #endif
     m = __ballot_sync(0xffffffffu, cls == kClsNear) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_near<PTS, TBL, LN>(r.A, r.B, r.C, r.D, t, gc, acc); });
+    walk_class<4>(m, sa, [&](RecVec<4> const &r) { line_near<PTS, TBL, LN>(r.A, r.B, r.C, r.D, t, gc, GRT_FAST_ACC); });
     GRT_TM_END(kTmNear, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsLorentzFull) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, LN, true>(r.A, r.B, t, gc, acc); });
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, LN, true>(r.A, r.B, t, gc, GRT_FAST_ACC); });
     GRT_TM_END(kTmLorFull, tm_n);
     m = __ballot_sync(0xffffffffu, cls == kClsLorentzEdge) & t.gmask;
 #if GRT_DBG_TIMERS
     tm_n = __popc(m);
 #endif
-    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, LN, false>(r.A, r.B, t, gc, acc); });
+    walk_class<2>(m, sa, [&](RecVec<2> const &r) { line_lorentz<PTS, TBL, LN, false>(r.A, r.B, t, gc, GRT_FAST_ACC); });
     GRT_TM_END(kTmLorEdge, tm_n);
+#ifdef GRT_SINGLE
+    // the batch's float partial sums (<= 32 lines) join the double accumulators
+#pragma unroll
+    for (int j=0; j<PTS; j+=2)
+    {
+        float f0, f1;
+        unpack2(facc[j/2], f0, f1);
+        acc[j] += (double)f0;
+        acc[j+1] += (double)f1;
+    }
+#endif
+#undef GRT_FAST_ACC
 }
 
 
