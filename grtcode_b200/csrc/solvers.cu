@@ -565,6 +565,240 @@ sw_kernel(int const num_levels, double const w0, double const dw, uint64_t const
 }
 
 
+// ---- shortwave, staged through L2 ----------------------------------------------------
+// sw_kernel above keeps seven per-thread arrays of MAXL values in local memory: with enough
+// threads resident to hide its latency they spill to DRAM (13x the algorithmic traffic).  The
+// expensive part of a layer -- the Eddington reflectivities and transmittances, six double
+// exp and a sqrt -- does not depend on the other layers; only the adding recursions are
+// sequential.  So a block of four warps takes 32 wavenumbers at a time:
+//   phase A  all 128 threads evaluate the (wavenumber, layer) pairs independently (warp = one
+//            layer row of 32 wavenumbers: every access 256 contiguous bytes) and park the five
+//            layer values in a block-private scratch slab in global memory -- 69 KB per block
+//            at 54 layers, 61 MB for 6 blocks on each SM: it lives in L2 and is overwritten in
+//            place stage after stage, so it never has to reach DRAM;
+//   phase B  warp 0 runs the two recursions of shortwave.c:242-330 for its 32 wavenumbers,
+//            Rdd / Rfd in shared memory, while the other blocks of the SM are in phase A.
+// Same expressions on the same operands as sw_kernel, hence the same bits.
+constexpr int kStagedThreads = 128;
+constexpr int kStagedBlocksPerSM = 6;
+constexpr int kStageWidth = 32;
+
+__host__ __device__ constexpr size_t sw_stage_doubles(int const num_layers)
+{
+    return (size_t)5*(size_t)num_layers*kStageWidth;
+}
+
+template <bool FUSED>
+__global__ void __launch_bounds__(kStagedThreads, kStagedBlocksPerSM)
+sw_staged_kernel(int const num_levels, double const w0, double const dw, uint64_t const nw,
+                 LayerDensity const dens, real_t const *omega_in, real_t const *g_in,
+                 real_t const *tau_in, double const mu_dir, double const mu_dif,
+                 real_t const *alb_dir, real_t const *alb_dif, double const tsi,
+                 real_t const *solar, typename FluxOut<FUSED>::type *flux_up,
+                 typename FluxOut<FUSED>::type *flux_down, uint64_t const first,
+                 uint64_t const last, double *scratch)
+{
+    typedef typename FluxOut<FUSED>::type flux_t;
+    extern __shared__ double staged_smem[];
+    int const L = num_levels - 1;
+    // shared: Rdd[L+1][32], Rfd[L+1][32], then (FUSED) the block's broadband sums [2][L+1]
+    double *s_rdd = staged_smem;
+    double *s_rfd = staged_smem + (size_t)num_levels*kStageWidth;
+    double *s_sum = staged_smem + (size_t)2*num_levels*kStageWidth;
+    int const lane = threadIdx.x & 31;
+    int const warp = threadIdx.x >> 5;
+    if (FUSED)
+    {
+        for (int t=threadIdx.x; t<2*num_levels; t+=kStagedThreads) s_sum[t] = 0.;
+    }
+    fp const mu_d = mu_dir;                          // fp_t arguments of sw_flux
+    fp const mu_f = mu_dif;
+    fp const tsi_fp = tsi;
+    double *slab = scratch + (size_t)blockIdx.x*sw_stage_doubles(L);
+    size_t const plane = (size_t)L*kStageWidth;      // one of the five layer values, [L][32]
+    uint64_t const stages = (nw + kStageWidth - 1)/kStageWidth;
+    for (uint64_t stage=blockIdx.x; stage<stages; stage+=gridDim.x)
+    {
+        uint64_t const i = stage*kStageWidth + (uint64_t)lane;
+        bool const live = i < nw;
+        uint64_t const ii = live ? i : nw - 1;
+        // ---- phase A: layer values (shortwave.c:86-236), one layer row per warp and turn
+        {
+            double const w = w0 + (double)ii*dw;
+            for (int j=warp; j<L; j+=kStagedThreads/32)
+            {
+                size_t const o = (size_t)j*nw + ii;
+                fp omega, g, tau;
+                if (FUSED)
+                {
+                    // add_optics of [gas, rayleigh] (optics.c:134-146)
+                    fp const tg = tau_in[o];
+                    fp const tr = rayleigh_tau(w, (fp)dens.n[j]);
+                    tau = tg + tr;
+                    g = 0./tr;
+                    omega = tr/tau;
+                }
+                else
+                {
+                    omega = omega_in[o];
+                    g = g_in[o];
+                    tau = tau_in[o];
+                }
+                // delta-Eddington scaling (shortwave.c:86-89)
+                fp const gs = g/(g + 1.);
+                fp const f = g*g;
+                fp const os = (1. - f)*omega/(1. - omega*f);
+                fp const ts = tau*(1. - omega*f);
+                fp r_dir, t_dir, t_pure, r_dif, t_dif;
+                eddington_pair(os, ts, mu_d, mu_f, gs, &r_dir, &t_dir, &t_pure, &r_dif, &t_dif);
+                double *dst = slab + (size_t)j*kStageWidth + lane;
+                __stcg(dst, (double)r_dir);
+                __stcg(dst + plane, (double)t_dir);
+                __stcg(dst + 2*plane, (double)t_pure);
+                __stcg(dst + 3*plane, (double)r_dif);
+                __stcg(dst + 4*plane, (double)t_dif);
+            }
+        }
+        __syncthreads();
+        // ---- phase B: adding from the surface up (shortwave.c:242-260), then the beams
+        // from the top down (shortwave.c:262-330, 339-405)
+        if (warp == 0)
+        {
+            double const *src = slab + lane;
+            fp rdd_below = alb_dir[ii];
+            fp rfd_below = alb_dif[ii];
+            s_rdd[(size_t)L*kStageWidth + lane] = rdd_below;
+            s_rfd[(size_t)L*kStageWidth + lane] = rfd_below;
+            {
+                size_t o = (size_t)(L - 1)*kStageWidth;
+                fp r_dir = __ldcg(src + o);
+                fp t_dir = __ldcg(src + o + plane);
+                fp t_pure = __ldcg(src + o + 2*plane);
+                fp r_dif = __ldcg(src + o + 3*plane);
+                fp t_dif = __ldcg(src + o + 4*plane);
+                for (int j=L-1; j>=0; --j)
+                {
+                    // the next layer's values are in flight while this one is added
+                    fp n_r_dir = 0., n_t_dir = 0., n_t_pure = 0., n_r_dif = 0., n_t_dif = 0.;
+                    if (j > 0)
+                    {
+                        size_t const on = (size_t)(j - 1)*kStageWidth;
+                        n_r_dir = __ldcg(src + on);
+                        n_t_dir = __ldcg(src + on + plane);
+                        n_t_pure = __ldcg(src + on + 2*plane);
+                        n_r_dif = __ldcg(src + on + 3*plane);
+                        n_t_dif = __ldcg(src + on + 4*plane);
+                    }
+                    fp const A = t_pure;
+                    fp const B = 1./(1. - r_dif*rfd_below);
+                    fp const rdd = r_dir + (A*rdd_below + (t_dir - A)*rfd_below)*t_dif*B;
+                    fp const rfd = r_dif + t_dif*t_dif*rfd_below*B;
+                    s_rdd[(size_t)j*kStageWidth + lane] = rdd;
+                    s_rfd[(size_t)j*kStageWidth + lane] = rfd;
+                    rdd_below = rdd;
+                    rfd_below = rfd;
+                    r_dir = n_r_dir; t_dir = n_t_dir; t_pure = n_t_pure; r_dif = n_r_dif;
+                    t_dif = n_t_dif;
+                }
+            }
+            fp const scale = solar[ii]*mu_d;         // flux *= solar_flux*mu_dir (shortwave.c:402)
+            double weight = 0.;
+            if (FUSED)
+            {
+                weight = (live && ii >= first && ii <= last)
+                             ? ((ii == first || ii == last) ? 0.5*dw : dw) : 0.;
+                if (first == last) weight = 0.;
+            }
+            auto emit = [&](int const level, fp const up, fp const down)
+            {
+                if (FUSED)
+                {
+                    double u = (double)up*weight;
+                    double d = (double)down*weight;
+                    for (int o=16; o>0; o>>=1)
+                    {
+                        u += __shfl_down_sync(0xffffffffu, u, o);
+                        d += __shfl_down_sync(0xffffffffu, d, o);
+                    }
+                    if (lane == 0)
+                    {
+                        s_sum[level] += u;
+                        s_sum[num_levels + level] += d;
+                    }
+                }
+                else if (live)
+                {
+                    flux_up[(size_t)level*nw + ii] = (flux_t)up;
+                    flux_down[(size_t)level*nw + ii] = (flux_t)down;
+                }
+            };
+            fp dir_beam = 1.;
+            fp dif_beam = 0.;
+            {
+                fp const r0 = dir_beam*(fp)s_rdd[lane];
+                fp const t0 = dir_beam;
+                emit(0, tsi_fp*(r0*scale), tsi_fp*(t0*scale));      // shortwave.c:448
+            }
+            fp rfu_above = 0.;          // Rfu[j-2]
+            fp r_dir = __ldcg(src);
+            fp t_dir = __ldcg(src + plane);
+            fp t_pure = __ldcg(src + 2*plane);
+            fp r_dif = __ldcg(src + 3*plane);
+            fp t_dif = __ldcg(src + 4*plane);
+            fp rfu = r_dif;             // Rfu[j-1] = R_dif[0]
+            for (int j=1; j<num_levels; ++j)
+            {
+                // layer j-1's values are in registers; layer j's are fetched meanwhile
+                fp n_r_dir = 0., n_t_dir = 0., n_t_pure = 0., n_r_dif = 0., n_t_dif = 0.;
+                if (j < L)
+                {
+                    size_t const on = (size_t)j*kStageWidth;
+                    n_r_dir = __ldcg(src + on);
+                    n_t_dir = __ldcg(src + on + plane);
+                    n_t_pure = __ldcg(src + on + 2*plane);
+                    n_r_dif = __ldcg(src + on + 3*plane);
+                    n_t_dif = __ldcg(src + on + 4*plane);
+                }
+                if (j > 1)
+                {
+                    // Rfu[j-1] from Rfu[j-2]
+                    fp const Bu = 1./(1. - r_dif*rfu);
+                    fp const next = r_dif + t_dif*t_dif*rfu*Bu;
+                    rfu_above = rfu;
+                    rfu = next;
+                    fp const C = 1./(1. - r_dif*rfu_above);
+                    dif_beam = (dir_beam*r_dir*rfu_above + dif_beam)*t_dif*C +
+                               dir_beam*(t_dir - t_pure);
+                }
+                else
+                {
+                    dif_beam = dir_beam*(t_dir - t_pure);
+                }
+                dir_beam *= t_pure;
+                fp const rdd_j = s_rdd[(size_t)j*kStageWidth + lane];
+                fp const rfd_j = s_rfd[(size_t)j*kStageWidth + lane];
+                fp const B = 1./(1. - rfd_j*rfu);
+                fp const R = (dir_beam*rdd_j + dif_beam*rfd_j)*B;
+                fp const T = dir_beam*(1. + rdd_j*rfu*B) + dif_beam*B;
+                emit(j, tsi_fp*(R*scale), tsi_fp*(T*scale));
+                r_dir = n_r_dir; t_dir = n_t_dir; t_pure = n_t_pure; r_dif = n_r_dif;
+                t_dif = n_t_dif;
+            }
+        }
+        __syncthreads();
+    }
+    if (FUSED)
+    {
+        for (int t=threadIdx.x; t<2*num_levels; t+=kStagedThreads)
+        {
+            int const dir = t/num_levels;
+            int const level = t - dir*num_levels;
+            atomicAdd(dir ? &((double *)flux_down)[level] : &((double *)flux_up)[level], s_sum[t]);
+        }
+    }
+}
+
+
 // ---- broadband integration (driver.c:302-319) ----------------------------------------
 __global__ void __launch_bounds__(256)
 integrate_kernel(uint64_t const nw, double const dw, real_t const *flux, double *out)
@@ -696,14 +930,58 @@ static int fetch_levels(cudaStream_t st, double const *buf, int num_levels, real
 
 using namespace grt;
 
+// Per-device scratch slabs of sw_staged_kernel (grow-only).
+static double *g_sw_scratch[64];
+static size_t g_sw_scratch_bytes[64];
+
+static int sw_scratch(int device, size_t bytes, double **ptr)
+{
+    if (device < 0 || device >= 64) return fail("device id %d out of range", device);
+    if (bytes > g_sw_scratch_bytes[device])
+    {
+        if (g_sw_scratch[device] != nullptr) GRT_CUDA(cudaFree(g_sw_scratch[device]));
+        g_sw_scratch[device] = nullptr;
+        g_sw_scratch_bytes[device] = 0;
+        GRT_CUDA(cudaMalloc(&g_sw_scratch[device], bytes));
+        g_sw_scratch_bytes[device] = bytes;
+    }
+    *ptr = g_sw_scratch[device];
+    return 0;
+}
+
 template <bool FUSED>
-static int launch_sw(cudaStream_t st, int num_levels, double w0, double dw, uint64_t nw,
-                     LayerDensity const &dens, real_t const *omega, real_t const *g,
+static int launch_sw(int device, cudaStream_t st, int num_levels, double w0, double dw,
+                     uint64_t nw, LayerDensity const &dens, real_t const *omega, real_t const *g,
                      real_t const *tau, double mu_dir, double mu_dif, real_t const *alb_dir,
                      real_t const *alb_dif, double tsi, real_t const *solar,
                      typename FluxOut<FUSED>::type *up, typename FluxOut<FUSED>::type *down,
                      uint64_t first, uint64_t last)
 {
+    char const *which = getenv("GRT_SW_KERNEL");      // measurement knob: "thread" = sw_kernel
+    if (which == nullptr || strcmp(which, "thread") != 0)
+    {
+        static bool configured[64][2];
+        int const L = num_levels - 1;
+        size_t const smem = sizeof(double)*((size_t)2*num_levels*kStageWidth + 2*(size_t)num_levels);
+        if (smem > 48*1024 && !configured[device][FUSED ? 1 : 0])
+        {
+            GRT_CUDA(cudaFuncSetAttribute(sw_staged_kernel<FUSED>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)(sizeof(double)*((size_t)2*(GRT_MAX_LAYERS + 1)*kStageWidth +
+                                                                2*(size_t)(GRT_MAX_LAYERS + 1)))));
+            configured[device][FUSED ? 1 : 0] = true;
+        }
+        uint64_t const stages = (nw + kStageWidth - 1)/kStageWidth;
+        uint64_t const resident = (uint64_t)kStagedBlocksPerSM*(uint64_t)sm_count(device);
+        unsigned const blocks = (unsigned)(stages < resident ? stages : resident);
+        double *scratch = nullptr;
+        GRT_TRY(sw_scratch(device, sizeof(double)*sw_stage_doubles(L)*blocks, &scratch));
+        sw_staged_kernel<FUSED><<<blocks, kStagedThreads, smem, st>>>(
+            num_levels, w0, dw, nw, dens, omega, g, tau, mu_dir, mu_dif, alb_dir, alb_dif, tsi,
+            solar, up, down, first, last, scratch);
+        GRT_CUDA(cudaGetLastError());
+        return 0;
+    }
     unsigned const blocks = (unsigned)((nw + kSolverThreads - 1)/kSolverThreads);
     // Measurement knob: resident blocks per SM, enforced with idle dynamic shared memory (the
     // per-thread layer arrays of the resident threads are what has to fit in L2).
@@ -807,7 +1085,7 @@ int grt_sw_fluxes(int device, int num_levels, uint64_t nw, real_t const *omega_d
     cudaStream_t st;
     GRT_TRY(stream_of(device, &st));
     LayerDensity dens{};
-    return launch_sw<false>(st, num_levels, 0., 0., nw, dens, omega_dev, g_dev, tau_dev, mu_dir,
+    return launch_sw<false>(device, st, num_levels, 0., 0., nw, dens, omega_dev, g_dev, tau_dev, mu_dir,
                             mu_dif, alb_dir_dev, alb_dif_dev, tsi, solar_dev, flux_up_dev,
                             flux_down_dev, 0, nw - 1);
 }
@@ -899,7 +1177,7 @@ int grt_sw_column(int device, int num_levels, double w0, double dw, uint64_t nw,
     double *buf;
     GRT_TRY(out_buffer(device, &buf));
     GRT_CUDA(cudaMemsetAsync(buf, 0, sizeof(double)*2*num_levels, st));
-    GRT_TRY(launch_sw<true>(st, num_levels, w0, dw, nw, dens, nullptr, nullptr, tau_gas_dev,
+    GRT_TRY(launch_sw<true>(device, st, num_levels, w0, dw, nw, dens, nullptr, nullptr, tau_gas_dev,
                             mu_dir, mu_dif, alb_dir_dev, alb_dif_dev, tsi, solar_dev, buf,
                             buf + num_levels, first, last));
     return fetch_levels(st, buf, num_levels, up, down);
