@@ -398,10 +398,11 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
                  PrepMeta const meta, double const w0, double const wres, uint64_t const nw,
                  int const fsteps, LineRec *recs, PrepStats *stats, double *vkey,
                  unsigned *vidx, TieList *ties, unsigned long long *tie_overflow,
-                 unsigned const tie_capacity)
+                 unsigned const tie_capacity, int *hmax)
 {
     uint64_t const j = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
     int const i = blockIdx.y;
+    int my_h = -1;                       // core half-width of this record (core_gather_kernel)
     unsigned long long my_samples = 0;
     unsigned int my_rec = 0;
     unsigned int my_lor = 0;
@@ -446,6 +447,10 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
         my_lor = cnt.lor;
         size_t const gi = (size_t)i*lines.num_lines + j;
         recs[gi] = r;
+        if (r.fc != kSkip && r.hw0 != kHwLorentz && (r.hw0 == kHwCoreOnly || r.xlim1 > 0.f))
+        {
+            my_h = core_half_width(r.repwid, r.xlim1, r.hw0 == kHwCoreOnly, wres, fsteps);
+        }
         if (tie && ties != nullptr && r.fc != kSkip)
         {
             unsigned const k = atomicAdd(&ties->count, 1u);
@@ -458,6 +463,11 @@ line_prep_kernel(LineView const lines, int const num_layers, LayerView const lay
             vkey[gi] = (double)r.v;
             vidx[gi] = (unsigned)gi;
         }
+    }
+    if (hmax != nullptr)
+    {
+        my_h = __reduce_max_sync(0xffffffffu, my_h);
+        if ((threadIdx.x & 31) == 0 && my_h >= 0) atomicMax(&hmax[i], my_h);
     }
     // Block-level statistics (bench bookkeeping only).
     __shared__ unsigned long long sh[4];
@@ -577,6 +587,9 @@ struct grt_gas
     PrepStats *d_stats = nullptr;
     int *d_tile_order = nullptr;         // tiles by line count, heaviest first
     unsigned int *d_work_counter = nullptr;
+    int *d_hmax = nullptr;               // [layers]: largest core half-width (core gather)
+    int *d_first_at = nullptr;           // core gather: first record at or after every 64th point
+    int num_granules = 0;
     int num_tiles = 0;
     unsigned *d_tile_first = nullptr;    // (inside the d_tile_order allocation)
     unsigned *d_tile_last = nullptr;
@@ -735,6 +748,26 @@ static int finalize_lines(grt_gas *g, int const method)
     {
         GRT_CUDA(cudaMemcpyAsync(g->d_tips, g->h_tips.data(), sizeof(double)*g->h_tips.size(),
                                  cudaMemcpyHostToDevice, g->stream));
+    }
+    if (g->d_first_at) { GRT_CUDA(cudaFree(g->d_first_at)); g->d_first_at = nullptr; }
+    if (method == 2)
+    {
+        // core_gather_kernel: first record at or after every 64th grid point (one point of
+        // slack; the kernel widens the range by the core half-width and the pressure shift)
+        int const granules = (int)((g->nw + kCoreGranule - 1)/kCoreGranule);
+        std::vector<int> first_at((size_t)granules + 1);
+        for (int k=0; k<granules; ++k)
+        {
+            double const edge = g->w0 + ((double)k*kCoreGranule - 1.)*g->dw;
+            first_at[k] = (int)(std::lower_bound(packed.begin(), packed.begin() + n, edge) -
+                                packed.begin());
+        }
+        first_at[granules] = (int)n;
+        GRT_CUDA(cudaMalloc(&g->d_first_at, sizeof(int)*first_at.size()));
+        GRT_CUDA(cudaMemcpyAsync(g->d_first_at, first_at.data(), sizeof(int)*first_at.size(),
+                                 cudaMemcpyHostToDevice, g->stream));
+        GRT_CUDA(cudaStreamSynchronize(g->stream));
+        g->num_granules = granules;
     }
     if (g->d_core_order) { GRT_CUDA(cudaFree(g->d_core_order)); g->d_core_order = nullptr; }
     if (method == 2 && n > 0)
@@ -1201,6 +1234,7 @@ int grt_gas_create(grt_gas **gas, int device, int num_levels, double w0, double 
     GRT_CUDA(cudaMalloc(&g->d_inputs, sizeof(double)*input_doubles));
     GRT_CUDA(cudaMalloc(&g->d_stats, sizeof(PrepStats)));
     GRT_CUDA(cudaMalloc(&g->d_work_counter, sizeof(unsigned int)));
+    GRT_CUDA(cudaMalloc(&g->d_hmax, sizeof(int)*GRT_MAX_LAYERS));
     GRT_CUDA(cudaMalloc(&g->d_ties, sizeof(TieList)));
     GRT_CUDA(cudaMalloc(&g->d_tie_overflow, sizeof(unsigned long long)*kTieCapacity));
     GRT_CUDA(cudaMalloc(&g->d_patch, sizeof(RecordPatch)*(kTieInline + kTieCapacity)));
@@ -1227,6 +1261,8 @@ int grt_gas_destroy(grt_gas *g)
     cudaFree(g->d_stats);
     cudaFree(g->d_tile_order);
     cudaFree(g->d_work_counter);
+    cudaFree(g->d_hmax);
+    cudaFree(g->d_first_at);
     cudaFree(g->d_ties); cudaFree(g->d_tie_overflow); cudaFree(g->d_patch);
     cudaFree(g->d_class_counts);
     cudaFreeHost(g->h_block); cudaFreeHost(g->h_patch); cudaFreeHost(g->h_tie_overflow);
@@ -1484,6 +1520,7 @@ int grt_gas_optical_depth(grt_gas *g, real_t const *p_atm_in, real_t const *t_in
     int const fsteps = (int)std::ceil((double)25.f/g->dw);
 #endif
     GRT_CUDA(cudaMemsetAsync(g->d_stats, 0, sizeof(PrepStats), st));
+    GRT_CUDA(cudaMemsetAsync(g->d_hmax, 0xff, sizeof(int)*GRT_MAX_LAYERS, st));
     GRT_CUDA(cudaMemsetAsync(g->d_ties, 0, 2*sizeof(unsigned), st));
     if (N > 0)
     {
@@ -1533,7 +1570,7 @@ int grt_gas_optical_depth(grt_gas *g, real_t const *p_atm_in, real_t const *t_in
                                                method != 2 ? g->d_vkey : nullptr,
                                                method != 2 ? g->d_vidx : nullptr,
                                                patch ? g->d_ties : nullptr, g->d_tie_overflow,
-                                               kTieCapacity);
+                                               kTieCapacity, method == 2 ? g->d_hmax : nullptr);
         ++launches;
     }
     // The one host synchronisation of the call: K1's counters and its list of near-tie
@@ -1634,7 +1671,34 @@ int grt_gas_optical_depth(grt_gas *g, real_t const *p_atm_in, real_t const *t_in
     }
     ++launches;
     GRT_CUDA(cudaEventRecord(g->ev[2], st));
-    if (N > 0)
+    // GRT_CORE=gather: the line cores through core_gather_kernel -- no atomics, optical depths
+    // bit-reproducible from run to run -- at three times the core kernel's time (measured,
+    // profiles/r02k_core_gather_ab.txt: config 2 526 -> 600 ms per step); the default is the
+    // scatter with double atomics (3 % of the samples; the wing sweep has none).
+    bool gather = false;
+    if (char const *env = getenv("GRT_CORE")) gather = strcmp(env, "gather") == 0;
+    if (N > 0 && gather)
+    {
+        CoreGather cg;
+        cg.first_at = g->d_first_at;
+        cg.num_granules = g->num_granules;
+        cg.hmax = g->d_hmax;
+        cg.margin_pts = (int)std::ceil(g->max_abs_delta*pmax/g->dw) + 3;
+        cg.num_tiles = (int)((g->nw + kCoreTile - 1)/kCoreTile);
+        cg.work_counter = g->d_work_counter;
+        // lowest pressure first: the widest Doppler cores, i.e. the most expensive tiles
+        std::vector<std::pair<double, int>> by_p((size_t)L);
+        for (int i=0; i<L; ++i) by_p[i] = {std::fabs(p_atm[i]) + std::fabs(p_atm[i+1]), i};
+        std::stable_sort(by_p.begin(), by_p.end());
+        for (int i=0; i<L; ++i) cg.layer_order[i] = (short)by_p[i].second;
+        GRT_CUDA(cudaMemsetAsync(g->d_work_counter, 0, sizeof(unsigned int), st));
+        unsigned const items = (unsigned)cg.num_tiles*(unsigned)L;
+        unsigned const want = (items + kCoreWarps - 1)/kCoreWarps;
+        unsigned const blocks = std::min(want, (unsigned)(4*sm_count(g->device)));
+        core_gather_kernel<<<blocks, kCoreWarps*32, 0, st>>>(sp, cg);
+        ++launches;
+    }
+    else if (N > 0)
     {
         dim3 grid((unsigned)((N + 127)/128), (unsigned)L);
         core_sweep_kernel<<<grid, 128, 0, st>>>(sp);

@@ -957,8 +957,12 @@ static int launch_sw(int device, cudaStream_t st, int num_levels, double w0, dou
                      typename FluxOut<FUSED>::type *up, typename FluxOut<FUSED>::type *down,
                      uint64_t first, uint64_t last)
 {
-    char const *which = getenv("GRT_SW_KERNEL");      // measurement knob: "thread" = sw_kernel
-    if (which == nullptr || strcmp(which, "thread") != 0)
+    // Measured on config 2 (profiles/r02j_sw_staged.txt): the staged kernel moves 5.4 GB of DRAM
+    // traffic per launch instead of 31.5 GB but takes 16.5 ms against 11.2 ms -- with one warp in
+    // four on the recursions and 24 warps per SM its in-order dependency chains leave the FP64
+    // pipe half idle -- so sw_kernel stays the default; GRT_SW_KERNEL=staged selects this one.
+    char const *which = getenv("GRT_SW_KERNEL");
+    if (which != nullptr && strcmp(which, "staged") == 0)
     {
         static bool configured[64][2];
         int const L = num_levels - 1;

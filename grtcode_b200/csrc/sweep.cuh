@@ -1284,6 +1284,16 @@ class_histogram_kernel(SweepParams const p, int const tile_points, unsigned long
 }
 
 
+// Half-width of a record's |x| < xlim1 window in grid points, rounded up generously (the
+// samples themselves are selected by the reference's float comparison).
+__host__ __device__ __forceinline__ int core_half_width(float const repwid, float const xlim1,
+                                                        bool const flagged, double const wres,
+                                                        int const F)
+{
+    double const hd = flagged ? (double)(2*F + 2) : (double)xlim1/((double)repwid*wres) + 2.;
+    return hd < (double)(2*F + 2) ? (int)hd : 2*F + 2;
+}
+
 // K3c: samples with |x| < XLIM1 (Humlicek regions 2, 3 and CPF12) of every Voigt-branch
 // record, plus every sample of the rare records flagged kHwCoreOnly.  One thread per
 // record walks outwards from the line centre (fc, fc-1, fc+1, ...): the records of a warp
@@ -1323,9 +1333,7 @@ core_sweep_kernel(SweepParams const p)
     int const F = p.fsteps;
     int const s = max(fc - F, 0);
     int const e = min(fc + F, p.nw - 1);
-    // Half-width of the |x| < xlim1 window in grid points, rounded up generously.
-    double const hd = flagged ? (double)(2*F + 2) : (double)xlim1/((double)B.x*p.wres) + 2.;
-    int const h = hd < (double)(2*F + 2) ? (int)hd : 2*F + 2;
+    int const h = core_half_width(B.x, xlim1, flagged, p.wres, F);
     wn_t const wres = (wn_t)p.wres;
     wn_t const dwno = wn_add(wn_index_times(s, wres), (wn_t)p.w0);
     real_t *tau = p.tau + (size_t)layer*p.nw;
@@ -1344,6 +1352,250 @@ core_sweep_kernel(SweepParams const p)
                 double const k = voigt_line_eval(line, xi);
                 atomicAdd(&tau[f], (real_t)(cline*k));
             }
+        }
+    }
+}
+
+
+
+// K3c as a gather (no atomics): a warp owns kCoreTile consecutive grid points of one layer,
+// sums in a shared-memory tile every core sample that falls on them and adds the tile to tau
+// with plain stores -- the records are sorted by centre, so the ones that can reach a tile are
+// a contiguous range of the list (first_at[], one entry per 64 grid points, widened by the
+// layer's largest core half-width and the largest pressure shift).  Results no longer depend
+// on the order in which atomics happen to land: tau is bit-reproducible from run to run.
+//   narrow records (fewer than 32 of their core points in the tile) are queued and walked 32
+//     at a time, one record per lane, point by point from the low end of their windows; lanes
+//     that meet on a grid point in the same step (neighbouring lines with the same nearest
+//     grid point) are summed by a segmented warp scan before one of them stores;
+//   wide records (Doppler cores of the shortwave at low pressure: up to a thousand points) are
+//     walked by the whole warp, 32 consecutive points per step: every lane in the same Voigt
+//     region, no conflicts, full lanes.
+constexpr int kCoreTile = 512;
+constexpr int kCoreWarps = 8;
+constexpr int kCoreGranule = 64;
+
+struct CoreGather
+{
+    int const *first_at;           // [num_granules + 1]: first record with v0 >= w0 + (64k - 1) wres
+    int num_granules;
+    int const *hmax;               // [layers]: largest core half-width of the layer's records, or -1
+    int margin_pts;                // pressure shift + rounding slack, in grid points
+    int num_tiles;
+    unsigned *work_counter;
+    short layer_order[GRT_MAX_LAYERS];   // layers by pressure, lowest (widest cores) first
+};
+
+struct CoreRec
+{
+    wn_t vline, repwid, dwno;
+    double cline;
+    float y, xlim0, xlim1;
+    int s, a, b;                   // window start; first and last point of this tile to visit
+    bool flagged;
+};
+
+// The record's core points inside [lo, hi]: false if there are none.
+__device__ __forceinline__ bool core_rec_load(SweepParams const &p, LineRec const *rp,
+                                              int const lo, int const hi, CoreRec &c)
+{
+    float4 const B = *reinterpret_cast<float4 const *>(&rp->repwid);   // repwid, yq, yrrtpi, fc
+    float4 const C = *reinterpret_cast<float4 const *>(&rp->hw0);      // hw0, y, xlim0, xlim1
+    int const fc = __float_as_int(B.w);
+    int const hw0 = __float_as_int(C.x);
+    if (fc == kSkip || hw0 == kHwLorentz) return false;
+    c.flagged = hw0 == kHwCoreOnly;
+    if (!c.flagged && C.w <= 0.f) return false;
+    int const F = p.fsteps;
+    int const h = core_half_width(B.x, C.w, c.flagged, p.wres, F);
+    c.s = max(fc - F, 0);
+    int const e = min(fc + F, p.nw - 1);
+    c.a = max(max(fc - h, c.s), lo);
+    c.b = min(min(fc + h, e), hi);
+    if (c.a > c.b) return false;
+    c.y = C.y;
+    c.xlim0 = C.z;
+    c.xlim1 = C.w;
+#ifdef GRT_SINGLE
+    float4 const A = *reinterpret_cast<float4 const *>(&rp->v);
+    c.vline = A.x;
+    c.cline = (double)A.y;
+    c.repwid = B.x;
+#else
+    double2 const vc = *reinterpret_cast<double2 const *>(&rp->v);
+    c.vline = vc.x;
+    c.cline = vc.y;
+    c.repwid = (double)B.x;
+#endif
+    c.dwno = wn_add(wn_index_times(c.s, (wn_t)p.wres), (wn_t)p.w0);
+    return true;
+}
+
+__device__ __forceinline__ bool core_sample(CoreRec const &c, VoigtLine &line, wn_t const wres,
+                                            int const f, double &val)
+{
+    float const xi = abscissa_from(wn_add(c.dwno, wn_index_times(f - c.s, wres)), c.vline, c.repwid);
+    if (c.flagged || fabsf(xi) < c.xlim1)
+    {
+        val = c.cline*voigt_line_eval(line, xi);
+        return true;
+    }
+    return false;
+}
+
+// One group of at most 32 queued narrow records, one per lane.
+__device__ __forceinline__ void core_narrow_group(SweepParams const &p, LineRec const *layer_recs,
+                                                  unsigned const *queue, int const n, int const lo,
+                                                  int const hi, int const lane, double *acc)
+{
+    CoreRec c;
+    c.a = 0;
+    VoigtLine line;
+    int len = 0;
+    if (lane < n)
+    {
+        core_rec_load(p, layer_recs + queue[lane], lo, hi, c);
+        voigt_line_init(line, c.y, c.xlim0, c.xlim1);
+        len = c.b - c.a + 1;
+    }
+    int const maxlen = __reduce_max_sync(0xffffffffu, len);
+    wn_t const wres = (wn_t)p.wres;
+    for (int t=0; t<maxlen; ++t)
+    {
+        double val = 0.;
+        bool active = false;
+        int const f = c.a + t;
+        if (t < len) active = core_sample(c, line, wres, f, val);
+        int const key = active ? f : -1 - lane;
+        // neighbouring lanes on the same grid point: segmented inclusive scan over each run
+        // of adjacent lanes with one key (a run starts where the key changes)
+        int const prev = __shfl_up_sync(0xffffffffu, key, 1);
+        unsigned const heads = __ballot_sync(0xffffffffu, lane == 0 || prev != key);
+        if (heads != 0xffffffffu)
+        {
+            int const start = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));
+#pragma unroll
+            for (int off=1; off<32; off<<=1)
+            {
+                double const v2 = __shfl_up_sync(0xffffffffu, val, off);
+                if (lane - off >= start) val += v2;
+            }
+        }
+        int const next = __shfl_down_sync(0xffffffffu, key, 1);
+        bool const writer = active && (lane == 31 || next != key);
+        // runs of the same point that are not adjacent (lines of two molecules interleaved):
+        // the writers take turns, lowest lane first
+        unsigned const peers = __match_any_sync(0xffffffffu, writer ? key : -1 - lane);
+        int const rank = __popc(peers & ((1u << lane) - 1u));
+        int const rounds = __reduce_max_sync(0xffffffffu, writer ? __popc(peers) : 1);
+        for (int r=0; r<rounds; ++r)
+        {
+            if (writer && rank == r) acc[key - lo] += val;
+            __syncwarp();
+        }
+    }
+}
+
+// One wide record, the whole warp on it.
+__device__ __forceinline__ void core_wide_record(SweepParams const &p, LineRec const *rp,
+                                                 int const lo, int const hi, int const lane,
+                                                 double *acc)
+{
+    CoreRec c;
+    if (!core_rec_load(p, rp, lo, hi, c)) return;
+    VoigtLine line;
+    voigt_line_init(line, c.y, c.xlim0, c.xlim1);
+    wn_t const wres = (wn_t)p.wres;
+    for (int f0=c.a; f0<=c.b; f0+=32)
+    {
+        int const f = f0 + lane;
+        double val;
+        if (f <= c.b && core_sample(c, line, wres, f, val)) acc[f - lo] += val;
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(kCoreWarps*32)
+core_gather_kernel(SweepParams const p, CoreGather const q)
+{
+    __shared__ double s_acc[kCoreWarps][kCoreTile];
+    __shared__ unsigned s_queue[kCoreWarps][64];
+    int const lane = threadIdx.x & 31;
+    int const warp = threadIdx.x >> 5;
+    double *acc = s_acc[warp];
+    unsigned *queue = s_queue[warp];
+    unsigned const total = (unsigned)q.num_tiles*(unsigned)p.num_layers;
+    for (;;)
+    {
+        unsigned item = 0;
+        if (lane == 0) item = atomicAdd(q.work_counter, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= total) break;
+        int const layer = q.layer_order[item/(unsigned)q.num_tiles];
+        int const tile = (int)(item%(unsigned)q.num_tiles);
+        int const H = q.hmax[layer];
+        if (H < 0) continue;
+        int const lo = tile*kCoreTile;
+        int const hi = min(lo + kCoreTile - 1, p.nw - 1);
+        int const M = H + q.margin_pts;
+        int const g0 = max(lo - M, 0)/kCoreGranule;
+        int const g1 = min((hi + M)/kCoreGranule + 1, q.num_granules);
+        unsigned const cfirst = (unsigned)q.first_at[g0];
+        unsigned const clast = (unsigned)q.first_at[g1];
+        LineRec const *layer_recs = p.recs + (size_t)layer*p.num_lines;
+        bool touched = false;
+        int qn = 0;
+        for (unsigned base=cfirst; base<clast; base+=32u)
+        {
+            unsigned const r = base + (unsigned)lane;
+            int extent = 0;
+            if (r < clast)
+            {
+                CoreRec c;
+                if (core_rec_load(p, layer_recs + r, lo, hi, c)) extent = c.b - c.a + 1;
+            }
+            unsigned const narrow = __ballot_sync(0xffffffffu, extent > 0 && extent < 32);
+            unsigned wide = __ballot_sync(0xffffffffu, extent >= 32);
+            if ((narrow | wide) && !touched)
+            {
+                for (int k=lane; k<kCoreTile; k+=32) acc[k] = 0.;
+                touched = true;
+                __syncwarp();
+            }
+            if (narrow)
+            {
+                if ((narrow >> lane) & 1u) queue[qn + __popc(narrow & ((1u << lane) - 1u))] = r;
+                qn += __popc(narrow);
+                __syncwarp();
+                if (qn >= 32)
+                {
+                    core_narrow_group(p, layer_recs, queue, 32, lo, hi, lane, acc);
+                    unsigned const keep = (lane < qn - 32) ? queue[32 + lane] : 0u;
+                    __syncwarp();
+                    if (lane < qn - 32) queue[lane] = keep;
+                    qn -= 32;
+                    __syncwarp();
+                }
+            }
+            while (wide)
+            {
+                int const b = __ffs(wide) - 1;
+                wide &= wide - 1;
+                core_wide_record(p, layer_recs + (base + (unsigned)b), lo, hi, lane, acc);
+            }
+        }
+        if (qn > 0) core_narrow_group(p, layer_recs, queue, qn, lo, hi, lane, acc);
+        if (touched)
+        {
+            __syncwarp();
+            real_t *tau = p.tau + (size_t)layer*p.nw;
+            for (int k=lane; k<kCoreTile; k+=32)
+            {
+                double const v = acc[k];
+                int const f = lo + k;
+                if (f <= hi && v != 0.) tau[f] = (real_t)((double)tau[f] + v);
+            }
+            __syncwarp();
         }
     }
 }

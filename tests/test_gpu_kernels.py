@@ -64,6 +64,32 @@ def test_sweep_variants_agree(built, tmp_path, dw, levels):
     assert parity.relative_error(tau, ref).max() <= 1e-12
 
 
+@pytest.mark.parametrize("case", ["lw_0.01", "lw_0.1_dense", "sw_low_pressure"])
+def test_core_gather_matches_the_scatter_kernel_and_is_reproducible(built, tmp_path, case):
+    """core_gather_kernel (no atomics: a warp owns 512 grid points of a layer) against
+    core_sweep_kernel (one thread per record, double atomics): the same samples in a different
+    order -- and, unlike the scatter, the same bits from run to run.  The cases cover narrow
+    cores with several lines per grid point (the segmented warp sum), and the wide Doppler
+    cores of the shortwave at low pressure (whole-warp walk, records reaching over tiles)."""
+    import numpy as np
+    from grtcode_b200 import synth
+    from tests import parity
+    if case == "lw_0.01":
+        args = (700., 760., 0.01, 12, {synth.H2O: 6000, synth.CO2: 9000, synth.O3: 5000}, 51)
+    elif case == "lw_0.1_dense":
+        args = (600., 700., 0.1, 20, {synth.H2O: 4000, synth.CO2: 6000, synth.N2O: 3000}, 52)
+    else:
+        args = (29950., 30050., 0.01, 40, {synth.H2O: 900, synth.O3: 900, synth.O2: 300}, 53)
+    a, sa = _tau(tmp_path, *args, 2, {"GRT_CORE": "gather"})
+    b, _ = _tau(tmp_path, *args, 2, {"GRT_CORE": "gather"})
+    c, sc = _tau(tmp_path, *args, 2, {"GRT_CORE": "scatter"})
+    assert a.tobytes() == b.tobytes()
+    rel = parity.relative_error(a, c)
+    print(f"{case}: gather vs scatter max rel {rel.max():.2e}; core {sa['core_ns']/1e6:.3f} ms "
+          f"(gather) / {sc['core_ns']/1e6:.3f} ms (scatter)")
+    assert rel.max() <= 1e-12
+
+
 @pytest.mark.parametrize("method", [0, 1])
 def test_binned_sort_paths_agree(built, tmp_path, method):
     """Two device-wide radix passes against CUB's segmented sort: both stable, so the same

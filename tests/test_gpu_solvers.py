@@ -150,10 +150,14 @@ def _sw_optics(case, layers, n, rng):
     return tau, omega, g
 
 
+@pytest.mark.parametrize("kernel", ["thread", "staged"])
 @pytest.mark.parametrize("layers", [1, 7, 200])
 @pytest.mark.parametrize("case", ["simple", "thick", "thin", "strong", "decades",
                                   "pure_absorption", "conservative", "mixed_branches"])
-def test_shortwave_reference_cases(built, case, layers):
+def test_shortwave_reference_cases(built, case, layers, kernel, monkeypatch):
+    """kernel: sw_kernel (one thread per wavenumber, the default) and sw_staged_kernel
+    (GRT_SW_KERNEL=staged: layer values staged through an L2-resident slab)."""
+    monkeypatch.setenv("GRT_SW_KERNEL", kernel)
     r = R.Ref()
     n = int(r.grid(W0, WN, DW).n)
     rng = np.random.default_rng(13)
@@ -217,3 +221,31 @@ def test_rayleigh_and_add_optics_match_the_reference(built):
     assert _rel(tau, want_arr[0]) <= 1e-14
     assert _rel(om, want_arr[1]) <= 1e-13
     assert _rel(gg, want_arr[2]) <= 1e-13
+
+
+def test_staged_shortwave_column_matches_the_thread_kernel(built, monkeypatch):
+    """The fused column call (Rayleigh mixed in, broadband sums in the kernel) through both
+    shortwave kernels: the same expressions on the same operands, so the broadband fluxes
+    agree to the order of their sums."""
+    layers, n = 54, 20001
+    grid = api.spectral_grid(1000., 1200., 0.01)
+    rng = np.random.default_rng(3)
+    tau = np.exp(rng.uniform(np.log(1e-6), np.log(30.), (layers, n)))
+    p = np.exp(np.linspace(np.log(0.02), np.log(1000.), layers + 1))
+    alb = np.full(n, 0.2)
+    solar = np.full(n, 1./(0.01*(n - 1)))
+    gas = api.OpticsObject(layers, grid)
+    gas.update(tau, np.zeros_like(tau), np.zeros_like(tau))
+    out = {}
+    for kernel in ("thread", "staged"):
+        monkeypatch.setenv("GRT_SW_KERNEL", kernel)
+        sw = api.ShortwaveSolver(layers + 1, grid)
+        out[kernel] = [np.array(x, dtype=np.float64)
+                       for x in sw.column(gas, p, 0.7, 0.5, alb, alb, 1361., solar,
+                                          window=(100, n - 200))]
+        sw.close()
+    gas.close()
+    for a, b in zip(out["thread"], out["staged"]):
+        assert np.all(np.isfinite(a)) and a.max() > 1.
+        np.testing.assert_allclose(b, a, rtol=1e-12 if api.DTYPE == np.float64 else 1e-6, atol=0.)
+
