@@ -997,6 +997,15 @@ __device__ __forceinline__ void process_batch(LineRec const *stage, int const cn
 }
 
 
+// Measurement knobs of the coarse-grid (grouped) kernels: stages of the record ring and
+// resident blocks per SM the register budget is set for (0 = the general rule below).
+#ifndef GRT_COARSE_STAGES
+#define GRT_COARSE_STAGES 4
+#endif
+#ifndef GRT_COARSE_MINBLOCKS
+#define GRT_COARSE_MINBLOCKS 0
+#endif
+
 template <int PTS, int NL, int LN = 32>
 struct SweepConfig
 {
@@ -1005,10 +1014,12 @@ struct SweepConfig
     // cycles on a batch and two stages hide the copy; the grouped kernels of the coarse grids
     // go through a batch in a fraction of that (narrow tiles, two or four lines at a time), so
     // they keep four batches in flight.
-    static constexpr int kStages = (LN == 32) ? 2 : 4;
+    static constexpr int kStages = (LN == 32) ? 2 : GRT_COARSE_STAGES;
     static constexpr int kRingBytes = kSweepWarps*kStages*kStageBytes + kSweepWarps*kStages*8;
     // registers: PTS*NL accumulators + PTS cached abscissae, all double
-    static constexpr int kMinBlocks = (PTS*NL <= 8) ? 3 : ((PTS*NL <= 16) ? 2 : 1);
+    static constexpr int kMinBlocks = (LN != 32 && PTS <= 4 && GRT_COARSE_MINBLOCKS > 0)
+                                          ? GRT_COARSE_MINBLOCKS
+                                          : ((PTS*NL <= 8) ? 3 : ((PTS*NL <= 16) ? 2 : 1));
 };
 
 // Entries of the fl(i*wres) table for a kernel with tiles of LN*PTS points: i = f - s runs
