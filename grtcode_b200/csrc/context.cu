@@ -27,6 +27,12 @@ int stream_of(int device, cudaStream_t *stream)
         cudaDeviceProp prop;
         GRT_CUDA(cudaGetDeviceProperties(&prop, device));
         g_sm_count[device] = prop.multiProcessorCount;
+        // grt_malloc / grt_free are stream-ordered (below): keep freed blocks in the device's
+        // pool instead of returning them to the driver at every synchronisation
+        cudaMemPool_t pool;
+        GRT_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        unsigned long long keep = ~0ull;
+        GRT_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
         g_have_stream[device] = true;
     }
     *stream = g_streams[device];
@@ -69,11 +75,17 @@ int grt_device_name(int device, char *buf, int len)
     return 0;
 }
 
+// Device arrays of the public objects (Optics_t, solver buffers): allocated and freed in the
+// order of the device's stream, on which every kernel and copy of this library runs, from the
+// device's memory pool.  add_optics allocates its result at every call and the caller destroys
+// it (optics.c:84-148): with cudaMalloc / cudaFree that was two driver calls and a full
+// synchronisation per 6.5 GB object of a config-2 step.
 int grt_malloc(int device, void **ptr_dev, size_t bytes)
 {
     if (ptr_dev == nullptr) return fail("null pointer");
-    GRT_CUDA(cudaSetDevice(device));
-    GRT_CUDA(cudaMalloc(ptr_dev, bytes > 0 ? bytes : 1));
+    cudaStream_t s;
+    GRT_TRY(grt::stream_of(device, &s));
+    GRT_CUDA(cudaMallocAsync(ptr_dev, bytes > 0 ? bytes : 1, s));
     return 0;
 }
 
@@ -81,8 +93,7 @@ int grt_free(int device, void *ptr_dev)
 {
     cudaStream_t s;
     GRT_TRY(grt::stream_of(device, &s));
-    GRT_CUDA(cudaStreamSynchronize(s));
-    GRT_CUDA(cudaFree(ptr_dev));
+    GRT_CUDA(cudaFreeAsync(ptr_dev, s));
     return 0;
 }
 

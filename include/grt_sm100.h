@@ -40,7 +40,11 @@ typedef double grt_real;
 #define GRT_NUM_CIA_SPECIES 2
 
 /* ---- device + memory: replaces the gmalloc/gfree/gmemset/gmemcpy macros of
- * utilities/src/debug.h:311-348 and get_num_gpus of utilities/src/device.c:26. */
+ * utilities/src/debug.h:311-348 and get_num_gpus of utilities/src/device.c:26.
+ * grt_malloc / grt_free are ordered on the library stream (cudaMallocAsync / cudaFreeAsync from
+ * the device's pool, freed blocks kept for reuse): a pointer is valid for every later call of
+ * this library at once; code that touches it on ANOTHER stream must first synchronise with the
+ * library stream (any call that returns data to the host does). */
 int grt_device_count(int *count);
 int grt_device_name(int device, char *buf, int len);
 int grt_malloc(int device, void **ptr_dev, size_t bytes);

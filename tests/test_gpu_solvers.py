@@ -245,7 +245,8 @@ def test_staged_shortwave_column_matches_the_thread_kernel(built, monkeypatch):
                                           window=(100, n - 200))]
         sw.close()
     gas.close()
+    assert out["thread"][1].max() > 100.         # the direct beam at the top: tsi*mu over the window
     for a, b in zip(out["thread"], out["staged"]):
-        assert np.all(np.isfinite(a)) and a.max() > 1.
+        assert np.all(np.isfinite(a)) and a.max() > 0.
         np.testing.assert_allclose(b, a, rtol=1e-12 if api.DTYPE == np.float64 else 1e-6, atol=0.)
 
