@@ -28,6 +28,7 @@ namespace grt {
 constexpr int kBinThreads = 256;          // one warp per bin of a gather group
 constexpr int kNip = 3;                 // spectral_bin-internal.h:30
 constexpr int kBinLanePerLine = 16;     // bins of up to 16 points: local lines lane per line
+constexpr int kBinLinePerWarp = 128;    // bins of up to 128 points: local lines one at a time
 
 struct BinGeometry
 {
@@ -466,9 +467,63 @@ bin_gather_kernel(BinParams const p, BinRanges32 const *ranges)
                     }
                 }
             }
+            else if (npts <= kBinLinePerWarp)
+            {
+                // fine grid, bins of up to 128 points: line by line, a lane per grid point
+                // (32 at a time).  The line's Voigt constants are formed once, and only if one
+                // of its samples in this bin lies inside |x| < XLIM0 (voigt_line_eval: the
+                // per-line form of RFM_voigt.c:109-278, bit-identical to voigt_core and about
+                // half its instructions in the CPF12 sums); chunks wholly in the far wing
+                // take the far-wing quotient directly.
+                double *mine = sh_acc + g*ppb;
+                for (unsigned i=R.loc_lo; i<R.loc_hi; ++i)
+                {
+                    double2 const A = wa[i];
+                    float4 const B = wb[i];
+                    double const repwid = widen_positive(B.x);
+                    bool const lorentz = B.w != B.w;
+                    bool have_line = false;
+                    VoigtLine line;
+                    evals += (unsigned long long)npts;
+#pragma unroll 1
+                    for (int pbase=0; pbase<npts; pbase+=32)
+                    {
+                        int const pt = pbase + lane;
+                        bool const live = pt < npts;
+                        double const loc_t = __dadd_rn(loc_w, __dmul_rn((double)(live ? pt : pbase), b.wres));
+                        float const xi = abscissa_from(loc_t, A.x, repwid);
+                        float const ax = fabsf(xi);
+                        double k;
+                        if (lorentz)
+                        {
+                            k = A.y/widen_positive(xi*xi + B.y);      // RFM_voigt.c:97-106
+                        }
+                        else if (!__any_sync(0xffffffffu, ax < B.w))
+                        {
+                            k = widen_positive(div_exact(B.z, ax*ax + B.y));
+                        }
+                        else
+                        {
+                            if (!have_line)
+                            {
+                                LineRec const *r = recs + i;
+                                voigt_line_init(line, r->y, r->xlim0, r->xlim1);
+                                have_line = true;
+                            }
+                            k = voigt_line_eval(line, xi);
+                        }
+                        if (live)
+                        {
+                            if (lorentz) mine[pt] += k;
+                            else mine[pt] = fma(A.y, k, mine[pt]);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
             else
             {
-                // fine grid: a lane per grid point (32 at a time), every local line in turn
+                // finer grids still: a lane per grid point (32 at a time), every local line in turn
                 for (int pbase=0; pbase<npts; pbase+=32)
                 {
                     int const pt = pbase + lane;

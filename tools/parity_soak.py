@@ -72,7 +72,10 @@ def _oracle_child(path, ds, c, col, mols):
     np.savez(path, **{k: v for k, v in want.items() if isinstance(v, np.ndarray)})
 
 
-def run_case(root: str, c: dict) -> dict:
+def run_case(root: str, c: dict, isolate: bool = True) -> dict:
+    """isolate: the reference in a forked child (this tool, whose parent never enters the
+    reference's OpenMP runtime); False = in this process (pytest, where earlier tests have
+    started OpenMP threads that a forked child would wait for forever)."""
     ds = parity.build_dataset(root, c["w0"], c["wn"], c["lines"], c["seed"], c["cfcs"], c["cias"])
     mols = tuple(c["lines"].keys())
     col = synth.make_column(c["levels"], np.random.default_rng(c["seed"]), molecules=mols,
@@ -81,13 +84,18 @@ def run_case(root: str, c: dict) -> dict:
     # (kernels.c:214-262 with bracket() on empty ranges) and may take the process with them
     import multiprocessing as mp
     path = os.path.join(root, "want.npz")
-    child = mp.get_context("fork").Process(target=_oracle_child, args=(path, ds, c, col, mols))
-    child.start()
-    child.join()
+    exitcode = 0
+    if isolate:
+        child = mp.get_context("fork").Process(target=_oracle_child, args=(path, ds, c, col, mols))
+        child.start()
+        child.join()
+        exitcode = child.exitcode
+    else:
+        _oracle_child(path, ds, c, col, mols)
     got = parity.gpu_column(ds, c["w0"], c["wn"], c["dw"], col, mols, c["use_ctm"],
                             method=c["method"])
-    if child.exitcode != 0:
-        return {"reference_crashed": int(child.exitcode), "finite": bool(np.isfinite(got["tau"]).all()),
+    if exitcode != 0:
+        return {"reference_crashed": int(exitcode), "finite": bool(np.isfinite(got["tau"]).all()),
                 "tau_max_rel": 0., "tau_gt_1e9": 0, "flux_max_abs": 0., "points": 0,
                 "samples": int(got["stats"]["samples"])}
     want = {k: v.astype(np.float64) for k, v in dict(np.load(path)).items()}
