@@ -20,12 +20,16 @@ for spec in sys.argv[1:]:
     if name != "base":
         env["GRT_LIB_DIR"] = os.path.join(ROOT, "grtcode_b200", "variants", name)
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "2", "--warmup",
-                          "2", "--no-cpu-baseline"], env=env, capture_output=True, text=True)
+                          "2", "--no-cpu-baseline"] + os.environ.get("GRT_AB_ARGS", "").split(),
+                         env=env, capture_output=True, text=True)
     lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
     if not lines:
         print(spec, "FAILED", out.stderr[-1500:])
         continue
     d = json.loads(lines[0])
+    if d.get("roofline") is None:          # binned methods: the step time only
+        print(f"{spec:12s} config2 {d['ms_per_step']:7.1f} ms/step ({d['config']['method']})", flush=True)
+        continue
     k2 = d["roofline"]["kernel_ms_per_step"]
     k3 = d["rfmip"]["kernel_ms_per_column"]
     print(f"{spec:12s} config2 {d['ms_per_step']:7.1f} ms/step  lw_wing {k2['lw_wing']:6.1f} sw_wing "
