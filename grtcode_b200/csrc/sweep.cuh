@@ -452,6 +452,12 @@ __device__ __forceinline__ void add_pair_if(double &a0, double &a1, double const
 #define GRT_SEED_MIX 0
 #endif
 
+// Near-class visits whose window holds the whole tile skip the per-point window predicates
+// (a second copy of the near body: config 2 525.9 -> 523.5 ms, profiles/r02q_ab_near_covered.txt).
+#ifndef GRT_NEAR_COVERED
+#define GRT_NEAR_COVERED 1
+#endif
+
 // Far-edge records share the fast class's pipelined loop (see process_batch).
 #ifndef GRT_MERGE_EDGE
 #define GRT_MERGE_EDGE 0
@@ -698,7 +704,7 @@ __device__ __forceinline__ void line_near_single(RecA const A, float4 const B, f
 // with every dependency chain in flight; each pair of 32-point chunks is then dispatched
 // warp-uniformly to far wing / region 1 / both (measured: -2.4 % on the config-2 step
 // against forming them inside the branches).
-template <int PTS, bool TBL, int LN>
+template <int PTS, bool TBL, int LN, bool COVERED>
 __device__ __forceinline__ void line_near_pairs(RecA const A, float4 const B, float4 const C,
                                           float4 const D, TileCtx const &t,
                                           GridCache<PTS, TBL> &gc,
@@ -734,8 +740,9 @@ __device__ __forceinline__ void line_near_pairs(RecA const A, float4 const B, fl
         int const dhi = max(fc - cb, cb + 2*LN - 1 - fc);
         int const fa = f0 + LN*j;
         int const fb = fa + LN;
-        bool const ina = (fa >= s) && (fa <= e);
-        bool const inb = (fb >= s) && (fb <= e);
+        // COVERED: the window holds the whole tile (the usual case away from window ends)
+        bool const ina = COVERED || ((fa >= s) && (fa <= e));
+        bool const inb = COVERED || ((fb >= s) && (fb <= e));
         float x0, x1;
         unpack2(xi[j/2], x0, x1);
         if (dlo > hw0)
@@ -774,8 +781,20 @@ __device__ __forceinline__ void line_near(RecA const A, float4 const B, float4 c
                                           GridCache<PTS, TBL> &gc,
                                           typename BatchAcc<PTS>::type &acc)
 {
-    if (PTS <= 2) line_near_single<PTS, TBL, LN>(A, B, C, D, t, gc, acc);
-    else line_near_pairs<PTS, TBL, LN>(A, B, C, D, t, gc, acc);
+    if (PTS <= 2)
+    {
+        line_near_single<PTS, TBL, LN>(A, B, C, D, t, gc, acc);
+        return;
+    }
+#if GRT_NEAR_COVERED
+    int const fc = __float_as_int(B.w);
+    if (fc - t.fsteps <= t.warp_base && fc + t.fsteps >= t.warp_last && fc + t.fsteps <= t.nw - 1)
+    {
+        line_near_pairs<PTS, TBL, LN, true>(A, B, C, D, t, gc, acc);
+        return;
+    }
+#endif
+    line_near_pairs<PTS, TBL, LN, false>(A, B, C, D, t, gc, acc);
 }
 
 
